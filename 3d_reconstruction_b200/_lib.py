@@ -1,0 +1,83 @@
+"""ctypes binding of the C-ABI in include/b200m.h (lib/libb200m.so, built in-tree by build.py).
+
+The product path has no CPU fallback: if the shared library is missing, loading raises; if the
+machine has no sm_100 GPU, every compute entry point returns B200M_E_NO_DEVICE and we raise.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libb200m.so")
+
+# every symbol include/b200m.h declares (tests check the library exports all of them)
+SYMBOLS = (
+    "b200m_version",
+    "b200m_last_error_string",
+    "b200m_device_check",
+    "b200m_sm_count",
+    "b200m_bank_prepare_u8",
+    "b200m_workspace_bytes",
+    "b200m_knn2_u8",
+    "b200m_match_pairs_u8",
+    "b200m_set_option",
+    "b200m_get_option",
+    "b200m_debug_dot_tile_u8",
+)
+
+E_NO_DEVICE = -4
+
+
+class B200MError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"b200m error {code}: {msg}")
+        self.code = code
+
+
+_lib = None
+
+
+def lib() -> C.CDLL:
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} is missing: build the CUDA extension first (python -c 'import __graft_entry__ as g; g.build()'). "
+            "There is no CPU fallback.")
+    L = C.CDLL(LIB_PATH)
+    vp, i32, i64, sz, dbl = C.c_void_p, C.c_int32, C.c_int64, C.c_size_t, C.c_double
+    L.b200m_version.restype = C.c_int
+    L.b200m_last_error_string.restype = C.c_char_p
+    L.b200m_device_check.restype = C.c_int
+    L.b200m_sm_count.restype = C.c_int
+    L.b200m_bank_prepare_u8.restype = C.c_int
+    L.b200m_bank_prepare_u8.argtypes = [vp, i32, i64, vp, vp, vp]
+    L.b200m_workspace_bytes.restype = sz
+    L.b200m_workspace_bytes.argtypes = [i64, i64]
+    L.b200m_knn2_u8.restype = C.c_int
+    L.b200m_knn2_u8.argtypes = [vp, vp, vp, i32, i64, vp, i64, vp, vp, vp, sz, vp]
+    L.b200m_match_pairs_u8.restype = C.c_int
+    L.b200m_match_pairs_u8.argtypes = [vp, vp, vp, i32, i64, vp, i64, dbl, C.c_int, vp, vp, vp, vp, i64, vp, sz, vp]
+    L.b200m_set_option.restype = C.c_int
+    L.b200m_set_option.argtypes = [C.c_char_p, i64]
+    L.b200m_get_option.restype = i64
+    L.b200m_get_option.argtypes = [C.c_char_p]
+    L.b200m_debug_dot_tile_u8.restype = C.c_int
+    L.b200m_debug_dot_tile_u8.argtypes = [vp, vp, vp, vp]
+    _lib = L
+    return L
+
+
+def check(rc: int) -> None:
+    if rc != 0:
+        raise B200MError(rc, lib().b200m_last_error_string().decode("utf-8", "replace"))
+
+
+def set_option(name: str, value: int) -> None:
+    check(lib().b200m_set_option(name.encode(), int(value)))
+
+
+def get_option(name: str) -> int:
+    return int(lib().b200m_get_option(name.encode()))

@@ -1,0 +1,110 @@
+"""Packed u8 descriptor bank resident in HBM.
+
+Replaces the per-pair repacking the reference does at matching.py:107-120 (a Python list
+comprehension + fresh host->device copies for every pair) with one packed tensor
+uint8 [n_img, k_stride, 128] + int32 squared norms [n_img, k_stride] + int32 k_per_image [n_img].
+The on-disk source format is the object array written at feature_extraction.py:50
+(`output/all_descriptors.npy`, one [K_i, 128] array per image).
+"""
+from __future__ import annotations
+
+from typing import Sequence
+
+import numpy as np
+import torch
+
+from . import _lib
+
+DESC_DIM = 128
+TILE_T = 256
+
+
+def round_up(x: int, m: int) -> int:
+    return (x + m - 1) // m * m
+
+
+def to_u8_descriptors(a) -> np.ndarray:
+    """[K,128] array -> contiguous uint8, verifying integer values in [0,255] for non-u8 input."""
+    a = np.asarray(a.detach().cpu().numpy() if isinstance(a, torch.Tensor) else a)
+    if a.ndim != 2 or a.shape[1] != DESC_DIM:
+        raise ValueError(f"descriptors must be [K,{DESC_DIM}], got {a.shape}")
+    if a.dtype == np.uint8:
+        return np.ascontiguousarray(a)
+    r = np.rint(a)
+    if a.size and (not np.array_equal(r, a) or r.min() < 0 or r.max() > 255):
+        raise ValueError("the exact u8 path needs integer-valued descriptors in [0,255] (OpenCV SIFT); "
+                         "float descriptors (DISK/SuperPoint) are not handled by this path")
+    return np.ascontiguousarray(r.astype(np.uint8))
+
+
+class DescriptorBank:
+    """Device-resident bank. Padding rows are zero with the sentinel norm (see include/b200m.h)."""
+
+    def __init__(self, desc: torch.Tensor, k_per_image: torch.Tensor, sqnorm: torch.Tensor):
+        self.desc = desc
+        self.k_per_image = k_per_image
+        self.sqnorm = sqnorm
+        self._k_host = None
+
+    # ------------------------------------------------------------------ construction
+    @classmethod
+    def from_packed(cls, desc: torch.Tensor, k_per_image: torch.Tensor) -> "DescriptorBank":
+        """desc: uint8 CUDA [n_img, k_stride, 128], k_stride % 256 == 0. Padding is zeroed in place."""
+        if not desc.is_cuda:
+            raise RuntimeError("the descriptor bank must live on a CUDA device (there is no CPU path)")
+        if desc.dtype != torch.uint8 or desc.dim() != 3 or desc.shape[2] != DESC_DIM or not desc.is_contiguous():
+            raise ValueError("desc must be contiguous uint8 [n_img, k_stride, 128]")
+        if desc.shape[1] % TILE_T != 0:
+            raise ValueError("k_stride must be a multiple of 256")
+        k_per_image = k_per_image.to(device=desc.device, dtype=torch.int32).contiguous()
+        if k_per_image.numel() != desc.shape[0]:
+            raise ValueError("k_per_image must have one entry per image")
+        sqnorm = torch.empty(desc.shape[:2], dtype=torch.int32, device=desc.device)
+        with torch.cuda.device(desc.device):
+            st = torch.cuda.current_stream().cuda_stream
+            _lib.check(_lib.lib().b200m_bank_prepare_u8(desc.data_ptr(), desc.shape[0], desc.shape[1],
+                                                        k_per_image.data_ptr(), sqnorm.data_ptr(), st))
+        return cls(desc, k_per_image, sqnorm)
+
+    @classmethod
+    def from_arrays(cls, arrays: Sequence, device="cuda", k_stride: int | None = None) -> "DescriptorBank":
+        """arrays: one [K_i,128] array per image (u8, or integer-valued float as cv2.SIFT emits)."""
+        u8 = [to_u8_descriptors(a) for a in arrays]
+        if not u8:
+            raise ValueError("empty descriptor list")
+        kmax = max(a.shape[0] for a in u8)
+        ks = round_up(max(kmax, 1), TILE_T) if k_stride is None else int(k_stride)
+        if ks % TILE_T or ks < kmax:
+            raise ValueError("k_stride must be a multiple of 256 and >= the largest image")
+        host = torch.zeros((len(u8), ks, DESC_DIM), dtype=torch.uint8)
+        if torch.cuda.is_available():
+            host = host.pin_memory()
+        hv = host.numpy()
+        for i, a in enumerate(u8):
+            hv[i, :a.shape[0]] = a
+        kpi = torch.tensor([a.shape[0] for a in u8], dtype=torch.int32)
+        dev = torch.device(device)
+        if dev.type != "cuda":
+            raise RuntimeError("the descriptor bank must live on a CUDA device (there is no CPU path)")
+        return cls.from_packed(host.to(dev, non_blocking=True), kpi.to(dev))
+
+    # ------------------------------------------------------------------ accessors
+    @property
+    def n_img(self) -> int:
+        return int(self.desc.shape[0])
+
+    @property
+    def k_stride(self) -> int:
+        return int(self.desc.shape[1])
+
+    @property
+    def device(self) -> torch.device:
+        return self.desc.device
+
+    def k_host(self) -> np.ndarray:
+        if self._k_host is None:
+            self._k_host = self.k_per_image.cpu().numpy()
+        return self._k_host
+
+    def nbytes(self) -> int:
+        return self.desc.numel() + 4 * self.sqnorm.numel() + 4 * self.k_per_image.numel()

@@ -1,0 +1,345 @@
+// C-ABI of the B200 matcher (see include/b200m.h). Host side: argument checks, TMA descriptor
+// encoding, batching of pairs through a bounded workspace, kernel launches. No CPU fallback.
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "../../include/b200m.h"
+#include "match_finalize.cuh"
+#include "match_sweep.cuh"
+
+namespace {
+
+thread_local char g_err[512] = "";
+
+struct Options {
+  int64_t epilogue = 1;
+  int64_t grid = 0;
+  int64_t batch = 0;
+} g_opt;
+
+int fail(int code, const char* fmt, const char* detail = "") {
+  snprintf(g_err, sizeof(g_err), fmt, detail);
+  return code;
+}
+
+#define CUDA_TRY(expr)                                                            \
+  do {                                                                            \
+    cudaError_t e_ = (expr);                                                      \
+    if (e_ != cudaSuccess) {                                                      \
+      snprintf(g_err, sizeof(g_err), "%s failed: %s", #expr, cudaGetErrorString(e_)); \
+      return B200M_E_CUDA;                                                        \
+    }                                                                             \
+  } while (0)
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (fn) return fn;
+  void* p = nullptr;
+  cudaDriverEntryPointQueryResult q;
+  if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+      q != cudaDriverEntryPointSuccess)
+    return nullptr;
+  fn = reinterpret_cast<EncodeTiledFn>(p);
+  return fn;
+}
+
+// [n_rows, 128] u8 row-major, box = 128 rows x 128 B, 128-byte swizzle (matches make_desc_k128).
+int make_row_tmap(CUtensorMap* tm, const void* base, uint64_t n_rows) {
+  EncodeTiledFn enc = get_encode_fn();
+  if (!enc) return fail(B200M_E_NO_DEVICE, "cuTensorMapEncodeTiled entry point unavailable%s");
+  cuuint64_t dims[2] = {128, n_rows};
+  cuuint64_t strides[1] = {128};
+  cuuint32_t box[2] = {128, 128};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void*>(base), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    snprintf(g_err, sizeof(g_err), "cuTensorMapEncodeTiled failed with CUresult %d", static_cast<int>(r));
+    return B200M_E_CUDA;
+  }
+  return B200M_OK;
+}
+
+struct DeviceInfo {
+  int ok = 0;   // 0 unknown, 1 good, -1 bad
+  int sms = 0;
+};
+
+DeviceInfo& device_info() {
+  static thread_local DeviceInfo info;
+  static thread_local int cached_dev = -1;
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess) {
+    info.ok = -1;
+    cudaGetLastError();
+    return info;
+  }
+  if (dev == cached_dev && info.ok != 0) return info;
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, dev) != cudaSuccess) {
+    info.ok = -1;
+    cudaGetLastError();
+    return info;
+  }
+  cached_dev = dev;
+  info.ok = (prop.major == 10) ? 1 : -1;
+  info.sms = prop.multiProcessorCount;
+  return info;
+}
+
+constexpr size_t kSweepSmemBytes = sizeof(b200m::SweepSmem) + 1024;
+
+template <int kMode>
+int launch_sweep(const CUtensorMap& tmap, const b200m::SweepParams& sp, int grid, cudaStream_t st) {
+  static thread_local bool attr_set = false;
+  if (!attr_set) {
+    CUDA_TRY(cudaFuncSetAttribute(b200m::sweep_kernel<kMode>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  static_cast<int>(kSweepSmemBytes)));
+    attr_set = true;
+  }
+  b200m::sweep_kernel<kMode><<<grid, b200m::kThreads, kSweepSmemBytes, st>>>(tmap, sp);
+  CUDA_TRY(cudaGetLastError());
+  return B200M_OK;
+}
+
+int64_t batch_pairs(int64_t k_stride, int64_t n_pairs) {
+  int64_t b = g_opt.batch > 0 ? g_opt.batch : ((int64_t(1) << 24) / (k_stride > 0 ? k_stride : 1));
+  if (b < 1) b = 1;
+  if (b > n_pairs) b = n_pairs;
+  if (b < 1) b = 1;
+  return b;
+}
+
+int check_common(const void* bank, const void* sqnorm, const void* kpi, int32_t n_img, int64_t k_stride,
+                 const void* pairs, int64_t n_pairs) {
+  if (!bank || !sqnorm || !kpi || n_img <= 0) return fail(B200M_E_BAD_ARG, "null bank/sqnorm/k_per_image or n_img <= 0%s");
+  if (k_stride <= 0 || (k_stride % B200M_TILE_T) != 0)
+    return fail(B200M_E_BAD_ARG, "k_stride must be a positive multiple of 256%s");
+  if (n_pairs < 0 || (n_pairs > 0 && !pairs)) return fail(B200M_E_BAD_ARG, "bad pairs / n_pairs%s");
+  if (static_cast<int64_t>(n_img) * k_stride >= (int64_t(1) << 31))
+    return fail(B200M_E_BAD_ARG, "bank has more than 2^31 rows%s");
+  if (device_info().ok != 1) return fail(B200M_E_NO_DEVICE, "no sm_100 CUDA device available (no CPU fallback)%s");
+  return B200M_OK;
+}
+
+// Runs the sweep for pairs [p0, p0 + nb) into the workspace and leaves rowres/colbest ready.
+int sweep_batch(const CUtensorMap& tmap, const int32_t* sqnorm, const int32_t* kpi, int64_t k_stride,
+                const int32_t* pairs_batch, int64_t nb, int4* rowres, unsigned long long* colbest,
+                cudaStream_t st) {
+  CUDA_TRY(cudaMemsetAsync(colbest, 0xFF, sizeof(unsigned long long) * nb * k_stride, st));
+  b200m::SweepParams sp;
+  sp.sqnorm = sqnorm;
+  sp.k_per_image = kpi;
+  sp.pairs = pairs_batch;
+  sp.k_stride = k_stride;
+  sp.n_pairs = static_cast<int32_t>(nb);
+  sp.qtiles = static_cast<int32_t>(k_stride / B200M_TILE_Q);
+  sp.rowres = rowres;
+  sp.colbest = colbest;
+  int grid = g_opt.grid > 0 ? static_cast<int>(g_opt.grid) : device_info().sms;
+  const int64_t items = nb * sp.qtiles;
+  if (grid > items) grid = static_cast<int>(items);
+  if (grid < 1) grid = 1;
+  return g_opt.epilogue == 0 ? launch_sweep<0>(tmap, sp, grid, st) : launch_sweep<1>(tmap, sp, grid, st);
+}
+
+}  // namespace
+
+extern "C" {
+
+int b200m_version(void) { return B200M_VERSION; }
+const char* b200m_last_error_string(void) { return g_err; }
+
+int b200m_device_check(void) {
+  if (device_info().ok != 1) return fail(B200M_E_NO_DEVICE, "no sm_100 CUDA device available%s");
+  return B200M_OK;
+}
+
+int b200m_sm_count(void) {
+  if (device_info().ok != 1) return fail(B200M_E_NO_DEVICE, "no sm_100 CUDA device available%s");
+  return device_info().sms;
+}
+
+int b200m_set_option(const char* name, int64_t value) {
+  if (!name) return fail(B200M_E_BAD_ARG, "null option name%s");
+  if (!strcmp(name, "epilogue")) { g_opt.epilogue = value; return B200M_OK; }
+  if (!strcmp(name, "grid")) { g_opt.grid = value; return B200M_OK; }
+  if (!strcmp(name, "batch")) { g_opt.batch = value; return B200M_OK; }
+  return fail(B200M_E_BAD_ARG, "unknown option %s", name);
+}
+
+int64_t b200m_get_option(const char* name) {
+  if (!name) return -1;
+  if (!strcmp(name, "epilogue")) return g_opt.epilogue;
+  if (!strcmp(name, "grid")) return g_opt.grid;
+  if (!strcmp(name, "batch")) return g_opt.batch;
+  return -1;
+}
+
+int b200m_bank_prepare_u8(uint8_t* bank, int32_t n_img, int64_t k_stride, const int32_t* k_per_image,
+                          int32_t* sqnorm, void* stream) {
+  if (!bank || !k_per_image || !sqnorm || n_img <= 0) return fail(B200M_E_BAD_ARG, "null argument or n_img <= 0%s");
+  if (k_stride <= 0 || (k_stride % B200M_TILE_T) != 0)
+    return fail(B200M_E_BAD_ARG, "k_stride must be a positive multiple of 256%s");
+  if (device_info().ok != 1) return fail(B200M_E_NO_DEVICE, "no sm_100 CUDA device available (no CPU fallback)%s");
+  const int64_t n_rows = static_cast<int64_t>(n_img) * k_stride;
+  const int block = 256;
+  int64_t blocks = (n_rows * 32 + block - 1) / block;
+  const int64_t max_blocks = static_cast<int64_t>(device_info().sms) * 16;
+  if (blocks > max_blocks) blocks = max_blocks;
+  b200m::bank_prepare_kernel<<<static_cast<int>(blocks), block, 0, static_cast<cudaStream_t>(stream)>>>(
+      bank, n_rows, k_stride, k_per_image, sqnorm, B200M_PAD_NORM);
+  CUDA_TRY(cudaGetLastError());
+  return B200M_OK;
+}
+
+size_t b200m_workspace_bytes(int64_t k_stride, int64_t n_pairs) {
+  if (k_stride <= 0 || n_pairs <= 0) return 256;
+  const int64_t b = batch_pairs(k_stride, n_pairs);
+  return static_cast<size_t>(b) * k_stride * (sizeof(int4) + sizeof(unsigned long long)) + 256;
+}
+
+int b200m_knn2_u8(const uint8_t* bank, const int32_t* sqnorm, const int32_t* k_per_image, int32_t n_img,
+                  int64_t k_stride, const int32_t* pairs, int64_t n_pairs, int32_t* out_train_idx,
+                  float* out_dist, void* workspace, size_t workspace_bytes, void* stream) {
+  int rc = check_common(bank, sqnorm, k_per_image, n_img, k_stride, pairs, n_pairs);
+  if (rc) return rc;
+  if (n_pairs == 0) return B200M_OK;
+  if (!out_train_idx || !out_dist || !workspace) return fail(B200M_E_BAD_ARG, "null output / workspace%s");
+  if (workspace_bytes < b200m_workspace_bytes(k_stride, n_pairs)) return fail(B200M_E_WORKSPACE, "workspace too small%s");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  CUtensorMap tmap;
+  rc = make_row_tmap(&tmap, bank, static_cast<uint64_t>(n_img) * k_stride);
+  if (rc) return rc;
+  const int64_t B = batch_pairs(k_stride, n_pairs);
+  uintptr_t wsp = (reinterpret_cast<uintptr_t>(workspace) + 255) & ~uintptr_t(255);
+  int4* rowres = reinterpret_cast<int4*>(wsp);
+  unsigned long long* colbest = reinterpret_cast<unsigned long long*>(rowres + B * k_stride);
+  for (int64_t p0 = 0; p0 < n_pairs; p0 += B) {
+    const int64_t nb = (n_pairs - p0 < B) ? (n_pairs - p0) : B;
+    rc = sweep_batch(tmap, sqnorm, k_per_image, k_stride, pairs + 2 * p0, nb, rowres, colbest, st);
+    if (rc) return rc;
+    dim3 grid(static_cast<unsigned>((k_stride + 255) / 256), static_cast<unsigned>(nb));
+    b200m::knn2_finalize_kernel<<<grid, 256, 0, st>>>(rowres, pairs + 2 * p0, k_per_image, k_stride,
+                                                      out_train_idx + 2 * p0 * k_stride, out_dist + 2 * p0 * k_stride);
+    CUDA_TRY(cudaGetLastError());
+  }
+  return B200M_OK;
+}
+
+int b200m_match_pairs_u8(const uint8_t* bank, const int32_t* sqnorm, const int32_t* k_per_image, int32_t n_img,
+                         int64_t k_stride, const int32_t* pairs, int64_t n_pairs, double ratio, int mutual,
+                         int32_t* out_query_idx, int32_t* out_train_idx, float* out_dist, int32_t* out_count,
+                         int64_t cap, void* workspace, size_t workspace_bytes, void* stream) {
+  int rc = check_common(bank, sqnorm, k_per_image, n_img, k_stride, pairs, n_pairs);
+  if (rc) return rc;
+  if (n_pairs == 0) return B200M_OK;
+  if (!out_query_idx || !out_train_idx || !out_dist || !out_count || !workspace || cap <= 0)
+    return fail(B200M_E_BAD_ARG, "null output / workspace or cap <= 0%s");
+  if (workspace_bytes < b200m_workspace_bytes(k_stride, n_pairs)) return fail(B200M_E_WORKSPACE, "workspace too small%s");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  CUtensorMap tmap;
+  rc = make_row_tmap(&tmap, bank, static_cast<uint64_t>(n_img) * k_stride);
+  if (rc) return rc;
+  const int64_t B = batch_pairs(k_stride, n_pairs);
+  uintptr_t wsp = (reinterpret_cast<uintptr_t>(workspace) + 255) & ~uintptr_t(255);
+  int4* rowres = reinterpret_cast<int4*>(wsp);
+  unsigned long long* colbest = reinterpret_cast<unsigned long long*>(rowres + B * k_stride);
+  for (int64_t p0 = 0; p0 < n_pairs; p0 += B) {
+    const int64_t nb = (n_pairs - p0 < B) ? (n_pairs - p0) : B;
+    rc = sweep_batch(tmap, sqnorm, k_per_image, k_stride, pairs + 2 * p0, nb, rowres, colbest, st);
+    if (rc) return rc;
+    b200m::match_finalize_kernel<1024><<<static_cast<unsigned>(nb), 1024, 0, st>>>(
+        rowres, colbest, pairs + 2 * p0, k_per_image, k_stride, ratio, mutual, out_query_idx + p0 * cap,
+        out_train_idx + p0 * cap, out_dist + p0 * cap, out_count + p0, cap);
+    CUDA_TRY(cudaGetLastError());
+  }
+  return B200M_OK;
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------ diagnostics
+namespace b200m {
+
+struct DebugSmem {
+  uint8_t a[kABytes];
+  uint8_t b[kBBytes];
+  uint64_t full, done;
+  uint32_t tmem_base;
+};
+
+__global__ void __launch_bounds__(128, 1)
+debug_dot_tile_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                      int32_t* __restrict__ out) {
+  extern __shared__ uint8_t smem_raw[];
+  DebugSmem& sm = *reinterpret_cast<DebugSmem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const uint32_t warp = threadIdx.x >> 5, lane = lane_id();
+  if (threadIdx.x == 0) {
+    mbar_init(&sm.full, 1);
+    mbar_init(&sm.done, 1);
+    fence_mbar_init();
+  }
+  if (warp == 1) tmem_alloc<256>(&sm.tmem_base);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = sm.tmem_base;
+  if (threadIdx.x == 0) {
+    mbar_arrive_expect_tx(&sm.full, kABytes + kBBytes);
+    tma_load_2d(sm.a, &tmap_a, 0, 0, &sm.full);
+    tma_load_2d(sm.b, &tmap_b, 0, 0, &sm.full);
+    tma_load_2d(sm.b + kBBytes / 2, &tmap_b, 0, 128, &sm.full);
+    mbar_wait(&sm.full, 0);
+    tc_fence_after();
+    const uint64_t adesc = make_desc_k128(smem_u32(sm.a));
+    const uint64_t bdesc = make_desc_k128(smem_u32(sm.b));
+    constexpr uint32_t idesc = make_idesc_u8(kTQ, kTT);
+#pragma unroll
+    for (int k = 0; k < kD / 32; ++k) mma_i8_ss(tmem_base, adesc + 2 * k, bdesc + 2 * k, idesc, k > 0 ? 1u : 0u);
+    tc_commit(&sm.done);
+  }
+  __syncwarp();
+  mbar_wait(&sm.done, 0);
+  tc_fence_after();
+  const int row = warp * 32 + lane;
+  for (int c = 0; c < 8; ++c) {
+    int v[32];
+    tmem_ld_32x32(tmem_base + ((warp * 32u) << 16) + c * 32, v);
+    tmem_ld_wait();
+#pragma unroll
+    for (int j = 0; j < 32; ++j) out[row * kTT + c * 32 + j] = v[j];
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc<256>(tmem_base);
+  }
+}
+
+}  // namespace b200m
+
+extern "C" int b200m_debug_dot_tile_u8(const uint8_t* a_rows, const uint8_t* b_rows, int32_t* out, void* stream) {
+  if (!a_rows || !b_rows || !out) return fail(B200M_E_BAD_ARG, "null argument%s");
+  if (device_info().ok != 1) return fail(B200M_E_NO_DEVICE, "no sm_100 CUDA device available (no CPU fallback)%s");
+  CUtensorMap ta, tb;
+  int rc = make_row_tmap(&ta, a_rows, 128);
+  if (rc) return rc;
+  rc = make_row_tmap(&tb, b_rows, 256);
+  if (rc) return rc;
+  const size_t smem = sizeof(b200m::DebugSmem) + 1024;
+  CUDA_TRY(cudaFuncSetAttribute(b200m::debug_dot_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                static_cast<int>(smem)));
+  b200m::debug_dot_tile_kernel<<<1, 128, smem, static_cast<cudaStream_t>(stream)>>>(ta, tb, out);
+  CUDA_TRY(cudaGetLastError());
+  return B200M_OK;
+}

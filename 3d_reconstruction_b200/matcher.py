@@ -1,0 +1,185 @@
+"""Host-side mirror of the reference's matching call shape over the C-ABI (include/b200m.h).
+
+Three faces over one kernel:
+  * match_pairs / knn2_pairs   -- batched: a DescriptorBank + an int32 [P,2] pair list (the scheduler's output)
+  * knn_match / match          -- cv2-shaped single pair: descriptor arrays in, index/distance arrays out
+                                  (cv2.BFMatcher(NORM_L2).knnMatch(k=2) + ratio + crossCheck)
+  * B200Matcher.__call__       -- LightGlue-shaped: matcher({'image0': feats0, 'image1': feats1}) -> dict,
+                                  so matching.py:122-128 runs unchanged on its output.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+
+import numpy as np
+import torch
+
+from . import _lib
+from .bank import DescriptorBank
+
+
+@dataclass
+class MatchConfig:
+    ratio: float = 0.75      # Lowe ratio on float32 distances (<= 0 disables)
+    mutual: bool = True      # cross-check
+    metric: str = "l2_u8"    # the exact integer path; the bf16 inner-product path is a later row
+    k: int = 2
+
+
+@dataclass
+class PairMatches:
+    """Device-side result of match_pairs: fixed-capacity slots per pair + counts."""
+    query_idx: torch.Tensor   # int32 [P, cap]
+    train_idx: torch.Tensor   # int32 [P, cap]
+    dist: torch.Tensor        # float32 [P, cap]
+    count: torch.Tensor       # int32 [P]
+    cap: int
+
+    def check_overflow(self) -> None:
+        mx = int(self.count.max().item()) if self.count.numel() else 0
+        if mx > self.cap:
+            raise OverflowError(f"a pair produced {mx} matches but cap is {self.cap}; matches are never truncated silently")
+
+    def to_lists(self):
+        """-> list of (idx0 int64 [S], idx1 int64 [S], dist float32 [S]) numpy triples, one per pair."""
+        self.check_overflow()
+        cnt = self.count.cpu().numpy()
+        q = self.query_idx.cpu().numpy()
+        t = self.train_idx.cpu().numpy()
+        d = self.dist.cpu().numpy()
+        return [(q[p, :c].astype(np.int64), t[p, :c].astype(np.int64), d[p, :c].copy()) for p, c in enumerate(cnt)]
+
+
+def _pairs_tensor(pairs, device) -> torch.Tensor:
+    if isinstance(pairs, torch.Tensor):
+        t = pairs.to(device=device, dtype=torch.int32)
+    else:
+        t = torch.as_tensor(np.asarray(pairs, dtype=np.int32).reshape(-1, 2)).to(device)
+    if t.dim() != 2 or t.shape[1] != 2:
+        raise ValueError("pairs must be [P,2]")
+    return t.contiguous()
+
+
+def _workspace(bank: DescriptorBank, n_pairs: int) -> torch.Tensor:
+    nbytes = _lib.lib().b200m_workspace_bytes(bank.k_stride, n_pairs)
+    return torch.empty(int(nbytes), dtype=torch.uint8, device=bank.device)
+
+
+def match_pairs(bank: DescriptorBank, pairs, ratio: float = 0.75, mutual: bool = True, cap: int | None = None,
+                out: PairMatches | None = None, workspace: torch.Tensor | None = None) -> PairMatches:
+    """Full rule for every (query_img, train_img) pair; asynchronous on the current stream."""
+    pairs_t = _pairs_tensor(pairs, bank.device)
+    P = int(pairs_t.shape[0])
+    if cap is None:
+        cap = bank.k_stride
+    if out is None:
+        dev = bank.device
+        out = PairMatches(torch.empty((P, cap), dtype=torch.int32, device=dev),
+                          torch.empty((P, cap), dtype=torch.int32, device=dev),
+                          torch.empty((P, cap), dtype=torch.float32, device=dev),
+                          torch.zeros((P,), dtype=torch.int32, device=dev), int(cap))
+    if P == 0:
+        return out
+    ws = workspace if workspace is not None else _workspace(bank, P)
+    with torch.cuda.device(bank.device):
+        st = torch.cuda.current_stream().cuda_stream
+        _lib.check(_lib.lib().b200m_match_pairs_u8(
+            bank.desc.data_ptr(), bank.sqnorm.data_ptr(), bank.k_per_image.data_ptr(), bank.n_img, bank.k_stride,
+            pairs_t.data_ptr(), P, float(ratio if ratio is not None else 0.0), int(bool(mutual)),
+            out.query_idx.data_ptr(), out.train_idx.data_ptr(), out.dist.data_ptr(), out.count.data_ptr(),
+            int(out.cap), ws.data_ptr(), ws.numel(), st))
+    return out
+
+
+def knn2_pairs(bank: DescriptorBank, pairs, workspace: torch.Tensor | None = None):
+    """knnMatch(k=2) for every pair -> (train_idx int32 [P,k_stride,2], dist float32 [P,k_stride,2])."""
+    pairs_t = _pairs_tensor(pairs, bank.device)
+    P = int(pairs_t.shape[0])
+    idx = torch.full((P, bank.k_stride, 2), -1, dtype=torch.int32, device=bank.device)
+    dist = torch.full((P, bank.k_stride, 2), float("inf"), dtype=torch.float32, device=bank.device)
+    if P == 0:
+        return idx, dist
+    ws = workspace if workspace is not None else _workspace(bank, P)
+    with torch.cuda.device(bank.device):
+        st = torch.cuda.current_stream().cuda_stream
+        _lib.check(_lib.lib().b200m_knn2_u8(
+            bank.desc.data_ptr(), bank.sqnorm.data_ptr(), bank.k_per_image.data_ptr(), bank.n_img, bank.k_stride,
+            pairs_t.data_ptr(), P, idx.data_ptr(), dist.data_ptr(), ws.data_ptr(), ws.numel(), st))
+    return idx, dist
+
+
+# ---------------------------------------------------------------------- cv2-shaped single pair
+def knn_match(desc_q, desc_t, k: int = 2, device="cuda"):
+    """cv2.BFMatcher(NORM_L2).knnMatch(desc_q, desc_t, k=2) as arrays:
+    (train_idx int32 [Kq,2], dist float32 [Kq,2]); -1 / inf where cv2 would return a shorter row."""
+    if k != 2:
+        raise ValueError("only k=2 is implemented (the hot path's knnMatch call)")
+    bank = DescriptorBank.from_arrays([desc_q, desc_t], device=device)
+    idx, dist = knn2_pairs(bank, [[0, 1]])
+    kq = int(bank.k_host()[0])
+    return idx[0, :kq].cpu().numpy(), dist[0, :kq].cpu().numpy()
+
+
+def match(desc_q, desc_t, ratio: float = 0.75, mutual: bool = True, device="cuda"):
+    """(query_idx int32 [S], train_idx int32 [S], dist float32 [S]), ascending query index."""
+    bank = DescriptorBank.from_arrays([desc_q, desc_t], device=device)
+    res = match_pairs(bank, [[0, 1]], ratio=ratio, mutual=mutual)
+    q, t, d = res.to_lists()[0]
+    return q.astype(np.int32), t.astype(np.int32), d
+
+
+# ---------------------------------------------------------------------- LightGlue-shaped
+class B200Matcher:
+    """Drop-in for the callable built at matching.py:20 and called at matching.py:122.
+
+    Input contract (lightglue/lightglue.py:326-334): data['image0'|'image1'] dicts holding
+    'descriptors' [1,M,128] (+ 'keypoints', 'image_size', accepted and ignored by the kNN rule).
+    Output contract (lightglue/lightglue.py:442-450): 'matches0' [1,M], 'matches1' [1,N] (-1 = unmatched),
+    'matching_scores0/1', 'matches': [LongTensor[S,2]] ascending in query index, 'scores': [FloatTensor[S]].
+    'scores' carries the float32 L2 distance of each match (lower is better; matching.py ignores it).
+    """
+
+    def __init__(self, config: MatchConfig | None = None, device="cuda"):
+        self.conf = config or MatchConfig()
+        self.device = torch.device(device)
+        if self.conf.metric != "l2_u8":
+            raise NotImplementedError("only the exact u8 L2 path is built so far")
+
+    def eval(self):
+        return self
+
+    def to(self, device):
+        self.device = torch.device(device)
+        return self
+
+    def __call__(self, data: dict) -> dict:
+        for key in ("image0", "image1"):
+            assert key in data, f"Missing key {key} in data"          # lightglue.py:347-348
+        d0 = data["image0"]["descriptors"]
+        d1 = data["image1"]["descriptors"]
+        assert d0.dim() == 3 and d1.dim() == 3 and d0.shape[0] == 1 and d1.shape[0] == 1, "batch size must be 1"
+        assert d0.shape[-1] == 128 and d1.shape[-1] == 128            # lightglue.py:365-366
+        m, n = d0.shape[1], d1.shape[1]
+        bank = DescriptorBank.from_arrays([d0[0], d1[0]], device=self.device)
+        res = match_pairs(bank, [[0, 1]], ratio=self.conf.ratio, mutual=self.conf.mutual)
+        res.check_overflow()
+        s = int(res.count[0].item())
+        q = res.query_idx[0, :s].long()
+        t = res.train_idx[0, :s].long()
+        dist = res.dist[0, :s]
+        dev = self.device
+        m0 = torch.full((1, m), -1, dtype=torch.long, device=dev)
+        m1 = torch.full((1, n), -1, dtype=torch.long, device=dev)
+        sc0 = torch.zeros((1, m), device=dev)
+        sc1 = torch.zeros((1, n), device=dev)
+        m0[0, q] = t
+        sc0[0, q] = dist
+        if self.conf.mutual:          # one-to-one only under the cross-check
+            m1[0, t] = q
+            sc1[0, t] = dist
+        return {
+            "matches0": m0, "matches1": m1, "matching_scores0": sc0, "matching_scores1": sc1,
+            "stop": 0, "matches": [torch.stack([q, t], -1)], "scores": [dist],
+        }
+
+    forward = __call__

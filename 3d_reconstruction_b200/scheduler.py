@@ -1,0 +1,59 @@
+"""Pair schedules and their static partition over ranks.
+
+The reference decides which pairs to match with a BoW view graph + BFS (matching.py:24-99); the
+BASELINE.json configs use exhaustive and sliding-window schedules instead. Pairs are (query_img,
+train_img) rows of an int32 [P,2] array, the format consumed by match_pairs and written to
+output/img_pairs.npy (matching.py:188).
+"""
+from __future__ import annotations
+
+import numpy as np
+
+
+def exhaustive_pairs(n_img: int) -> np.ndarray:
+    """All i<j pairs in row-major order: n(n-1)/2 rows."""
+    i, j = np.triu_indices(n_img, k=1)
+    return np.stack([i, j], 1).astype(np.int32)
+
+
+def window_pairs(n_img: int, window: int) -> np.ndarray:
+    """Each image against the next `window` images, clipped at the end."""
+    out = [(i, j) for i in range(n_img) for j in range(i + 1, min(n_img, i + 1 + window))]
+    return np.asarray(out, dtype=np.int32).reshape(-1, 2)
+
+
+def blocked_order(pairs: np.ndarray, block: int = 16) -> np.ndarray:
+    """Reorder pairs so that consecutive pairs share images inside block x block patches of the (i,j)
+    grid (a 16 x 16 patch of 16k-keypoint images is 2 x 32 MiB of descriptors: L2-resident)."""
+    pairs = np.asarray(pairs, dtype=np.int32).reshape(-1, 2)
+    if len(pairs) == 0:
+        return pairs
+    key = np.lexsort((pairs[:, 1], pairs[:, 0], pairs[:, 1] // block, pairs[:, 0] // block))
+    return pairs[key]
+
+
+def pair_cost(pairs: np.ndarray, k_per_image: np.ndarray) -> np.ndarray:
+    k = np.asarray(k_per_image, dtype=np.int64)
+    return k[pairs[:, 0]] * k[pairs[:, 1]]
+
+
+def partition(pairs: np.ndarray, world_size: int, rank: int, k_per_image=None):
+    """Static, deterministic partition: contiguous chunks of the (blocked) pair list with near-equal
+    total cost K_q*K_t. Returns (pairs_of_rank, indices_into_pairs). Every rank computes the same
+    split, so no communication is needed and the gathered result order is well defined."""
+    pairs = np.asarray(pairs, dtype=np.int32).reshape(-1, 2)
+    n = len(pairs)
+    if world_size <= 1:
+        return pairs, np.arange(n)
+    if k_per_image is None:
+        cost = np.ones(n, dtype=np.float64)
+    else:
+        cost = np.maximum(pair_cost(pairs, k_per_image).astype(np.float64), 1.0)
+    csum = np.concatenate([[0.0], np.cumsum(cost)])
+    total = csum[-1]
+    bounds = np.searchsorted(csum, total * np.arange(world_size + 1) / world_size, side="left")
+    bounds[0], bounds[-1] = 0, n
+    bounds = np.maximum.accumulate(bounds)
+    lo, hi = int(bounds[rank]), int(bounds[rank + 1])
+    idx = np.arange(lo, hi)
+    return pairs[lo:hi], idx

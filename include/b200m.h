@@ -1,0 +1,116 @@
+/*
+ * b200m.h -- C-ABI of the B200-native pairwise descriptor matcher.
+ *
+ * This is the drop-in boundary for ONE hot path of daovietanh190499/3D_Reconstruction:
+ * "two descriptor sets in -> (query index, train index, distance) match lists out".
+ * The reference has no FFI of its own; the interface each entry point stands in for is cited
+ * as reference file:line (paths relative to the reference repository root):
+ *
+ *   matching.py:122            matches01 = matcher({'image0': feats0, 'image1': feats1})
+ *   matching.py:123-128        idx0 / idx1 extraction from matches01['matches']
+ *   lightglue/lightglue.py:218-227   MatchAssignment.forward  (dense M x N similarity)
+ *   lightglue/lightglue.py:235-254   filter_matches           (row/col arg-best + mutual check)
+ *   lightglue/lightglue.py:417-426   match list packing, ascending query index
+ *   (named by BASELINE.json, third-party)  cv2.BFMatcher(NORM_L2).knnMatch(k=2) + Lowe ratio + cross-check
+ *
+ * Conventions
+ *   - every pointer except `pairs_host`-style arguments is a DEVICE pointer unless its name ends in _host;
+ *   - the library never allocates or frees caller-visible memory: outputs and the scratch
+ *     workspace are caller-allocated (size it with b200m_workspace_bytes);
+ *   - all compute entry points are asynchronous on `stream` (a cudaStream_t passed as void*);
+ *   - return value: 0 = OK, negative = error (B200M_E_*), text via b200m_last_error_string();
+ *   - there is no CPU fallback and no other-architecture fallback: on a machine without an
+ *     sm_100 GPU every compute entry point returns B200M_E_NO_DEVICE.
+ *
+ * Descriptor bank layout (HBM): uint8 [n_img, k_stride, 128], row-major, k_stride a multiple
+ * of 256; image i owns rows [0, k_per_image[i]) of its slab, the remaining rows are padding.
+ * b200m_bank_prepare_u8 zeroes the padding and writes the int32 squared norms
+ * [n_img, k_stride] (padding rows get the sentinel B200M_PAD_NORM).
+ */
+#ifndef B200M_H_
+#define B200M_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200M_VERSION 100          /* 0.1.0 */
+#define B200M_DESC_DIM 128         /* SIFT / DISK descriptor length handled by the u8 path */
+#define B200M_TILE_Q 128           /* query rows per tile (UMMA M) */
+#define B200M_TILE_T 256           /* train rows per tile (UMMA N) */
+#define B200M_PAD_NORM (1 << 23)   /* > 128*255^2 = 8,323,200: marks a padding row */
+
+enum {
+  B200M_OK = 0,
+  B200M_E_BAD_ARG = -1,      /* null pointer, k_stride not a multiple of 256, negative sizes ... */
+  B200M_E_BAD_DIM = -2,      /* descriptor length not supported */
+  B200M_E_WORKSPACE = -3,    /* workspace too small */
+  B200M_E_NO_DEVICE = -4,    /* no sm_100 device / driver entry point missing */
+  B200M_E_CUDA = -5          /* a CUDA call failed; see b200m_last_error_string() */
+};
+
+int b200m_version(void);
+const char* b200m_last_error_string(void);
+
+/* 0 when the current CUDA device can run the sm_100a kernels, B200M_E_NO_DEVICE otherwise. */
+int b200m_device_check(void);
+
+/* Number of SMs the sweep kernel will be launched on (persistent grid); <0 on error. */
+int b200m_sm_count(void);
+
+/* Zero the padding rows of `bank` and compute squared L2 norms (exact, int32).
+ * Replaces the per-pair repacking at matching.py:107-120 with a one-off pass. */
+int b200m_bank_prepare_u8(uint8_t* bank, int32_t n_img, int64_t k_stride,
+                          const int32_t* k_per_image, int32_t* sqnorm, void* stream);
+
+/* Scratch bytes needed to process `n_pairs` pairs of images with slab stride `k_stride`.
+ * Pairs are processed in internal batches, so this saturates at a fixed batch size. */
+size_t b200m_workspace_bytes(int64_t k_stride, int64_t n_pairs);
+
+/* cv2.BFMatcher(NORM_L2).knnMatch(query, train, k=2) for every (query_img, train_img) pair.
+ *   pairs          int32 [n_pairs, 2]  (query image, train image), device
+ *   out_train_idx  int32 [n_pairs, k_stride, 2]  best / second-best train row, -1 = none
+ *   out_dist       float [n_pairs, k_stride, 2]  float32 sqrt of the exact int32 squared distance
+ * Rows >= k_per_image[query_img] are left untouched. Ties -> lowest train index (cv2 rule). */
+int b200m_knn2_u8(const uint8_t* bank, const int32_t* sqnorm, const int32_t* k_per_image,
+                  int32_t n_img, int64_t k_stride,
+                  const int32_t* pairs, int64_t n_pairs,
+                  int32_t* out_train_idx, float* out_dist,
+                  void* workspace, size_t workspace_bytes, void* stream);
+
+/* The full matching rule of the hot path for every pair:
+ *   2-NN in L2  ->  keep q if dist1 < ratio * dist2 (float32 distances, double compare,
+ *   exactly `m.distance < ratio * n.distance` on cv2 DMatch)  ->  if mutual != 0 keep (q,t) only
+ *   when q is the nearest query of t (lowest-index ties, cv2 crossCheck rule).
+ * ratio <= 0 disables the ratio test.  A query with a single train candidate has no second
+ * neighbour and is dropped by the ratio test (cv2: the `for m, n in knn` unpack needs two).
+ *   out_query_idx / out_train_idx / out_dist   [n_pairs, cap], ascending query index
+ *   out_count  int32 [n_pairs]: matches FOUND; if > cap only the first cap were stored and the
+ *              caller must treat the pair as overflowed (never silently truncated). */
+int b200m_match_pairs_u8(const uint8_t* bank, const int32_t* sqnorm, const int32_t* k_per_image,
+                         int32_t n_img, int64_t k_stride,
+                         const int32_t* pairs, int64_t n_pairs,
+                         double ratio, int mutual,
+                         int32_t* out_query_idx, int32_t* out_train_idx, float* out_dist,
+                         int32_t* out_count, int64_t cap,
+                         void* workspace, size_t workspace_bytes, void* stream);
+
+/* Tuning / introspection knobs (process-global, read at launch time).
+ *   "epilogue"  0 = exact reference epilogue, 1 = threshold-reject epilogue (default)
+ *   "grid"      number of persistent CTAs, 0 = one per SM (default)
+ *   "batch"     pairs per internal batch, 0 = default */
+int b200m_set_option(const char* name, int64_t value);
+int64_t b200m_get_option(const char* name);
+
+/* Diagnostics: raw 128 x 256 int32 dot-product tile through the same TMA + tcgen05 path
+ * (used by the self-test to validate descriptors/swizzle independently of the epilogue). */
+int b200m_debug_dot_tile_u8(const uint8_t* a_rows /*[128,128]*/, const uint8_t* b_rows /*[256,128]*/,
+                            int32_t* out /*[128,256]*/, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200M_H_ */

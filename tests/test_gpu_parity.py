@@ -1,0 +1,184 @@
+"""GPU parity tests: the CUDA path, called through the C-ABI, against the oracle and the committed
+cv2 fixtures. Bit-exact for indices; distances compared as float32 bit patterns."""
+import importlib
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import oracle_int
+
+pytestmark = pytest.mark.gpu
+
+
+def _bits(x):
+    return np.ascontiguousarray(x, dtype=np.float32).view(np.uint32)
+
+
+@pytest.fixture(scope="module", params=[1, 0], ids=["epi_reject", "epi_exact"])
+def epi(pkg, request):
+    pkg.set_option("epilogue", request.param)
+    yield request.param
+    pkg.set_option("epilogue", 1)
+
+
+def test_debug_dot_tile(pkg):
+    """TMA + swizzle + smem descriptors + tcgen05.mma.kind::i8 + tcgen05.ld, without any epilogue."""
+    rng = np.random.default_rng(1)
+    a = rng.integers(0, 256, size=(128, 128)).astype(np.uint8)
+    b = rng.integers(0, 256, size=(256, 128)).astype(np.uint8)
+    a[0] = 255
+    b[0] = 255
+    ad, bd = torch.from_numpy(a).cuda(), torch.from_numpy(b).cuda()
+    out = torch.empty((128, 256), dtype=torch.int32, device="cuda")
+    lib = pkg._lib
+    lib.check(lib.lib().b200m_debug_dot_tile_u8(ad.data_ptr(), bd.data_ptr(), out.data_ptr(),
+                                               torch.cuda.current_stream().cuda_stream))
+    torch.cuda.synchronize()
+    ref = a.astype(np.int64) @ b.astype(np.int64).T
+    got = out.cpu().numpy().astype(np.int64)
+    assert np.array_equal(got, ref), f"mismatching elements: {(got != ref).sum()} of {ref.size}"
+
+
+def _check_pair(pkg, q, t):
+    idx, dist = pkg.knn_match(q, t)
+    eidx, edist, _ = oracle_int.knn2(q, t)
+    assert np.array_equal(idx, eidx), f"knn idx mismatch rows: {np.nonzero((idx != eidx).any(1))[0][:10]}"
+    assert np.array_equal(_bits(dist), _bits(edist))
+    for ratio, mutual in [(0.75, True), (0.75, False), (0.0, True)]:
+        got = pkg.match(q, t, ratio=ratio, mutual=mutual)
+        exp = oracle_int.match(q, t, ratio, mutual)
+        assert np.array_equal(got[0], exp[0]) and np.array_equal(got[1], exp[1]), (ratio, mutual)
+        assert np.array_equal(_bits(got[2]), _bits(exp[2])), (ratio, mutual)
+
+
+@pytest.mark.parametrize("name", ["sift_pair.npz", "ties.npz"])
+def test_golden_fixture(pkg, epi, golden_dir, name):
+    """BASELINE.json config 1 (real SIFT of DSC_0001/DSC_0002) and the tie fixture vs stored cv2 output."""
+    g = np.load(os.path.join(golden_dir, name))
+    idx, dist = pkg.knn_match(g["q"], g["t"])
+    assert np.array_equal(idx, g["knn_idx"])
+    assert np.array_equal(_bits(dist), _bits(g["knn_dist"]))
+    ratio = 0.75 if name == "sift_pair.npz" else 0.0
+    q, t, d = pkg.match(g["q"], g["t"], ratio=ratio, mutual=True)
+    assert np.array_equal(q, g["m_q"]) and np.array_equal(t, g["m_t"])
+    assert np.array_equal(_bits(d), _bits(g["m_d"]))
+    assert len(q) > 0
+
+
+@pytest.mark.parametrize("kq,kt", [(1, 1), (1, 2), (2, 1), (5, 300), (128, 256), (129, 257), (300, 5),
+                                    (1000, 777), (640, 2048)])
+def test_ragged_shapes_random(pkg, epi, kq, kt):
+    rng = np.random.default_rng(kq * 7919 + kt)
+    q = rng.integers(0, 256, size=(kq, 128)).astype(np.uint8)
+    t = rng.integers(0, 256, size=(kt, 128)).astype(np.uint8)
+    _check_pair(pkg, q, t)
+
+
+def test_adversarial_ties_and_extremes(pkg, epi):
+    rng = np.random.default_rng(11)
+    base = rng.integers(0, 2, size=(16, 128)).astype(np.uint8) * 255
+    q = base[rng.integers(0, 16, size=700)]
+    t = base[rng.integers(0, 16, size=900)]
+    q[10] = 0
+    t[20:40] = 0          # all-zero rows are valid competitors (not padding)
+    q[11] = 255
+    t[41] = 255           # max magnitude: d^2 up to 128*255^2
+    _check_pair(pkg, q, t)
+    # identical sets: every row has distance 0 to itself, duplicates tie
+    _check_pair(pkg, t, t)
+
+
+def test_empty_inputs(pkg):
+    q = np.zeros((0, 128), np.uint8)
+    t = np.random.default_rng(0).integers(0, 256, size=(10, 128)).astype(np.uint8)
+    assert pkg.match(q, t)[0].size == 0
+    assert pkg.match(t, q)[0].size == 0
+    idx, dist = pkg.knn_match(t, q)
+    assert (idx == -1).all() and np.isinf(dist).all()
+
+
+def test_synthetic_bank_batched(pkg, epi):
+    """Several images, ragged K, exhaustive pairs in one call: planted matches must survive."""
+    syn = importlib.import_module("3d_reconstruction_b200.synthetic")
+    ks = [1500, 1024, 999, 1300, 257]
+    desc, kpi = syn.make_bank_tensor(len(ks), 1500, seed=3, device="cpu", k_per_image=ks)
+    bank = pkg.DescriptorBank.from_packed(desc.cuda(), kpi)
+    pairs = pkg.exhaustive_pairs(len(ks))
+    pairs = np.concatenate([pairs, pairs[:, ::-1]], 0)      # both directions
+    res = pkg.match_pairs(bank, pairs).to_lists()
+    total = 0
+    for (a, b), (q, t, d) in zip(pairs, res):
+        eq, et, ed = oracle_int.match(desc[a, :ks[a]].numpy(), desc[b, :ks[b]].numpy(), 0.75, True)
+        assert np.array_equal(q, eq) and np.array_equal(t, et), (a, b)
+        assert np.array_equal(_bits(d), _bits(ed)), (a, b)
+        total += len(q)
+    assert total > 100
+    # small internal batches must give identical results
+    pkg.set_option("batch", 3)
+    try:
+        res2 = pkg.match_pairs(bank, pairs).to_lists()
+    finally:
+        pkg.set_option("batch", 0)
+    for x, y in zip(res, res2):
+        assert all(np.array_equal(u, v) for u, v in zip(x, y))
+
+
+def test_cap_overflow_is_reported(pkg):
+    rng = np.random.default_rng(2)
+    t = rng.integers(0, 256, size=(300, 128)).astype(np.uint8)
+    bank = pkg.DescriptorBank.from_arrays([t, t])
+    res = pkg.match_pairs(bank, [[0, 1]], ratio=0.0, mutual=True, cap=16)
+    assert int(res.count[0]) == 300
+    with pytest.raises(OverflowError):
+        res.to_lists()
+
+
+def test_full_size_properties(pkg):
+    """BASELINE config sizes (K=8192 and 16384): size-independent properties instead of a CPU oracle:
+    self-match is the identity with distance 0; knn best of (i,i) is the row itself; results are
+    deterministic across runs; mutual matches are one-to-one."""
+    syn = importlib.import_module("3d_reconstruction_b200.synthetic")
+    for k in (8192, 16384):
+        desc, kpi = syn.make_bank_tensor(3, k, seed=9, device="cuda", dup_frac=0.0)
+        bank = pkg.DescriptorBank.from_packed(desc, kpi)
+        r = pkg.match_pairs(bank, [[0, 0], [0, 1], [1, 0]], ratio=0.0, mutual=True)
+        lists = r.to_lists()
+        q, t, d = lists[0]
+        # distinct rows (dup_frac=0) => self-match is exactly the identity with zero distance
+        uniq = np.unique(desc[0].cpu().numpy(), axis=0).shape[0]
+        if uniq == k:
+            assert np.array_equal(q, np.arange(k)) and np.array_equal(t, q) and (d == 0).all()
+        # (0,1) and (1,0) under pure mutual-NN (no ratio) are transposes of each other unless ties interfere
+        q01, t01, d01 = lists[1]
+        q10, t10, d10 = lists[2]
+        a = set(zip(q01.tolist(), t01.tolist()))
+        b = set(zip(t10.tolist(), q10.tolist()))
+        assert len(a ^ b) <= max(2, len(a) // 1000)
+        assert len(set(t01.tolist())) == len(t01)            # one-to-one
+        r2 = pkg.match_pairs(bank, [[0, 0], [0, 1], [1, 0]], ratio=0.0, mutual=True).to_lists()
+        for x, y in zip(lists, r2):
+            assert all(np.array_equal(u, v) for u, v in zip(x, y))
+        # sampled rows against the oracle at full size
+        qd, td = desc[0].cpu().numpy(), desc[1].cpu().numpy()
+        idx, dist = pkg.knn2_pairs(bank, [[0, 1]])
+        rows = np.random.default_rng(k).choice(k, size=256, replace=False)
+        eidx, edist, _ = oracle_int.knn2(qd[rows], td)
+        assert np.array_equal(idx[0].cpu().numpy()[rows], eidx)
+        assert np.array_equal(_bits(dist[0].cpu().numpy()[rows]), _bits(edist))
+
+
+def test_lightglue_shaped_adapter(pkg, golden_dir):
+    g = np.load(os.path.join(golden_dir, "sift_pair.npz"))
+    m = pkg.B200Matcher().eval().to("cuda")
+    feats0 = {"descriptors": torch.from_numpy(g["q"].astype(np.float32))[None], "keypoints": torch.zeros(1, len(g["q"]), 2),
+              "image_size": torch.tensor([[1936., 1296.]])}
+    feats1 = {"descriptors": torch.from_numpy(g["t"].astype(np.float32))[None], "keypoints": torch.zeros(1, len(g["t"]), 2),
+              "image_size": torch.tensor([[1936., 1296.]])}
+    out = m({"image0": feats0, "image1": feats1})
+    matches = out["matches"][0]                       # what matching.py:124-128 reads
+    idx0, idx1 = matches[..., 0].cpu().numpy(), matches[..., 1].cpu().numpy()
+    assert np.array_equal(idx0, g["m_q"]) and np.array_equal(idx1, g["m_t"])
+    m0 = out["matches0"][0].cpu().numpy()
+    assert (m0[idx0] == idx1).all() and (m0 >= 0).sum() == len(idx0)

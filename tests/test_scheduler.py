@@ -1,0 +1,46 @@
+import importlib
+
+import numpy as np
+
+
+def test_exhaustive_and_window_counts(pkg):
+    assert len(pkg.exhaustive_pairs(64)) == 2016
+    assert len(pkg.exhaustive_pairs(257)) == 32896
+    w = pkg.window_pairs(2000, 32)
+    assert len(w) == 2000 * 32 - 32 * 33 // 2 == 63472
+    assert (w[:, 1] > w[:, 0]).all() and (w[:, 1] - w[:, 0] <= 32).all()
+
+
+def test_blocked_order_is_a_permutation(pkg):
+    p = pkg.exhaustive_pairs(40)
+    b = pkg.blocked_order(p, 16)
+    assert sorted(map(tuple, b.tolist())) == sorted(map(tuple, p.tolist()))
+
+
+def test_partition_covers_everything_once(pkg):
+    p = pkg.blocked_order(pkg.exhaustive_pairs(37))
+    k = np.random.default_rng(0).integers(100, 5000, size=37)
+    for ws in (1, 2, 3, 8):
+        seen = []
+        costs = []
+        for r in range(ws):
+            pr, idx = pkg.partition(p, ws, r, k)
+            assert np.array_equal(p[idx], pr)
+            seen.append(idx)
+            costs.append((k[pr[:, 0]].astype(np.int64) * k[pr[:, 1]]).sum())
+        allidx = np.concatenate(seen)
+        assert np.array_equal(np.sort(allidx), np.arange(len(p)))
+        assert np.array_equal(allidx, np.arange(len(p)))          # contiguous, in rank order
+        if ws > 1:
+            assert max(costs) <= 1.25 * (sum(costs) / ws)
+
+
+def test_synthetic_bank_has_planted_matches(pkg):
+    from oracle import oracle_int
+    syn = importlib.import_module("3d_reconstruction_b200.synthetic")
+    desc, kpi = syn.make_bank_tensor(3, 600, seed=1, device="cpu")
+    assert desc.shape == (3, 768, 128) and (desc[:, 600:] == 0).all()
+    q, t, d = oracle_int.match(desc[0, :600].numpy(), desc[1, :600].numpy())
+    assert len(q) > 20
+    desc2, _ = syn.make_bank_tensor(3, 600, seed=1, device="cpu")
+    assert (desc == desc2).all()
