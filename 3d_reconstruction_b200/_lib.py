@@ -17,6 +17,7 @@ SYMBOLS = (
     "b200m_last_error_string",
     "b200m_device_check",
     "b200m_sm_count",
+    "b200m_norm_table_elems",
     "b200m_bank_prepare_u8",
     "b200m_workspace_bytes",
     "b200m_knn2_u8",
@@ -52,6 +53,8 @@ def lib() -> C.CDLL:
     L.b200m_last_error_string.restype = C.c_char_p
     L.b200m_device_check.restype = C.c_int
     L.b200m_sm_count.restype = C.c_int
+    L.b200m_norm_table_elems.restype = i64
+    L.b200m_norm_table_elems.argtypes = [i32, i64]
     L.b200m_bank_prepare_u8.restype = C.c_int
     L.b200m_bank_prepare_u8.argtypes = [vp, i32, i64, vp, vp, vp]
     L.b200m_workspace_bytes.restype = sz

@@ -59,7 +59,8 @@ class DescriptorBank:
         k_per_image = k_per_image.to(device=desc.device, dtype=torch.int32).contiguous()
         if k_per_image.numel() != desc.shape[0]:
             raise ValueError("k_per_image must have one entry per image")
-        sqnorm = torch.empty(desc.shape[:2], dtype=torch.int32, device=desc.device)
+        n_tab = int(_lib.lib().b200m_norm_table_elems(desc.shape[0], desc.shape[1]))
+        sqnorm = torch.empty((n_tab,), dtype=torch.int32, device=desc.device)   # norms + per-32-row minima
         with torch.cuda.device(desc.device):
             st = torch.cuda.current_stream().cuda_stream
             _lib.check(_lib.lib().b200m_bank_prepare_u8(desc.data_ptr(), desc.shape[0], desc.shape[1],
@@ -108,3 +109,7 @@ class DescriptorBank:
 
     def nbytes(self) -> int:
         return self.desc.numel() + 4 * self.sqnorm.numel() + 4 * self.k_per_image.numel()
+
+    def norms(self) -> torch.Tensor:
+        """int32 [n_img, k_stride] view of the squared norms (B200M_PAD_NORM on padding rows)."""
+        return self.sqnorm[: self.n_img * self.k_stride].view(self.n_img, self.k_stride)

@@ -97,30 +97,67 @@ DeviceInfo& device_info() {
 
 constexpr size_t kSweepSmemBytes = sizeof(b200m::SweepSmem) + 1024;
 
-template <int kMode>
-int launch_sweep(const CUtensorMap& tmap, const b200m::SweepParams& sp, int grid, cudaStream_t st) {
+template <int kKind>
+int launch_sweep(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, const b200m::SweepParams& sp, int grid,
+                 cudaStream_t st) {
   static thread_local bool attr_set = false;
   if (!attr_set) {
-    CUDA_TRY(cudaFuncSetAttribute(b200m::sweep_kernel<kMode>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    CUDA_TRY(cudaFuncSetAttribute(b200m::sweep_kernel<kKind>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   static_cast<int>(kSweepSmemBytes)));
     attr_set = true;
   }
-  b200m::sweep_kernel<kMode><<<grid, b200m::kThreads, kSweepSmemBytes, st>>>(tmap, sp);
+  b200m::sweep_kernel<kKind><<<grid, b200m::kThreads, kSweepSmemBytes, st>>>(tmap_a, tmap_b, sp);
   CUDA_TRY(cudaGetLastError());
   return B200M_OK;
 }
 
+constexpr int64_t kDefaultBatchRows = int64_t(1) << 23;   // pairs * k_stride per internal batch
+
 int64_t batch_pairs(int64_t k_stride, int64_t n_pairs) {
-  int64_t b = g_opt.batch > 0 ? g_opt.batch : ((int64_t(1) << 24) / (k_stride > 0 ? k_stride : 1));
+  int64_t b = g_opt.batch > 0 ? g_opt.batch : (kDefaultBatchRows / (k_stride > 0 ? k_stride : 1));
   if (b < 1) b = 1;
   if (b > n_pairs) b = n_pairs;
   if (b < 1) b = 1;
   return b;
 }
 
+// Workspace carved per batch of B pairs (R = B * k_stride rows):
+struct Workspace {
+  int4* rowres;          // R
+  int32_t* surv_q;       // R
+  int32_t* surv_t;       // R
+  float* surv_d;         // R
+  int32_t* surv_thr;     // R
+  int32_t* surv_viol;    // R
+  int32_t* surv_count;   // B (padded to 64)
+  uint8_t* gathered;     // R * 128
+};
+
+size_t carve(Workspace* w, void* base, int64_t B, int64_t k_stride) {
+  const int64_t R = B * k_stride;
+  uintptr_t p0 = (reinterpret_cast<uintptr_t>(base) + 255) & ~uintptr_t(255);
+  uintptr_t p = p0;
+  auto take = [&](size_t bytes) { uintptr_t r = p; p += (bytes + 255) & ~size_t(255); return r; };
+  uintptr_t a = take(sizeof(int4) * R);
+  uintptr_t b = take(4 * R), c = take(4 * R), d = take(4 * R), e = take(4 * R), f = take(4 * R);
+  uintptr_t g = take(4 * (B + 64));
+  uintptr_t h = take(static_cast<size_t>(128) * R);
+  if (w) {
+    w->rowres = reinterpret_cast<int4*>(a);
+    w->surv_q = reinterpret_cast<int32_t*>(b);
+    w->surv_t = reinterpret_cast<int32_t*>(c);
+    w->surv_d = reinterpret_cast<float*>(d);
+    w->surv_thr = reinterpret_cast<int32_t*>(e);
+    w->surv_viol = reinterpret_cast<int32_t*>(f);
+    w->surv_count = reinterpret_cast<int32_t*>(g);
+    w->gathered = reinterpret_cast<uint8_t*>(h);
+  }
+  return (p - p0) + 256;
+}
+
 int check_common(const void* bank, const void* sqnorm, const void* kpi, int32_t n_img, int64_t k_stride,
                  const void* pairs, int64_t n_pairs) {
-  if (!bank || !sqnorm || !kpi || n_img <= 0) return fail(B200M_E_BAD_ARG, "null bank/sqnorm/k_per_image or n_img <= 0%s");
+  if (!bank || !sqnorm || !kpi || n_img <= 0) return fail(B200M_E_BAD_ARG, "null bank/norm_table/k_per_image or n_img <= 0%s");
   if (k_stride <= 0 || (k_stride % B200M_TILE_T) != 0)
     return fail(B200M_E_BAD_ARG, "k_stride must be a positive multiple of 256%s");
   if (n_pairs < 0 || (n_pairs > 0 && !pairs)) return fail(B200M_E_BAD_ARG, "bad pairs / n_pairs%s");
@@ -130,25 +167,38 @@ int check_common(const void* bank, const void* sqnorm, const void* kpi, int32_t 
   return B200M_OK;
 }
 
-// Runs the sweep for pairs [p0, p0 + nb) into the workspace and leaves rowres/colbest ready.
-int sweep_batch(const CUtensorMap& tmap, const int32_t* sqnorm, const int32_t* kpi, int64_t k_stride,
-                const int32_t* pairs_batch, int64_t nb, int4* rowres, unsigned long long* colbest,
-                cudaStream_t st) {
-  CUDA_TRY(cudaMemsetAsync(colbest, 0xFF, sizeof(unsigned long long) * nb * k_stride, st));
+int sweep_grid(int64_t items) {
+  int grid = g_opt.grid > 0 ? static_cast<int>(g_opt.grid) : device_info().sms;
+  if (grid > items) grid = static_cast<int>(items);
+  return grid < 1 ? 1 : grid;
+}
+
+b200m::SweepParams base_params(const int32_t* norm_table, int32_t n_img, const int32_t* kpi, int64_t k_stride,
+                               const int32_t* pairs_batch, int64_t nb, const Workspace& w) {
   b200m::SweepParams sp;
-  sp.sqnorm = sqnorm;
+  sp.sqnorm = norm_table;
+  sp.nbmin32 = norm_table + static_cast<int64_t>(n_img) * k_stride;
   sp.k_per_image = kpi;
   sp.pairs = pairs_batch;
   sp.k_stride = k_stride;
   sp.n_pairs = static_cast<int32_t>(nb);
-  sp.qtiles = static_cast<int32_t>(k_stride / B200M_TILE_Q);
-  sp.rowres = rowres;
-  sp.colbest = colbest;
-  int grid = g_opt.grid > 0 ? static_cast<int>(g_opt.grid) : device_info().sms;
-  const int64_t items = nb * sp.qtiles;
-  if (grid > items) grid = static_cast<int>(items);
-  if (grid < 1) grid = 1;
-  return g_opt.epilogue == 0 ? launch_sweep<0>(tmap, sp, grid, st) : launch_sweep<1>(tmap, sp, grid, st);
+  sp.blocks_per_pair = static_cast<int32_t>(k_stride / b200m::kRows);
+  sp.rowres = w.rowres;
+  sp.surv_count = w.surv_count;
+  sp.surv_q = w.surv_q;
+  sp.surv_thr = w.surv_thr;
+  sp.surv_viol = w.surv_viol;
+  return sp;
+}
+
+// First sweep: exact top-2 of every query row of every pair of the batch -> w.rowres
+int sweep_top2(const CUtensorMap& tmap_bank, const b200m::SweepParams& sp, cudaStream_t st) {
+  const int grid = sweep_grid(static_cast<int64_t>(sp.n_pairs) * sp.blocks_per_pair);
+  switch (g_opt.epilogue) {
+    case 0: return launch_sweep<b200m::kTop2Exact>(tmap_bank, tmap_bank, sp, grid, st);
+    case 2: return launch_sweep<b200m::kPeak>(tmap_bank, tmap_bank, sp, grid, st);
+    default: return launch_sweep<b200m::kTop2>(tmap_bank, tmap_bank, sp, grid, st);
+  }
 }
 
 }  // namespace
@@ -184,9 +234,15 @@ int64_t b200m_get_option(const char* name) {
   return -1;
 }
 
+int64_t b200m_norm_table_elems(int32_t n_img, int64_t k_stride) {
+  if (n_img <= 0 || k_stride <= 0) return 0;
+  const int64_t rows = static_cast<int64_t>(n_img) * k_stride;
+  return rows + rows / 32;
+}
+
 int b200m_bank_prepare_u8(uint8_t* bank, int32_t n_img, int64_t k_stride, const int32_t* k_per_image,
-                          int32_t* sqnorm, void* stream) {
-  if (!bank || !k_per_image || !sqnorm || n_img <= 0) return fail(B200M_E_BAD_ARG, "null argument or n_img <= 0%s");
+                          int32_t* norm_table, void* stream) {
+  if (!bank || !k_per_image || !norm_table || n_img <= 0) return fail(B200M_E_BAD_ARG, "null argument or n_img <= 0%s");
   if (k_stride <= 0 || (k_stride % B200M_TILE_T) != 0)
     return fail(B200M_E_BAD_ARG, "k_stride must be a positive multiple of 256%s");
   if (device_info().ok != 1) return fail(B200M_E_NO_DEVICE, "no sm_100 CUDA device available (no CPU fallback)%s");
@@ -195,22 +251,26 @@ int b200m_bank_prepare_u8(uint8_t* bank, int32_t n_img, int64_t k_stride, const 
   int64_t blocks = (n_rows * 32 + block - 1) / block;
   const int64_t max_blocks = static_cast<int64_t>(device_info().sms) * 16;
   if (blocks > max_blocks) blocks = max_blocks;
-  b200m::bank_prepare_kernel<<<static_cast<int>(blocks), block, 0, static_cast<cudaStream_t>(stream)>>>(
-      bank, n_rows, k_stride, k_per_image, sqnorm, B200M_PAD_NORM);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  b200m::bank_prepare_kernel<<<static_cast<int>(blocks), block, 0, st>>>(bank, n_rows, k_stride, k_per_image,
+                                                                         norm_table, B200M_PAD_NORM);
+  CUDA_TRY(cudaGetLastError());
+  int64_t blocks2 = (n_rows + block - 1) / block;
+  if (blocks2 > max_blocks) blocks2 = max_blocks;
+  b200m::norm_chunk_min_kernel<<<static_cast<int>(blocks2), block, 0, st>>>(norm_table, n_rows, norm_table + n_rows);
   CUDA_TRY(cudaGetLastError());
   return B200M_OK;
 }
 
 size_t b200m_workspace_bytes(int64_t k_stride, int64_t n_pairs) {
   if (k_stride <= 0 || n_pairs <= 0) return 256;
-  const int64_t b = batch_pairs(k_stride, n_pairs);
-  return static_cast<size_t>(b) * k_stride * (sizeof(int4) + sizeof(unsigned long long)) + 256;
+  return carve(nullptr, nullptr, batch_pairs(k_stride, n_pairs), k_stride);
 }
 
-int b200m_knn2_u8(const uint8_t* bank, const int32_t* sqnorm, const int32_t* k_per_image, int32_t n_img,
+int b200m_knn2_u8(const uint8_t* bank, const int32_t* norm_table, const int32_t* k_per_image, int32_t n_img,
                   int64_t k_stride, const int32_t* pairs, int64_t n_pairs, int32_t* out_train_idx,
                   float* out_dist, void* workspace, size_t workspace_bytes, void* stream) {
-  int rc = check_common(bank, sqnorm, k_per_image, n_img, k_stride, pairs, n_pairs);
+  int rc = check_common(bank, norm_table, k_per_image, n_img, k_stride, pairs, n_pairs);
   if (rc) return rc;
   if (n_pairs == 0) return B200M_OK;
   if (!out_train_idx || !out_dist || !workspace) return fail(B200M_E_BAD_ARG, "null output / workspace%s");
@@ -220,45 +280,58 @@ int b200m_knn2_u8(const uint8_t* bank, const int32_t* sqnorm, const int32_t* k_p
   rc = make_row_tmap(&tmap, bank, static_cast<uint64_t>(n_img) * k_stride);
   if (rc) return rc;
   const int64_t B = batch_pairs(k_stride, n_pairs);
-  uintptr_t wsp = (reinterpret_cast<uintptr_t>(workspace) + 255) & ~uintptr_t(255);
-  int4* rowres = reinterpret_cast<int4*>(wsp);
-  unsigned long long* colbest = reinterpret_cast<unsigned long long*>(rowres + B * k_stride);
+  Workspace w;
+  carve(&w, workspace, B, k_stride);
   for (int64_t p0 = 0; p0 < n_pairs; p0 += B) {
     const int64_t nb = (n_pairs - p0 < B) ? (n_pairs - p0) : B;
-    rc = sweep_batch(tmap, sqnorm, k_per_image, k_stride, pairs + 2 * p0, nb, rowres, colbest, st);
+    const b200m::SweepParams sp = base_params(norm_table, n_img, k_per_image, k_stride, pairs + 2 * p0, nb, w);
+    rc = sweep_top2(tmap, sp, st);
     if (rc) return rc;
     dim3 grid(static_cast<unsigned>((k_stride + 255) / 256), static_cast<unsigned>(nb));
-    b200m::knn2_finalize_kernel<<<grid, 256, 0, st>>>(rowres, pairs + 2 * p0, k_per_image, k_stride,
+    b200m::knn2_finalize_kernel<<<grid, 256, 0, st>>>(w.rowres, pairs + 2 * p0, k_per_image, k_stride,
                                                       out_train_idx + 2 * p0 * k_stride, out_dist + 2 * p0 * k_stride);
     CUDA_TRY(cudaGetLastError());
   }
   return B200M_OK;
 }
 
-int b200m_match_pairs_u8(const uint8_t* bank, const int32_t* sqnorm, const int32_t* k_per_image, int32_t n_img,
+int b200m_match_pairs_u8(const uint8_t* bank, const int32_t* norm_table, const int32_t* k_per_image, int32_t n_img,
                          int64_t k_stride, const int32_t* pairs, int64_t n_pairs, double ratio, int mutual,
                          int32_t* out_query_idx, int32_t* out_train_idx, float* out_dist, int32_t* out_count,
                          int64_t cap, void* workspace, size_t workspace_bytes, void* stream) {
-  int rc = check_common(bank, sqnorm, k_per_image, n_img, k_stride, pairs, n_pairs);
+  int rc = check_common(bank, norm_table, k_per_image, n_img, k_stride, pairs, n_pairs);
   if (rc) return rc;
   if (n_pairs == 0) return B200M_OK;
   if (!out_query_idx || !out_train_idx || !out_dist || !out_count || !workspace || cap <= 0)
     return fail(B200M_E_BAD_ARG, "null output / workspace or cap <= 0%s");
   if (workspace_bytes < b200m_workspace_bytes(k_stride, n_pairs)) return fail(B200M_E_WORKSPACE, "workspace too small%s");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  CUtensorMap tmap;
-  rc = make_row_tmap(&tmap, bank, static_cast<uint64_t>(n_img) * k_stride);
-  if (rc) return rc;
   const int64_t B = batch_pairs(k_stride, n_pairs);
-  uintptr_t wsp = (reinterpret_cast<uintptr_t>(workspace) + 255) & ~uintptr_t(255);
-  int4* rowres = reinterpret_cast<int4*>(wsp);
-  unsigned long long* colbest = reinterpret_cast<unsigned long long*>(rowres + B * k_stride);
+  Workspace w;
+  carve(&w, workspace, B, k_stride);
+  CUtensorMap tmap_bank, tmap_gath;
+  rc = make_row_tmap(&tmap_bank, bank, static_cast<uint64_t>(n_img) * k_stride);
+  if (rc) return rc;
+  rc = make_row_tmap(&tmap_gath, w.gathered, static_cast<uint64_t>(B) * k_stride);
+  if (rc) return rc;
   for (int64_t p0 = 0; p0 < n_pairs; p0 += B) {
     const int64_t nb = (n_pairs - p0 < B) ? (n_pairs - p0) : B;
-    rc = sweep_batch(tmap, sqnorm, k_per_image, k_stride, pairs + 2 * p0, nb, rowres, colbest, st);
+    const int32_t* pb = pairs + 2 * p0;
+    const b200m::SweepParams sp = base_params(norm_table, n_img, k_per_image, k_stride, pb, nb, w);
+    rc = sweep_top2(tmap_bank, sp, st);
     if (rc) return rc;
-    b200m::match_finalize_kernel<1024><<<static_cast<unsigned>(nb), 1024, 0, st>>>(
-        rowres, colbest, pairs + 2 * p0, k_per_image, k_stride, ratio, mutual, out_query_idx + p0 * cap,
+    b200m::select_kernel<1024><<<static_cast<unsigned>(nb), 1024, 0, st>>>(
+        w.rowres, pb, k_per_image, k_stride, ratio, bank, norm_table, mutual ? 1 : 0, w.surv_q, w.surv_t, w.surv_d,
+        w.surv_thr, w.surv_count, w.gathered);
+    CUDA_TRY(cudaGetLastError());
+    if (mutual) {
+      // lazy cross-check: second sweep only over the survivors' train descriptors
+      const int grid = sweep_grid(nb * sp.blocks_per_pair);
+      rc = launch_sweep<b200m::kThresh>(tmap_gath, tmap_bank, sp, grid, st);
+      if (rc) return rc;
+    }
+    b200m::emit_kernel<1024><<<static_cast<unsigned>(nb), 1024, 0, st>>>(
+        w.surv_q, w.surv_t, w.surv_d, w.surv_viol, w.surv_count, k_stride, mutual ? 1 : 0, out_query_idx + p0 * cap,
         out_train_idx + p0 * cap, out_dist + p0 * cap, out_count + p0, cap);
     CUDA_TRY(cudaGetLastError());
   }
@@ -271,7 +344,7 @@ int b200m_match_pairs_u8(const uint8_t* bank, const int32_t* sqnorm, const int32
 namespace b200m {
 
 struct DebugSmem {
-  uint8_t a[kABytes];
+  uint8_t a[kMBytes];
   uint8_t b[kBBytes];
   uint64_t full, done;
   uint32_t tmem_base;
@@ -294,7 +367,7 @@ debug_dot_tile_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_c
   tc_fence_after();
   const uint32_t tmem_base = sm.tmem_base;
   if (threadIdx.x == 0) {
-    mbar_arrive_expect_tx(&sm.full, kABytes + kBBytes);
+    mbar_arrive_expect_tx(&sm.full, kMBytes + kBBytes);
     tma_load_2d(sm.a, &tmap_a, 0, 0, &sm.full);
     tma_load_2d(sm.b, &tmap_b, 0, 0, &sm.full);
     tma_load_2d(sm.b + kBBytes / 2, &tmap_b, 0, 128, &sm.full);
@@ -302,7 +375,7 @@ debug_dot_tile_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_c
     tc_fence_after();
     const uint64_t adesc = make_desc_k128(smem_u32(sm.a));
     const uint64_t bdesc = make_desc_k128(smem_u32(sm.b));
-    constexpr uint32_t idesc = make_idesc_u8(kTQ, kTT);
+    constexpr uint32_t idesc = make_idesc_u8(kTM, kTT);
 #pragma unroll
     for (int k = 0; k < kD / 32; ++k) mma_i8_ss(tmem_base, adesc + 2 * k, bdesc + 2 * k, idesc, k > 0 ? 1u : 0u);
     tc_commit(&sm.done);

@@ -33,6 +33,21 @@ __global__ void bank_prepare_kernel(uint8_t* __restrict__ bank, int64_t n_rows, 
   }
 }
 
+// Minimum squared norm of every 32 consecutive rows (one warp per chunk): the sweep's
+// threshold-reject test needs min |col|^2 over a 32-column chunk.
+__global__ void norm_chunk_min_kernel(const int32_t* __restrict__ sqnorm, int64_t n_rows,
+                                      int32_t* __restrict__ nbmin32) {
+  const int64_t warp_global = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+  const int64_t n_warps = (static_cast<int64_t>(gridDim.x) * blockDim.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  for (int64_t c = warp_global; c < n_rows / 32; c += n_warps) {
+    int m = sqnorm[c * 32 + lane];
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) m = min(m, __shfl_xor_sync(0xffffffffu, m, off));
+    if (lane == 0) nbmin32[c] = m;
+  }
+}
+
 __device__ __forceinline__ float dist_from_sq(int d2) {
   // exact: d2 < 2^24 is representable, sqrt is IEEE round-to-nearest == cv2's std::sqrt(float)
   return __fsqrt_rn(static_cast<float>(d2));
@@ -58,75 +73,114 @@ __global__ void knn2_finalize_kernel(const int4* __restrict__ rowres, const int3
   }
 }
 
-// Ratio test + mutual check + order-preserving compaction. One CTA per pair.
-//   keep q  <=>  has second neighbour and double(d1) < ratio * double(d2)   (ratio > 0)
-//               and colbest[t1].row == q                                    (mutual)
+// Order-preserving block compaction helper: returns this thread's slot among the kept ones and
+// advances the CTA-wide running total. All threads of the CTA must call it.
+template <int kBlock>
+__device__ __forceinline__ int block_compact_slot(bool keep, int* warp_sums, int* running) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const unsigned ballot = __ballot_sync(0xffffffffu, keep);
+  const int prefix = __popc(ballot & ((1u << lane) - 1u));
+  if (lane == 0) warp_sums[warp] = __popc(ballot);
+  __syncthreads();
+  int woff = 0, total = 0;
+#pragma unroll
+  for (int w = 0; w < kBlock / 32; ++w) {
+    const int c = warp_sums[w];
+    if (w < warp) woff += c;
+    total += c;
+  }
+  const int start = *running;
+  __syncthreads();
+  if (threadIdx.x == 0) *running = start + total;
+  __syncthreads();
+  return start + woff + prefix;
+}
+
+// Ratio test on the row results of the first sweep; survivors are compacted in ascending query
+// order into the workspace and (for the mutual check) their train descriptors are gathered so the
+// second sweep can stream them with plain TMA.
+//   keep q  <=>  has second neighbour and double(d1) < ratio * double(d2)      (ratio > 0)
 // The compare is done in double on the float32 distances: exactly Python's
 // `m.distance < 0.75 * n.distance` on cv2 DMatch objects.
 template <int kBlock>
 __global__ void __launch_bounds__(kBlock)
-match_finalize_kernel(const int4* __restrict__ rowres, const unsigned long long* __restrict__ colbest,
-                      const int32_t* __restrict__ pairs, const int32_t* __restrict__ k_per_image,
-                      int64_t k_stride, double ratio, int mutual, int32_t* __restrict__ out_q,
-                      int32_t* __restrict__ out_t, float* __restrict__ out_d, int32_t* __restrict__ out_count,
-                      int64_t cap) {
+select_kernel(const int4* __restrict__ rowres, const int32_t* __restrict__ pairs,
+              const int32_t* __restrict__ k_per_image, int64_t k_stride, double ratio,
+              const uint8_t* __restrict__ bank, const int32_t* __restrict__ sqnorm, int do_gather,
+              int32_t* __restrict__ surv_q, int32_t* __restrict__ surv_t, float* __restrict__ surv_d,
+              int32_t* __restrict__ surv_thr, int32_t* __restrict__ surv_count,
+              uint8_t* __restrict__ gathered) {
   __shared__ int warp_sums[kBlock / 32];
   __shared__ int running;
   const int pair = blockIdx.x;
+  const int ti = pairs[2 * pair + 1];
   const int kq = k_per_image[pairs[2 * pair]];
-  const int kt = k_per_image[pairs[2 * pair + 1]];
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int kt = k_per_image[ti];
+  if (threadIdx.x == 0) running = 0;
+  __syncthreads();
+  const int64_t base = static_cast<int64_t>(pair) * k_stride;
+  const int64_t tbase = static_cast<int64_t>(ti) * k_stride;
+  for (int r0 = 0; r0 < kq && kt > 0; r0 += kBlock) {
+    const int r = r0 + threadIdx.x;
+    bool keep = false;
+    int4 v = make_int4(0, -1, 0, -1);
+    float d1f = 0.f;
+    if (r < kq) {
+      v = rowres[base + r];
+      const bool has1 = v.y >= 0 && v.y < kt;
+      const bool has2 = v.w >= 0 && v.w < kt;
+      if (has1) {
+        d1f = dist_from_sq(v.x);
+        keep = ratio > 0.0 ? (has2 && static_cast<double>(d1f) < ratio * static_cast<double>(dist_from_sq(v.z)))
+                           : true;
+      }
+    }
+    const int slot = block_compact_slot<kBlock>(keep, warp_sums, &running);
+    if (keep) {
+      const int64_t o = base + slot;
+      surv_q[o] = r;
+      surv_t[o] = v.y;
+      surv_d[o] = d1f;
+      surv_thr[o] = v.x - sqnorm[tbase + v.y];
+      if (do_gather) {
+        const uint4* src = reinterpret_cast<const uint4*>(bank + (tbase + v.y) * 128);
+        uint4* dst = reinterpret_cast<uint4*>(gathered + o * 128);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) dst[i] = src[i];
+      }
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) surv_count[pair] = running;
+}
+
+// Final order-preserving compaction of the survivors that passed the mutual check.
+template <int kBlock>
+__global__ void __launch_bounds__(kBlock)
+emit_kernel(const int32_t* __restrict__ surv_q, const int32_t* __restrict__ surv_t,
+            const float* __restrict__ surv_d, const int32_t* __restrict__ surv_viol,
+            const int32_t* __restrict__ surv_count, int64_t k_stride, int mutual,
+            int32_t* __restrict__ out_q, int32_t* __restrict__ out_t, float* __restrict__ out_d,
+            int32_t* __restrict__ out_count, int64_t cap) {
+  __shared__ int warp_sums[kBlock / 32];
+  __shared__ int running;
+  const int pair = blockIdx.x;
+  const int n = surv_count[pair];
   if (threadIdx.x == 0) running = 0;
   __syncthreads();
   const int64_t base = static_cast<int64_t>(pair) * k_stride;
   const int64_t obase = static_cast<int64_t>(pair) * cap;
-  for (int r0 = 0; r0 < kq && kt > 0; r0 += kBlock) {
-    const int r = r0 + threadIdx.x;
-    bool keep = false;
-    int t1 = -1;
-    float d1f = 0.f;
-    if (r < kq) {
-      const int4 v = rowres[base + r];
-      const bool has1 = v.y >= 0 && v.y < kt;
-      const bool has2 = v.w >= 0 && v.w < kt;
-      if (has1) {
-        t1 = v.y;
-        d1f = dist_from_sq(v.x);
-        if (ratio > 0.0) {
-          keep = has2 && (static_cast<double>(d1f) < ratio * static_cast<double>(dist_from_sq(v.z)));
-        } else {
-          keep = true;
-        }
-        if (keep && mutual) {
-          const unsigned long long cb = colbest[base + t1];
-          keep = static_cast<uint32_t>(cb & 0xffffffffull) == static_cast<uint32_t>(r);
-        }
-      }
+  for (int s0 = 0; s0 < n; s0 += kBlock) {
+    const int s = s0 + threadIdx.x;
+    const bool keep = s < n && (!mutual || surv_viol[base + s] == 0);
+    const int slot = block_compact_slot<kBlock>(keep, warp_sums, &running);
+    if (keep && slot < cap) {
+      out_q[obase + slot] = surv_q[base + s];
+      out_t[obase + slot] = surv_t[base + s];
+      out_d[obase + slot] = surv_d[base + s];
     }
-    const unsigned ballot = __ballot_sync(0xffffffffu, keep);
-    const int prefix = __popc(ballot & ((1u << lane) - 1u));
-    if (lane == 0) warp_sums[warp] = __popc(ballot);
-    __syncthreads();
-    int woff = 0, total = 0;
-#pragma unroll
-    for (int w = 0; w < kBlock / 32; ++w) {
-      const int c = warp_sums[w];
-      if (w < warp) woff += c;
-      total += c;
-    }
-    const int start = running;
-    if (keep) {
-      const int64_t slot = static_cast<int64_t>(start) + woff + prefix;
-      if (slot < cap) {
-        out_q[obase + slot] = r;
-        out_t[obase + slot] = t1;
-        out_d[obase + slot] = d1f;
-      }
-    }
-    __syncthreads();
-    if (threadIdx.x == 0) running = start + total;
-    __syncthreads();
   }
+  __syncthreads();
   if (threadIdx.x == 0) out_count[pair] = running;
 }
 

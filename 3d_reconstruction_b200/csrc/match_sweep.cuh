@@ -1,145 +1,162 @@
-// The sweep kernel: exhaustive squared-L2 distances between the query and train descriptors of
-// every scheduled image pair on tcgen05 int8 tensor cores, with the 2-NN (per query row) and the
-// nearest-query (per train column) reductions fused into the TMEM epilogue, so the Kq x Kt
-// distance matrix never leaves the SM.
+// The sweep kernel: exhaustive squared-L2 distances between two descriptor sets on tcgen05 int8
+// tensor cores with the nearest-neighbour reductions fused into the TMEM epilogue, so the distance
+// matrix never leaves the SM.
 //
 // Stands in for the dense contraction + arg-best passes of the reference matcher head
-//   lightglue/lightglue.py:223  sim = einsum('bmd,bnd->bmn')      (dense contraction)
-//   lightglue/lightglue.py:237  scores.max(2), scores.max(1)      (row / column arg-best)
+//   lightglue/lightglue.py:223      sim = einsum('bmd,bnd->bmn')     (dense contraction)
+//   lightglue/lightglue.py:237      scores.max(2), scores.max(1)     (row / column arg-best)
+//   lightglue/lightglue.py:239-242  mutual check
 // in the exact-integer L2 form BASELINE.json names (cv2.BFMatcher NORM_L2 knnMatch k=2 + crossCheck).
 //
-// One CTA = one SM, persistent over work items (pair, query tile of 128 rows). For an item the CTA
-// keeps the 128 x 128 B query tile resident in shared memory and sweeps the train image in tiles of
-// 256 rows:
-//   warp 0      TMA producer   (query tile per item, train tiles through a 5-deep ring)
-//   warp 1      MMA issuer     (4 x tcgen05.mma.kind::i8 M128 N256 K32 per train tile -> TMEM)
+// One CTA = one SM, persistent over work items. An item keeps a block of 256 "row" descriptors
+// (two UMMA M-tiles of 128) resident in shared memory and sweeps a "column" image in tiles of 256:
+//   warp 0      TMA producer   (row block per item; column tiles + their norms through rings)
+//   warp 1      MMA issuer     (per column tile: 2 x 4 tcgen05.mma.kind::i8 M128 N256 K32)
 //   warp 2      TMEM allocator
-//   warps 4-11  epilogue       (tcgen05.ld -> registers; row top-2 stays in registers for the
-//                               whole sweep, column minima go out as packed 64-bit atomicMin)
-// Two 128 x 256 int32 accumulators (all 512 TMEM columns) double-buffer MMA against the epilogue.
+//   warps 4-7   epilogue group 0 (M-tile 0, accumulator 0: TMEM columns 0..255)
+//   warps 8-11  epilogue group 1 (M-tile 1, accumulator 1: TMEM columns 256..511)
+// The two accumulators alternate, so the MMA of one M-tile overlaps the epilogue of the other, and
+// every column tile fetched from L2 is used for 256 rows. Each epilogue thread owns one row for the
+// whole sweep (tcgen05.ld 32x32b: lane == row), so row reductions never leave its registers.
+//
+// Two passes share the kernel (kKind):
+//   kTop2    rows = query descriptors of a pair, columns = train descriptors: exact top-2 per row.
+//            A threshold-reject epilogue does one 3-input integer max per two accumulator values and
+//            runs the exact insertion only for 8-column groups that can change the row's top-2.
+//   kThresh  the mutual (cross) check, done lazily: rows = train descriptors of the ratio-test
+//            survivors (gathered), columns = all query descriptors; a row is violated when some
+//            query is strictly nearer (or equally near with a lower index) than its own.
+//   kTop2Exact / kPeak  debugging (every element through the insertion) and MMA-only ceiling.
 #pragma once
 #include "ptx_sm100.cuh"
 
 namespace b200m {
 
 constexpr int kD = 128;             // descriptor bytes
-constexpr int kTQ = 128;            // query rows per tile  (UMMA M)
-constexpr int kTT = 256;            // train rows per tile  (UMMA N)
-constexpr int kABytes = kTQ * kD;   // 16 KiB
-constexpr int kBBytes = kTT * kD;   // 32 KiB
+constexpr int kTM = 128;            // rows per UMMA M-tile
+constexpr int kRows = 256;          // rows per work item (two M-tiles)
+constexpr int kTT = 256;            // columns per tile (UMMA N)
+constexpr int kMBytes = kTM * kD;   // 16 KiB per M-tile
+constexpr int kBBytes = kTT * kD;   // 32 KiB per column tile
 constexpr int kAStages = 2;
-constexpr int kBStages = 5;
-constexpr int kAccStages = 2;       // TMEM accumulator buffers of 256 columns
+constexpr int kBStages = 4;
+constexpr int kNStages = 4;         // norms ring
 constexpr int kEpiWarps = 8;
 constexpr int kFirstEpiWarp = 4;
 constexpr int kThreads = (kFirstEpiWarp + kEpiWarps) * 32;  // 384
-constexpr int kPadNorm = 1 << 23;
-constexpr int kIntMax = 0x7fffffff;
+constexpr int kPadNorm = 1 << 23;   // > 128*255^2: norm of a padding row
+constexpr int kBig = 1 << 28;       // "no candidate yet" score; 2*acc + kBig cannot overflow
+
+enum SweepKind { kTop2 = 0, kThresh = 1, kPeak = 2, kTop2Exact = 3 };
+
+struct NormSlot {
+  int32_t nb[kTT];      // squared norms of the tile's 256 columns
+  int32_t nbmin[8];     // minimum per 32-column chunk
+};
 
 struct SweepSmem {
   // tiles first: SWIZZLE_128B needs 1024 B alignment
-  uint8_t a[kAStages][kABytes];
+  uint8_t a[kAStages][2][kMBytes];
   uint8_t b[kBStages][kBBytes];
+  NormSlot norms[kNStages];
   uint64_t a_full[kAStages], a_empty[kAStages];
   uint64_t b_full[kBStages], b_empty[kBStages];
-  uint64_t t_full[kAccStages], t_empty[kAccStages];
+  uint64_t n_full[kNStages], n_empty[kNStages];
+  uint64_t t_full[2], t_empty[2];
   uint32_t tmem_base;
-  uint32_t pad_[3];
-  int32_t nbw[kEpiWarps][2][128];      // per epilogue warp: train norms of its 128 columns, double-buffered
-  int32_t nbmin[kEpiWarps][2][4];      // per 32-column chunk minimum of the above
-  int4 rowmerge[2][kTQ];               // half-1 warps hand their row top-2 to half-0 warps
 };
 
 struct SweepParams {
-  const int32_t* sqnorm;        // [n_img, k_stride]
+  const int32_t* sqnorm;        // [n_img * k_stride] squared norms (kPadNorm on padding rows)
+  const int32_t* nbmin32;       // [n_img * k_stride / 32] minima of the above per 32 rows
   const int32_t* k_per_image;   // [n_img]
-  const int32_t* pairs;         // [n_pairs, 2] for this batch
+  const int32_t* pairs;         // [n_pairs, 2] (query image, train image) of this batch
   int64_t k_stride;
   int32_t n_pairs;
-  int32_t qtiles;               // k_stride / 128
-  int4* rowres;                 // [n_pairs, k_stride] (d1^2, i1, d2^2, i2)
-  unsigned long long* colbest;  // [n_pairs, k_stride] (d^2 << 32) | query row
+  int32_t blocks_per_pair;      // k_stride / 256
+  // kTop2 output: per (pair, query row) (d1^2, i1, d2^2, i2)
+  int4* rowres;
+  // kThresh: survivors of the ratio test, slot s of pair p lives at p * k_stride + s
+  const int32_t* surv_count;    // [n_pairs]
+  const int32_t* surv_q;        // query row of the survivor
+  const int32_t* surv_thr;      // d1^2 - |t1|^2 : the score a query must beat
+  int32_t* surv_viol;           // out: 1 when a better (or equal, lower-index) query exists
 };
 
 struct ItemInfo {
-  int pair, qt, qi, ti, kq, kt, ntiles;
+  int pair, blk;
+  int row_img_row0;   // first A row in tensor-map A coordinates
+  int col_img;        // image whose rows are the columns
+  int n_rows;         // valid rows in this block (1..256)
+  int n_cols;         // valid columns in the sweep
+  int ntiles, nm;
   bool valid;
 };
 
+template <int kKind>
 __device__ __forceinline__ ItemInfo decode_item(const SweepParams& p, int item) {
   ItemInfo it;
-  it.pair = item / p.qtiles;
-  it.qt = item - it.pair * p.qtiles;
-  it.qi = __ldg(p.pairs + 2 * it.pair);
-  it.ti = __ldg(p.pairs + 2 * it.pair + 1);
-  it.kq = __ldg(p.k_per_image + it.qi);
-  it.kt = __ldg(p.k_per_image + it.ti);
-  it.ntiles = (it.kt + kTT - 1) / kTT;
-  it.valid = (it.qt * kTQ < it.kq) && (it.ntiles > 0);
+  it.pair = item / p.blocks_per_pair;
+  it.blk = item - it.pair * p.blocks_per_pair;
+  const int qi = __ldg(p.pairs + 2 * it.pair);
+  const int ti = __ldg(p.pairs + 2 * it.pair + 1);
+  const int kq = __ldg(p.k_per_image + qi);
+  const int kt = __ldg(p.k_per_image + ti);
+  if (kKind == kThresh) {
+    const int s = __ldg(p.surv_count + it.pair);
+    it.n_rows = s - it.blk * kRows;
+    it.n_cols = kq;
+    it.col_img = qi;
+    it.row_img_row0 = static_cast<int>(it.pair * p.k_stride + it.blk * kRows);   // gathered buffer
+  } else {
+    it.n_rows = kq - it.blk * kRows;
+    it.n_cols = kt;
+    it.col_img = ti;
+    it.row_img_row0 = static_cast<int>(qi * p.k_stride + it.blk * kRows);        // bank
+  }
+  if (it.n_rows > kRows) it.n_rows = kRows;
+  it.ntiles = (it.n_cols + kTT - 1) / kTT;
+  it.nm = it.n_rows > kTM ? 2 : 1;
+  it.valid = it.n_rows > 0 && it.ntiles > 0;
   return it;
 }
 
-// Exact insertion of (s, n) into a row's running top-2, n strictly increasing within a thread:
-// strict '<' keeps the lowest index on ties, and a duplicate of the best becomes the second best
+// Exact insertion of (s, n) into a row's running top-2. Within a thread n is strictly increasing,
+// so strict '<' keeps the lowest index on ties and a duplicate of the best becomes the second best
 // (the stable-argsort rule cv2.BFMatcher follows).
 __device__ __forceinline__ void top2_insert(int s, int n, int& s1, int& i1, int& s2, int& i2) {
   const bool lt1 = s < s1;
-  const bool lt2 = s < s2;
-  s2 = lt1 ? s1 : (lt2 ? s : s2);
-  i2 = lt1 ? i1 : (lt2 ? n : i2);
+  s2 = lt1 ? s1 : s;
+  i2 = lt1 ? i1 : n;
   s1 = lt1 ? s : s1;
   i1 = lt1 ? n : i1;
 }
 
-__device__ __forceinline__ bool lex_less(int sa, int ia, int sb, int ib) {
-  return sa < sb || (sa == sb && ia < ib);
+__device__ __forceinline__ int max8(const int* v) {
+  int m = __vimax3_s32(v[0], v[1], v[2]);
+  m = __vimax3_s32(m, v[3], v[4]);
+  m = __vimax3_s32(m, v[5], v[6]);
+  return max(m, v[7]);
 }
 
-// Transposing min-reduction: on entry lane r holds v[j] = key(row r, column j), j < 32;
-// on exit lane L holds in v[0] the minimum over the warp's 32 rows for column L.
-__device__ __forceinline__ void warp_colmin_32(int (&v)[32], uint32_t lane) {
-#pragma unroll
-  for (int off = 16; off >= 1; off >>= 1) {
-    const bool up = (lane & off) != 0;
-#pragma unroll
-    for (int j = 0; j < off; ++j) {
-      const int send = up ? v[j] : v[j + off];
-      const int keep = up ? v[j + off] : v[j];
-      const int recv = __shfl_xor_sync(0xffffffffu, send, off);
-      v[j] = min(keep, recv);
-    }
-  }
-}
-
-// Publish the warp's column minima for 32 columns. kc = (na - 2 a.b) * 128 + local query row.
-__device__ __forceinline__ void publish_colmin(int kc, int nb_col, int n_col, int kt, int qrow0,
-                                               unsigned long long* colbest_pair) {
-  const int score = kc >> 7;
-  if (n_col < kt && score < kPadNorm) {
-    const unsigned long long key =
-        (static_cast<unsigned long long>(static_cast<unsigned>(score + nb_col)) << 32) |
-        static_cast<unsigned>(qrow0 + (kc & 127));
-    unsigned long long* dst = colbest_pair + n_col;
-    const unsigned long long cur = *reinterpret_cast<volatile unsigned long long*>(dst);
-    if (key < cur) atomicMin(dst, key);
-  }
-}
-
-template <int kMode>
+template <int kKind>
 __global__ void __launch_bounds__(kThreads, 1)
-sweep_kernel(const __grid_constant__ CUtensorMap tmap, const SweepParams p) {
+sweep_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+             const SweepParams p) {
   extern __shared__ uint8_t smem_raw[];
   SweepSmem& sm = *reinterpret_cast<SweepSmem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
 
   const uint32_t warp = threadIdx.x >> 5;
   const uint32_t lane = lane_id();
-  const int n_items = p.n_pairs * p.qtiles;
+  const int n_items = p.n_pairs * p.blocks_per_pair;
 
   if (warp == 0 && lane == 0) {
-    tma_prefetch_desc(&tmap);
+    tma_prefetch_desc(&tmap_a);
+    tma_prefetch_desc(&tmap_b);
     for (int i = 0; i < kAStages; ++i) { mbar_init(&sm.a_full[i], 1); mbar_init(&sm.a_empty[i], 1); }
     for (int i = 0; i < kBStages; ++i) { mbar_init(&sm.b_full[i], 1); mbar_init(&sm.b_empty[i], 1); }
-    for (int i = 0; i < kAccStages; ++i) { mbar_init(&sm.t_full[i], 1); mbar_init(&sm.t_empty[i], kEpiWarps); }
+    for (int i = 0; i < kNStages; ++i) { mbar_init(&sm.n_full[i], 1); mbar_init(&sm.n_empty[i], kEpiWarps); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&sm.t_full[i], 1); mbar_init(&sm.t_empty[i], kEpiWarps / 2); }
     fence_mbar_init();
   }
   if (warp == 2) tmem_alloc<512>(&sm.tmem_base);
@@ -151,22 +168,31 @@ sweep_kernel(const __grid_constant__ CUtensorMap tmap, const SweepParams p) {
   if (warp == 0) {
     // ------------------------------------------------------------- TMA producer
     if (lane == 0) {
-      uint32_t a_it = 0, b_it = 0;
+      uint32_t a_it = 0, b_it = 0, n_it = 0;
       for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
-        const ItemInfo it = decode_item(p, item);
+        const ItemInfo it = decode_item<kKind>(p, item);
         if (!it.valid) continue;
         const uint32_t as = a_it % kAStages, aph = (a_it / kAStages) & 1;
         mbar_wait(&sm.a_empty[as], aph ^ 1);
-        mbar_arrive_expect_tx(&sm.a_full[as], kABytes);
-        tma_load_2d(sm.a[as], &tmap, 0, static_cast<int32_t>(it.qi * p.k_stride + it.qt * kTQ), &sm.a_full[as]);
+        mbar_arrive_expect_tx(&sm.a_full[as], it.nm * kMBytes);
+        for (int m = 0; m < it.nm; ++m) tma_load_2d(sm.a[as][m], &tmap_a, 0, it.row_img_row0 + m * kTM, &sm.a_full[as]);
         ++a_it;
-        const int32_t trow0 = static_cast<int32_t>(it.ti * p.k_stride);
+        const int64_t crow0 = static_cast<int64_t>(it.col_img) * p.k_stride;
         for (int t = 0; t < it.ntiles; ++t) {
+          const int32_t crow = static_cast<int32_t>(crow0 + t * kTT);
+          if (kKind != kPeak) {
+            const uint32_t ns = n_it % kNStages, nph = (n_it / kNStages) & 1;
+            mbar_wait(&sm.n_empty[ns], nph ^ 1);
+            mbar_arrive_expect_tx(&sm.n_full[ns], sizeof(NormSlot));
+            bulk_load(sm.norms[ns].nb, p.sqnorm + crow, kTT * 4, &sm.n_full[ns]);
+            bulk_load(sm.norms[ns].nbmin, p.nbmin32 + crow / 32, 8 * 4, &sm.n_full[ns]);
+            ++n_it;
+          }
           const uint32_t bs = b_it % kBStages, bph = (b_it / kBStages) & 1;
           mbar_wait(&sm.b_empty[bs], bph ^ 1);
           mbar_arrive_expect_tx(&sm.b_full[bs], kBBytes);
-          tma_load_2d(sm.b[bs], &tmap, 0, trow0 + t * kTT, &sm.b_full[bs]);
-          tma_load_2d(sm.b[bs] + kBBytes / 2, &tmap, 0, trow0 + t * kTT + 128, &sm.b_full[bs]);
+          tma_load_2d(sm.b[bs], &tmap_b, 0, crow, &sm.b_full[bs]);
+          tma_load_2d(sm.b[bs] + kBBytes / 2, &tmap_b, 0, crow + 128, &sm.b_full[bs]);
           ++b_it;
         }
       }
@@ -174,31 +200,32 @@ sweep_kernel(const __grid_constant__ CUtensorMap tmap, const SweepParams p) {
   } else if (warp == 1) {
     // ------------------------------------------------------------- MMA issuer
     if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc_u8(kTQ, kTT);
-      uint32_t a_it = 0, b_it = 0, t_it = 0;
+      constexpr uint32_t idesc = make_idesc_u8(kTM, kTT);
+      uint32_t a_it = 0, b_it = 0, t_it[2] = {0, 0};
       for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
-        const ItemInfo it = decode_item(p, item);
+        const ItemInfo it = decode_item<kKind>(p, item);
         if (!it.valid) continue;
         const uint32_t as = a_it % kAStages, aph = (a_it / kAStages) & 1;
         mbar_wait(&sm.a_full[as], aph);
-        const uint64_t adesc = make_desc_k128(smem_u32(sm.a[as]));
         for (int t = 0; t < it.ntiles; ++t) {
           const uint32_t bs = b_it % kBStages, bph = (b_it / kBStages) & 1;
-          const uint32_t ts = t_it % kAccStages, tph = (t_it / kAccStages) & 1;
           mbar_wait(&sm.b_full[bs], bph);
-          mbar_wait(&sm.t_empty[ts], tph ^ 1);
-          tc_fence_after();
           const uint64_t bdesc = make_desc_k128(smem_u32(sm.b[bs]));
-          const uint32_t tacc = tmem_base + ts * kTT;
+          for (int m = 0; m < it.nm; ++m) {
+            mbar_wait(&sm.t_empty[m], (t_it[m] & 1) ^ 1);
+            tc_fence_after();
+            const uint64_t adesc = make_desc_k128(smem_u32(sm.a[as][m]));
+            const uint32_t tacc = tmem_base + m * kTT;
 #pragma unroll
-          for (int k = 0; k < kD / 32; ++k) {
-            // +32 B along K inside the 128 B swizzle atom = +2 in the (addr >> 4) field
-            mma_i8_ss(tacc, adesc + 2 * k, bdesc + 2 * k, idesc, k > 0 ? 1u : 0u);
+            for (int k = 0; k < kD / 32; ++k) {
+              // +32 B along K inside the 128 B swizzle atom = +2 in the (addr >> 4) field
+              mma_i8_ss(tacc, adesc + 2 * k, bdesc + 2 * k, idesc, k > 0 ? 1u : 0u);
+            }
+            tc_commit(&sm.t_full[m]);   // accumulator m ready for its epilogue group
+            ++t_it[m];
           }
           tc_commit(&sm.b_empty[bs]);   // smem stage free once these MMAs retire
-          tc_commit(&sm.t_full[ts]);    // accumulator ready for the epilogue
           ++b_it;
-          ++t_it;
         }
         tc_commit(&sm.a_empty[as]);
         ++a_it;
@@ -208,125 +235,119 @@ sweep_kernel(const __grid_constant__ CUtensorMap tmap, const SweepParams p) {
     // ------------------------------------------------------------- epilogue
     const uint32_t ew = warp - kFirstEpiWarp;       // 0..7
     const uint32_t quad = warp & 3;                 // TMEM lane quadrant this warp may read
-    const uint32_t half = ew >> 2;                  // which 128 of the 256 tile columns
-    const int rl = quad * 32 + lane;                // query row inside the tile
-    uint32_t t_it = 0, item_it = 0;
+    const int m = ew >> 2;                          // M-tile / accumulator of this group
+    const int rl = m * kTM + quad * 32 + lane;      // row inside the item's block
+    uint32_t t_it = 0, n_it = 0;
     for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
-      const ItemInfo it = decode_item(p, item);
+      const ItemInfo it = decode_item<kKind>(p, item);
       if (!it.valid) continue;
-      const int qrow0 = it.qt * kTQ;
-      const int32_t* nb_img = p.sqnorm + it.ti * p.k_stride;
-      unsigned long long* colbest_pair = p.colbest + static_cast<int64_t>(it.pair) * p.k_stride;
-      const int na = __ldg(p.sqnorm + it.qi * p.k_stride + qrow0 + rl);   // kPadNorm on padding rows
-      const int rowc = na * 128 + rl;
-      int s1 = kIntMax, i1 = kIntMax, s2 = kIntMax, i2 = kIntMax;        // scores are nb - 2 a.b
+      const bool active = m < it.nm;
+      const int64_t orow = static_cast<int64_t>(it.pair) * p.k_stride + it.blk * kRows + rl;
 
-      // stage the norms of tile 0
-      {
-        const int4 nbv = __ldg(reinterpret_cast<const int4*>(nb_img + half * 128) + lane);
-        *reinterpret_cast<int4*>(&sm.nbw[ew][0][lane * 4]) = nbv;
-        int m = min(min(nbv.x, nbv.y), min(nbv.z, nbv.w));
-        m = min(m, __shfl_xor_sync(0xffffffffu, m, 1));
-        m = min(m, __shfl_xor_sync(0xffffffffu, m, 2));
-        m = min(m, __shfl_xor_sync(0xffffffffu, m, 4));
-        if ((lane & 7) == 0) sm.nbmin[ew][0][lane >> 3] = m;
-        __syncwarp();
+      // per-row state. scores are  |col|^2 - 2 row.col  (the row's own norm is added at the end)
+      int s1 = kBig, i1 = -1, s2 = kBig, i2 = -1;
+      int thr = kBig;          // kThresh: the score to beat;  my_q: the survivor's own query row
+      int my_q = 0;
+      int viol = 0;
+      if (kKind == kThresh) {
+        thr = -kBig;           // padding rows of the block can never be violated
+        if (active && rl < it.n_rows) {
+          thr = __ldg(p.surv_thr + orow);
+          my_q = __ldg(p.surv_q + orow);
+        }
       }
 
       for (int t = 0; t < it.ntiles; ++t) {
-        const uint32_t ts = t_it % kAccStages, tph = (t_it / kAccStages) & 1;
-        const int nbuf = t & 1;
-        // prefetch next tile's norms into registers while this tile is processed
-        int4 nbv_next = make_int4(kPadNorm, kPadNorm, kPadNorm, kPadNorm);
-        if (t + 1 < it.ntiles)
-          nbv_next = __ldg(reinterpret_cast<const int4*>(nb_img + (t + 1) * kTT + half * 128) + lane);
-
-        mbar_wait(&sm.t_full[ts], tph);
-        tc_fence_after();
-        const uint32_t taddr = tmem_base + ((quad * 32u) << 16) + ts * kTT + half * 128;
-        const int col0 = t * kTT + half * 128;
-        const int32_t* nbw = sm.nbw[ew][nbuf];
-
-#pragma unroll 1
-        for (int c = 0; c < 4; ++c) {
-          int v[32];
-          tmem_ld_32x32(taddr + c * 32, v);
-          tmem_ld_wait();
-          if (c == 3) {
-            // accumulator fully drained into registers: hand the TMEM buffer back to the MMA warp
+        const uint32_t ns = n_it % kNStages, nph = (n_it / kNStages) & 1;
+        ++n_it;
+        if (kKind == kPeak) {
+          if (active) {
+            mbar_wait(&sm.t_full[m], t_it & 1);
+            tc_fence_after();
+            int v[32];
+            tmem_ld_32x32(tmem_base + ((quad * 32u) << 16) + m * kTT, v);
+            tmem_ld_wait();
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(&sm.t_empty[ts]);
+            if (lane == 0) mbar_arrive(&sm.t_empty[m]);
+            s1 = min(s1, v[0]);
+            ++t_it;
           }
-          const int nbase = col0 + c * 32;
-          if (kMode == 0) {
-            // exact reference epilogue: every element goes through the top-2 insertion
-#pragma unroll
-            for (int j = 0; j < 32; ++j) {
-              const int s = nbw[c * 32 + j] - 2 * v[j];
-              top2_insert(s, nbase + j, s1, i1, s2, i2);
+          continue;
+        }
+        mbar_wait(&sm.n_full[ns], nph);
+        if (active) {
+          const NormSlot& nsl = sm.norms[ns];
+          mbar_wait(&sm.t_full[m], t_it & 1);
+          tc_fence_after();
+          const uint32_t taddr = tmem_base + ((quad * 32u) << 16) + m * kTT;
+          const int col0 = t * kTT;
+#pragma unroll 1
+          for (int c = 0; c < 8; ++c) {
+            int v[32];
+            tmem_ld_32x32(taddr + c * 32, v);
+            tmem_ld_wait();
+            if (c == 7) {
+              // accumulator fully drained into registers: hand it back to the MMA warp
+              tc_fence_before();
+              __syncwarp();
+              if (lane == 0) mbar_arrive(&sm.t_empty[m]);
             }
-          } else {
-            // threshold-reject epilogue: s < s2  <=>  2*acc > nb - s2; a chunk can only change the
-            // row's top-2 if 2*max(acc) + s2 > min(nb over the chunk). One 3-input max per two
-            // elements, the exact insertion runs only for chunks that pass.
-            int mx = v[0];
-#pragma unroll
-            for (int j = 1; j < 31; j += 2) mx = __vimax3_s32(mx, v[j], v[j + 1]);
-            mx = max(mx, v[31]);
-            const int nbm = sm.nbmin[ew][nbuf][c];
-            // s2 may be kIntMax: 2*mx + s2 would overflow, compare in 64 bit only on that path
-            const bool hit = (s2 == kIntMax) || (2 * mx + s2 > nbm);
-            if (hit) {
+            const int nbase = col0 + c * 32;
+            const int32_t* nb = nsl.nb + c * 32;
+            if (kKind == kTop2Exact) {
 #pragma unroll
               for (int j = 0; j < 32; ++j) {
-                const int s = nbw[c * 32 + j] - 2 * v[j];
+                const int s = nb[j] - 2 * v[j];
                 if (s < s2) top2_insert(s, nbase + j, s1, i1, s2, i2);
+              }
+            } else if (kKind == kTop2) {
+              // s < s2  <=>  2*acc + s2 > nb.  A group of columns can only change the row's top-2 if
+              // 2*max(acc) + s2 > min(nb); one 3-input max per two accumulator values.
+              const int g0 = max8(v), g1 = max8(v + 8), g2 = max8(v + 16), g3 = max8(v + 24);
+              const int mx = max(__vimax3_s32(g0, g1, g2), g3);
+              const int nbm = nsl.nbmin[c];
+              if (2 * mx + s2 > nbm) {
+#pragma unroll
+                for (int g = 0; g < 4; ++g) {
+                  const int gm = g == 0 ? g0 : (g == 1 ? g1 : (g == 2 ? g2 : g3));
+                  if (2 * gm + s2 > nbm) {
+#pragma unroll
+                    for (int j = 8 * g; j < 8 * g + 8; ++j) {
+                      const int s = nb[j] - 2 * v[j];
+                      if (s < s2) top2_insert(s, nbase + j, s1, i1, s2, i2);
+                    }
+                  }
+                }
+              }
+            } else {   // kThresh
+              // violated  <=>  exists column with s < thr, or s == thr and column index < my_q
+              const int g0 = max8(v), g1 = max8(v + 8), g2 = max8(v + 16), g3 = max8(v + 24);
+              const int mx = max(__vimax3_s32(g0, g1, g2), g3);
+              const int nbm = nsl.nbmin[c];
+              if (2 * mx + thr >= nbm) {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                  const int s = nb[j] - 2 * v[j];
+                  if (s < thr || (s == thr && nbase + j < my_q)) viol = 1;
+                }
               }
             }
           }
-          // column minima over this warp's 32 rows
-#pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = rowc - (v[j] << 8);
-          warp_colmin_32(v, lane);
-          publish_colmin(v[0], nbw[c * 32 + lane], nbase + lane, it.kt, qrow0, colbest_pair);
-        }
-
-        // stage next tile's norms (other buffer; this warp is the only reader/writer)
-        if (t + 1 < it.ntiles) {
-          *reinterpret_cast<int4*>(&sm.nbw[ew][nbuf ^ 1][lane * 4]) = nbv_next;
-          int m = min(min(nbv_next.x, nbv_next.y), min(nbv_next.z, nbv_next.w));
-          m = min(m, __shfl_xor_sync(0xffffffffu, m, 1));
-          m = min(m, __shfl_xor_sync(0xffffffffu, m, 2));
-          m = min(m, __shfl_xor_sync(0xffffffffu, m, 4));
-          if ((lane & 7) == 0) sm.nbmin[ew][nbuf ^ 1][lane >> 3] = m;
+          ++t_it;
         }
         __syncwarp();
-        ++t_it;
+        if (lane == 0) mbar_arrive(&sm.n_empty[ns]);
       }
 
-      // merge the two column halves of every row and store the row result
-      const uint32_t par = item_it & 1;
-      if (half == 1) sm.rowmerge[par][rl] = make_int4(s1, i1, s2, i2);
-      named_bar_sync(1, kEpiWarps * 32);
-      if (half == 0) {
-        const int4 o = sm.rowmerge[par][rl];
-        // half 0 holds lower column indices inside each tile but not globally: merge lexicographically
-        int r1s, r1i, r2s, r2i;
-        if (lex_less(o.x, o.y, s1, i1)) {
-          r1s = o.x; r1i = o.y;
-          if (lex_less(o.z, o.w, s1, i1)) { r2s = o.z; r2i = o.w; } else { r2s = s1; r2i = i1; }
+      if (active && rl < it.n_rows) {
+        if (kKind == kThresh) {
+          p.surv_viol[orow] = viol;
         } else {
-          r1s = s1; r1i = i1;
-          if (lex_less(o.x, o.y, s2, i2)) { r2s = o.x; r2i = o.y; } else { r2s = s2; r2i = i2; }
-        }
-        if (qrow0 + rl < it.kq) {
-          const int d1 = (r1s == kIntMax) ? kIntMax : r1s + na;
-          const int d2 = (r2s == kIntMax) ? kIntMax : r2s + na;
-          p.rowres[static_cast<int64_t>(it.pair) * p.k_stride + qrow0 + rl] = make_int4(d1, r1i, d2, r2i);
+          const int na = __ldg(p.sqnorm + it.row_img_row0 + rl);
+          p.rowres[orow] = make_int4(s1 + na, i1, s2 + na, i2);
         }
       }
-      ++item_it;
     }
   }
 

@@ -24,8 +24,8 @@
  *
  * Descriptor bank layout (HBM): uint8 [n_img, k_stride, 128], row-major, k_stride a multiple
  * of 256; image i owns rows [0, k_per_image[i]) of its slab, the remaining rows are padding.
- * b200m_bank_prepare_u8 zeroes the padding and writes the int32 squared norms
- * [n_img, k_stride] (padding rows get the sentinel B200M_PAD_NORM).
+ * b200m_bank_prepare_u8 zeroes the padding and writes the int32 norm table
+ * (squared norms [n_img, k_stride], padding rows = B200M_PAD_NORM, + per-32-row minima).
  */
 #ifndef B200M_H_
 #define B200M_H_
@@ -39,7 +39,7 @@ extern "C" {
 
 #define B200M_VERSION 100          /* 0.1.0 */
 #define B200M_DESC_DIM 128         /* SIFT / DISK descriptor length handled by the u8 path */
-#define B200M_TILE_Q 128           /* query rows per tile (UMMA M) */
+#define B200M_TILE_Q 128           /* query rows per UMMA M-tile (two per work item) */
 #define B200M_TILE_T 256           /* train rows per tile (UMMA N) */
 #define B200M_PAD_NORM (1 << 23)   /* > 128*255^2 = 8,323,200: marks a padding row */
 
@@ -61,10 +61,15 @@ int b200m_device_check(void);
 /* Number of SMs the sweep kernel will be launched on (persistent grid); <0 on error. */
 int b200m_sm_count(void);
 
-/* Zero the padding rows of `bank` and compute squared L2 norms (exact, int32).
+/* Elements (int32) of the norm table of a bank: n_img*k_stride squared norms followed by
+ * n_img*k_stride/32 minima over 32 consecutive rows (used by the threshold-reject epilogue). */
+int64_t b200m_norm_table_elems(int32_t n_img, int64_t k_stride);
+
+/* Zero the padding rows of `bank` and fill the norm table (exact int32 squared L2 norms,
+ * B200M_PAD_NORM on padding rows, then the per-32-row minima).
  * Replaces the per-pair repacking at matching.py:107-120 with a one-off pass. */
 int b200m_bank_prepare_u8(uint8_t* bank, int32_t n_img, int64_t k_stride,
-                          const int32_t* k_per_image, int32_t* sqnorm, void* stream);
+                          const int32_t* k_per_image, int32_t* norm_table, void* stream);
 
 /* Scratch bytes needed to process `n_pairs` pairs of images with slab stride `k_stride`.
  * Pairs are processed in internal batches, so this saturates at a fixed batch size. */
@@ -75,7 +80,7 @@ size_t b200m_workspace_bytes(int64_t k_stride, int64_t n_pairs);
  *   out_train_idx  int32 [n_pairs, k_stride, 2]  best / second-best train row, -1 = none
  *   out_dist       float [n_pairs, k_stride, 2]  float32 sqrt of the exact int32 squared distance
  * Rows >= k_per_image[query_img] are left untouched. Ties -> lowest train index (cv2 rule). */
-int b200m_knn2_u8(const uint8_t* bank, const int32_t* sqnorm, const int32_t* k_per_image,
+int b200m_knn2_u8(const uint8_t* bank, const int32_t* norm_table, const int32_t* k_per_image,
                   int32_t n_img, int64_t k_stride,
                   const int32_t* pairs, int64_t n_pairs,
                   int32_t* out_train_idx, float* out_dist,
@@ -90,7 +95,7 @@ int b200m_knn2_u8(const uint8_t* bank, const int32_t* sqnorm, const int32_t* k_p
  *   out_query_idx / out_train_idx / out_dist   [n_pairs, cap], ascending query index
  *   out_count  int32 [n_pairs]: matches FOUND; if > cap only the first cap were stored and the
  *              caller must treat the pair as overflowed (never silently truncated). */
-int b200m_match_pairs_u8(const uint8_t* bank, const int32_t* sqnorm, const int32_t* k_per_image,
+int b200m_match_pairs_u8(const uint8_t* bank, const int32_t* norm_table, const int32_t* k_per_image,
                          int32_t n_img, int64_t k_stride,
                          const int32_t* pairs, int64_t n_pairs,
                          double ratio, int mutual,
@@ -99,7 +104,8 @@ int b200m_match_pairs_u8(const uint8_t* bank, const int32_t* sqnorm, const int32
                          void* workspace, size_t workspace_bytes, void* stream);
 
 /* Tuning / introspection knobs (process-global, read at launch time).
- *   "epilogue"  0 = exact reference epilogue, 1 = threshold-reject epilogue (default)
+ *   "epilogue"  0 = exact insertion of every element (debug), 1 = threshold-reject (default),
+ *               2 = MMA-only ceiling measurement (results invalid)
  *   "grid"      number of persistent CTAs, 0 = one per SM (default)
  *   "batch"     pairs per internal batch, 0 = default */
 int b200m_set_option(const char* name, int64_t value);
