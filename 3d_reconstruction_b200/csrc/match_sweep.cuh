@@ -139,6 +139,60 @@ __device__ __forceinline__ int max8(const int* v) {
   return max(m, v[7]);
 }
 
+// Per-row epilogue state. Scores are  |col|^2 - 2 row.col  (the row's own norm is added at the end).
+struct RowState {
+  int s1, i1, s2, i2;   // kTop2: running best / second best (score, column)
+  int thr, my_q, viol;  // kThresh: score to beat, the survivor's own query row, result flag
+};
+
+// One 32-column chunk of one row. v = raw int32 dot products, nb = the columns' squared norms,
+// nbm = min(nb) over the chunk, nbase = index of the chunk's first column.
+template <int kKind>
+__device__ __forceinline__ void process_chunk(const int (&v)[32], const int32_t* nb, int nbm, int nbase,
+                                              RowState& st) {
+  if (kKind == kTop2Exact) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+      const int s = nb[j] - 2 * v[j];
+      if (s < st.s2) top2_insert(s, nbase + j, st.s1, st.i1, st.s2, st.i2);
+    }
+  } else if (kKind == kTop2) {
+    // s < s2  <=>  2*acc > nb - s2  <=>  acc > floor((nb - s2) / 2).  A group of columns can only
+    // change the row's top-2 if max(acc) > floor((min(nb) - s2) / 2): one 3-input max per two
+    // accumulator values, one compare per 8 columns, exact insertion only for groups that pass.
+    const int g0 = max8(v), g1 = max8(v + 8), g2 = max8(v + 16), g3 = max8(v + 24);
+    const int mx = max(__vimax3_s32(g0, g1, g2), g3);
+    int T = (nbm - st.s2) >> 1;
+    if (mx > T) {
+#pragma unroll
+      for (int g = 0; g < 4; ++g) {
+        const int gm = g == 0 ? g0 : (g == 1 ? g1 : (g == 2 ? g2 : g3));
+        if (gm > T) {
+#pragma unroll
+          for (int j = 8 * g; j < 8 * g + 8; ++j) {
+            const int s = nb[j] - 2 * v[j];
+            if (s < st.s2) top2_insert(s, nbase + j, st.s1, st.i1, st.s2, st.i2);
+          }
+          T = (nbm - st.s2) >> 1;
+        }
+      }
+    }
+  } else if (kKind == kThresh) {
+    // violated  <=>  exists column with s < thr, or s == thr and column index < my_q
+    //           =>   2*acc >= nb - thr  =>  acc > floor((min(nb) - thr - 1) / 2)
+    const int g0 = max8(v), g1 = max8(v + 8), g2 = max8(v + 16), g3 = max8(v + 24);
+    const int mx = max(__vimax3_s32(g0, g1, g2), g3);
+    const int T = (nbm - st.thr - 1) >> 1;
+    if (mx > T) {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        const int s = nb[j] - 2 * v[j];
+        if (s < st.thr || (s == st.thr && nbase + j < st.my_q)) st.viol = 1;
+      }
+    }
+  }
+}
+
 template <int kKind>
 __global__ void __launch_bounds__(kThreads, 1)
 sweep_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
@@ -244,17 +298,12 @@ sweep_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
       const bool active = m < it.nm;
       const int64_t orow = static_cast<int64_t>(it.pair) * p.k_stride + it.blk * kRows + rl;
 
-      // per-row state. scores are  |col|^2 - 2 row.col  (the row's own norm is added at the end)
-      int s1 = kBig, i1 = -1, s2 = kBig, i2 = -1;
-      int thr = kBig;          // kThresh: the score to beat;  my_q: the survivor's own query row
-      int my_q = 0;
-      int viol = 0;
-      if (kKind == kThresh) {
-        thr = -kBig;           // padding rows of the block can never be violated
-        if (active && rl < it.n_rows) {
-          thr = __ldg(p.surv_thr + orow);
-          my_q = __ldg(p.surv_q + orow);
-        }
+      RowState st;
+      st.s1 = kBig; st.i1 = -1; st.s2 = kBig; st.i2 = -1;
+      st.thr = -kBig; st.my_q = 0; st.viol = 0;      // padding rows of a kThresh block can never be violated
+      if (kKind == kThresh && active && rl < it.n_rows) {
+        st.thr = __ldg(p.surv_thr + orow);
+        st.my_q = __ldg(p.surv_q + orow);
       }
 
       for (int t = 0; t < it.ntiles; ++t) {
@@ -270,7 +319,7 @@ sweep_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&sm.t_empty[m]);
-            s1 = min(s1, v[0]);
+            st.s1 = min(st.s1, v[0]);
             ++t_it;
           }
           continue;
@@ -282,57 +331,26 @@ sweep_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
           tc_fence_after();
           const uint32_t taddr = tmem_base + ((quad * 32u) << 16) + m * kTT;
           const int col0 = t * kTT;
+          // Software-pipelined drain: the tcgen05.ld of the next 32 columns is in flight while the
+          // current 32 are processed (two register buffers, loop unrolled by two).
+          int va[32], vb[32];
+          tmem_ld_32x32(taddr, va);
+          tmem_ld_fence(va);
 #pragma unroll 1
-          for (int c = 0; c < 8; ++c) {
-            int v[32];
-            tmem_ld_32x32(taddr + c * 32, v);
-            tmem_ld_wait();
-            if (c == 7) {
+          for (int c = 0; c < 8; c += 2) {
+            tmem_ld_32x32(taddr + (c + 1) * 32, vb);
+            process_chunk<kKind>(va, nsl.nb + c * 32, nsl.nbmin[c], col0 + c * 32, st);
+            tmem_ld_fence(vb);
+            if (c + 2 < 8) {
+              tmem_ld_32x32(taddr + (c + 2) * 32, va);
+            } else {
               // accumulator fully drained into registers: hand it back to the MMA warp
               tc_fence_before();
               __syncwarp();
               if (lane == 0) mbar_arrive(&sm.t_empty[m]);
             }
-            const int nbase = col0 + c * 32;
-            const int32_t* nb = nsl.nb + c * 32;
-            if (kKind == kTop2Exact) {
-#pragma unroll
-              for (int j = 0; j < 32; ++j) {
-                const int s = nb[j] - 2 * v[j];
-                if (s < s2) top2_insert(s, nbase + j, s1, i1, s2, i2);
-              }
-            } else if (kKind == kTop2) {
-              // s < s2  <=>  2*acc + s2 > nb.  A group of columns can only change the row's top-2 if
-              // 2*max(acc) + s2 > min(nb); one 3-input max per two accumulator values.
-              const int g0 = max8(v), g1 = max8(v + 8), g2 = max8(v + 16), g3 = max8(v + 24);
-              const int mx = max(__vimax3_s32(g0, g1, g2), g3);
-              const int nbm = nsl.nbmin[c];
-              if (2 * mx + s2 > nbm) {
-#pragma unroll
-                for (int g = 0; g < 4; ++g) {
-                  const int gm = g == 0 ? g0 : (g == 1 ? g1 : (g == 2 ? g2 : g3));
-                  if (2 * gm + s2 > nbm) {
-#pragma unroll
-                    for (int j = 8 * g; j < 8 * g + 8; ++j) {
-                      const int s = nb[j] - 2 * v[j];
-                      if (s < s2) top2_insert(s, nbase + j, s1, i1, s2, i2);
-                    }
-                  }
-                }
-              }
-            } else {   // kThresh
-              // violated  <=>  exists column with s < thr, or s == thr and column index < my_q
-              const int g0 = max8(v), g1 = max8(v + 8), g2 = max8(v + 16), g3 = max8(v + 24);
-              const int mx = max(__vimax3_s32(g0, g1, g2), g3);
-              const int nbm = nsl.nbmin[c];
-              if (2 * mx + thr >= nbm) {
-#pragma unroll
-                for (int j = 0; j < 32; ++j) {
-                  const int s = nb[j] - 2 * v[j];
-                  if (s < thr || (s == thr && nbase + j < my_q)) viol = 1;
-                }
-              }
-            }
+            process_chunk<kKind>(vb, nsl.nb + (c + 1) * 32, nsl.nbmin[c + 1], col0 + (c + 1) * 32, st);
+            if (c + 2 < 8) tmem_ld_fence(va);
           }
           ++t_it;
         }
@@ -342,10 +360,10 @@ sweep_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
 
       if (active && rl < it.n_rows) {
         if (kKind == kThresh) {
-          p.surv_viol[orow] = viol;
+          p.surv_viol[orow] = st.viol;
         } else {
           const int na = __ldg(p.sqnorm + it.row_img_row0 + rl);
-          p.rowres[orow] = make_int4(s1 + na, i1, s2 + na, i2);
+          p.rowres[orow] = make_int4(st.s1 + na, st.i1, st.s2 + na, st.i2);
         }
       }
     }
