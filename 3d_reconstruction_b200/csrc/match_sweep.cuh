@@ -9,20 +9,22 @@
 // in the exact-integer L2 form BASELINE.json names (cv2.BFMatcher NORM_L2 knnMatch k=2 + crossCheck).
 //
 // One CTA = one SM, persistent over work items. An item keeps a block of 256 "row" descriptors
-// (two UMMA M-tiles of 128) resident in shared memory and sweeps a "column" image in tiles of 256:
-//   warp 0      TMA producer   (row block per item; column tiles + their norms through rings)
-//   warp 1      MMA issuer     (per column tile: 2 x 4 tcgen05.mma.kind::i8 M128 N256 K32)
-//   warp 2      TMEM allocator
-//   warps 4-7   epilogue group 0 (M-tile 0, accumulator 0: TMEM columns 0..255)
-//   warps 8-11  epilogue group 1 (M-tile 1, accumulator 1: TMEM columns 256..511)
-// The two accumulators alternate, so the MMA of one M-tile overlaps the epilogue of the other, and
-// every column tile fetched from L2 is used for 256 rows. Each epilogue thread owns one row for the
-// whole sweep (tcgen05.ld 32x32b: lane == row), so row reductions never leave its registers.
+// (two UMMA M-tiles of 128) resident in shared memory and sweeps a "column" image in tiles of 256
+// columns, each tile issued as two N=128 halves:
+//   warp 0       TMA producer  (row block per item; column tiles + their norms through rings)
+//   warp 1       MMA issuer    (per column tile: 4 accumulators x 4 tcgen05.mma.kind::i8 M128 N128 K32)
+//   warp 2       TMEM allocator
+//   warps 4-19   epilogue: 4 warps (one per TMEM lane quadrant) for each accumulator (m, h),
+//                m = M-tile, h = column half. TMEM columns of (m, h): m*256 + h*128 .. +127.
+// With four 128 x 128 int32 accumulators (all 512 TMEM columns) the MMA of one column half overlaps
+// the epilogue of the other half of the same rows, and every column tile fetched from L2 serves
+// 256 rows. Each epilogue thread owns one row (tcgen05.ld 32x32b: lane == row) and half of the
+// columns for the whole sweep; the two halves of a row meet once per item through shared memory.
 //
 // Two passes share the kernel (kKind):
 //   kTop2    rows = query descriptors of a pair, columns = train descriptors: exact top-2 per row.
 //            A threshold-reject epilogue does one 3-input integer max per two accumulator values and
-//            runs the exact insertion only for 8-column groups that can change the row's top-2.
+//            runs the exact insertion only for 4-column groups that can change the row's top-2.
 //   kThresh  the mutual (cross) check, done lazily: rows = train descriptors of the ratio-test
 //            survivors (gathered), columns = all query descriptors; a row is violated when some
 //            query is strictly nearer (or equally near with a lower index) than its own.
@@ -35,17 +37,19 @@ namespace b200m {
 constexpr int kD = 128;             // descriptor bytes
 constexpr int kTM = 128;            // rows per UMMA M-tile
 constexpr int kRows = 256;          // rows per work item (two M-tiles)
-constexpr int kTT = 256;            // columns per tile (UMMA N)
+constexpr int kTT = 256;            // columns per tile
+constexpr int kTN = 128;            // columns per MMA / accumulator (UMMA N)
 constexpr int kMBytes = kTM * kD;   // 16 KiB per M-tile
 constexpr int kBBytes = kTT * kD;   // 32 KiB per column tile
 constexpr int kAStages = 2;
 constexpr int kBStages = 4;
 constexpr int kNStages = 4;         // norms ring
-constexpr int kEpiWarps = 8;
+constexpr int kEpiWarps = 16;
 constexpr int kFirstEpiWarp = 4;
-constexpr int kThreads = (kFirstEpiWarp + kEpiWarps) * 32;  // 384
+constexpr int kThreads = (kFirstEpiWarp + kEpiWarps) * 32;  // 640
 constexpr int kPadNorm = 1 << 23;   // > 128*255^2: norm of a padding row
 constexpr int kBig = 1 << 28;       // "no candidate yet" score; 2*acc + kBig cannot overflow
+constexpr uint32_t kEpiBarrier = 1; // named barrier of the 16 epilogue warps
 
 enum SweepKind { kTop2 = 0, kThresh = 1, kPeak = 2, kTop2Exact = 3 };
 
@@ -59,10 +63,11 @@ struct SweepSmem {
   uint8_t a[kAStages][2][kMBytes];
   uint8_t b[kBStages][kBBytes];
   NormSlot norms[kNStages];
+  int4 rowmerge[2][kRows];          // column half 1 hands its row state to column half 0
   uint64_t a_full[kAStages], a_empty[kAStages];
   uint64_t b_full[kBStages], b_empty[kBStages];
   uint64_t n_full[kNStages], n_empty[kNStages];
-  uint64_t t_full[2], t_empty[2];
+  uint64_t t_full[4], t_empty[4];   // accumulator (m, h) -> index m * 2 + h
   uint32_t tmem_base;
 };
 
@@ -121,9 +126,9 @@ __device__ __forceinline__ ItemInfo decode_item(const SweepParams& p, int item) 
   return it;
 }
 
-// Exact insertion of (s, n) into a row's running top-2. Within a thread n is strictly increasing,
-// so strict '<' keeps the lowest index on ties and a duplicate of the best becomes the second best
-// (the stable-argsort rule cv2.BFMatcher follows).
+// Exact insertion of (s, n), s < s2, into a row's running top-2. Within a thread n is strictly
+// increasing, so strict '<' keeps the lowest index on ties and a duplicate of the best becomes the
+// second best (the stable-argsort rule cv2.BFMatcher follows).
 __device__ __forceinline__ void top2_insert(int s, int n, int& s1, int& i1, int& s2, int& i2) {
   const bool lt1 = s < s1;
   s2 = lt1 ? s1 : s;
@@ -132,12 +137,11 @@ __device__ __forceinline__ void top2_insert(int s, int n, int& s1, int& i1, int&
   i1 = lt1 ? n : i1;
 }
 
-__device__ __forceinline__ int max8(const int* v) {
-  int m = __vimax3_s32(v[0], v[1], v[2]);
-  m = __vimax3_s32(m, v[3], v[4]);
-  m = __vimax3_s32(m, v[5], v[6]);
-  return max(m, v[7]);
+__device__ __forceinline__ bool lex_less(int sa, int ia, int sb, int ib) {
+  return sa < sb || (sa == sb && ia < ib);
 }
+
+__device__ __forceinline__ int max4(const int* v) { return max(__vimax3_s32(v[0], v[1], v[2]), v[3]); }
 
 // Per-row epilogue state. Scores are  |col|^2 - 2 row.col  (the row's own norm is added at the end).
 struct RowState {
@@ -159,20 +163,24 @@ __device__ __forceinline__ void process_chunk(const int (&v)[32], const int32_t*
   } else if (kKind == kTop2) {
     // s < s2  <=>  2*acc > nb - s2  <=>  acc > floor((nb - s2) / 2).  A group of columns can only
     // change the row's top-2 if max(acc) > floor((min(nb) - s2) / 2): one 3-input max per two
-    // accumulator values, one compare per 8 columns, exact insertion only for groups that pass.
-    const int g0 = max8(v), g1 = max8(v + 8), g2 = max8(v + 16), g3 = max8(v + 24);
-    const int mx = max(__vimax3_s32(g0, g1, g2), g3);
+    // accumulator values, one compare per 4 columns of a chunk that passes, exact insertion only
+    // for the groups that pass.
+    int g[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) g[k] = max4(v + 4 * k);
+    const int mx = max(__vimax3_s32(__vimax3_s32(g[0], g[1], g[2]), g[3], g[4]), __vimax3_s32(g[5], g[6], g[7]));
     int T = (nbm - st.s2) >> 1;
     if (mx > T) {
 #pragma unroll
-      for (int g = 0; g < 4; ++g) {
-        const int gm = g == 0 ? g0 : (g == 1 ? g1 : (g == 2 ? g2 : g3));
-        if (gm > T) {
-#pragma unroll
-          for (int j = 8 * g; j < 8 * g + 8; ++j) {
-            const int s = nb[j] - 2 * v[j];
-            if (s < st.s2) top2_insert(s, nbase + j, st.s1, st.i1, st.s2, st.i2);
-          }
+      for (int k = 0; k < 8; ++k) {
+        if (g[k] > T) {
+          const int4 nb4 = *reinterpret_cast<const int4*>(nb + 4 * k);
+          const int sa = nb4.x - 2 * v[4 * k], sb = nb4.y - 2 * v[4 * k + 1];
+          const int sc = nb4.z - 2 * v[4 * k + 2], sd = nb4.w - 2 * v[4 * k + 3];
+          if (sa < st.s2) top2_insert(sa, nbase + 4 * k, st.s1, st.i1, st.s2, st.i2);
+          if (sb < st.s2) top2_insert(sb, nbase + 4 * k + 1, st.s1, st.i1, st.s2, st.i2);
+          if (sc < st.s2) top2_insert(sc, nbase + 4 * k + 2, st.s1, st.i1, st.s2, st.i2);
+          if (sd < st.s2) top2_insert(sd, nbase + 4 * k + 3, st.s1, st.i1, st.s2, st.i2);
           T = (nbm - st.s2) >> 1;
         }
       }
@@ -180,8 +188,10 @@ __device__ __forceinline__ void process_chunk(const int (&v)[32], const int32_t*
   } else if (kKind == kThresh) {
     // violated  <=>  exists column with s < thr, or s == thr and column index < my_q
     //           =>   2*acc >= nb - thr  =>  acc > floor((min(nb) - thr - 1) / 2)
-    const int g0 = max8(v), g1 = max8(v + 8), g2 = max8(v + 16), g3 = max8(v + 24);
-    const int mx = max(__vimax3_s32(g0, g1, g2), g3);
+    int g[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) g[k] = max4(v + 4 * k);
+    const int mx = max(__vimax3_s32(__vimax3_s32(g[0], g[1], g[2]), g[3], g[4]), __vimax3_s32(g[5], g[6], g[7]));
     const int T = (nbm - st.thr - 1) >> 1;
     if (mx > T) {
 #pragma unroll
@@ -210,7 +220,7 @@ sweep_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
     for (int i = 0; i < kAStages; ++i) { mbar_init(&sm.a_full[i], 1); mbar_init(&sm.a_empty[i], 1); }
     for (int i = 0; i < kBStages; ++i) { mbar_init(&sm.b_full[i], 1); mbar_init(&sm.b_empty[i], 1); }
     for (int i = 0; i < kNStages; ++i) { mbar_init(&sm.n_full[i], 1); mbar_init(&sm.n_empty[i], kEpiWarps); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&sm.t_full[i], 1); mbar_init(&sm.t_empty[i], kEpiWarps / 2); }
+    for (int i = 0; i < 4; ++i) { mbar_init(&sm.t_full[i], 1); mbar_init(&sm.t_empty[i], 4); }
     fence_mbar_init();
   }
   if (warp == 2) tmem_alloc<512>(&sm.tmem_base);
@@ -254,8 +264,8 @@ sweep_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
   } else if (warp == 1) {
     // ------------------------------------------------------------- MMA issuer
     if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc_u8(kTM, kTT);
-      uint32_t a_it = 0, b_it = 0, t_it[2] = {0, 0};
+      constexpr uint32_t idesc = make_idesc_u8(kTM, kTN);
+      uint32_t a_it = 0, b_it = 0, t_it[4] = {0, 0, 0, 0};
       for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
         const ItemInfo it = decode_item<kKind>(p, item);
         if (!it.valid) continue;
@@ -264,19 +274,23 @@ sweep_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
         for (int t = 0; t < it.ntiles; ++t) {
           const uint32_t bs = b_it % kBStages, bph = (b_it / kBStages) & 1;
           mbar_wait(&sm.b_full[bs], bph);
-          const uint64_t bdesc = make_desc_k128(smem_u32(sm.b[bs]));
-          for (int m = 0; m < it.nm; ++m) {
-            mbar_wait(&sm.t_empty[m], (t_it[m] & 1) ^ 1);
-            tc_fence_after();
-            const uint64_t adesc = make_desc_k128(smem_u32(sm.a[as][m]));
-            const uint32_t tacc = tmem_base + m * kTT;
 #pragma unroll
-            for (int k = 0; k < kD / 32; ++k) {
-              // +32 B along K inside the 128 B swizzle atom = +2 in the (addr >> 4) field
-              mma_i8_ss(tacc, adesc + 2 * k, bdesc + 2 * k, idesc, k > 0 ? 1u : 0u);
+          for (int h = 0; h < 2; ++h) {
+            const uint64_t bdesc = make_desc_k128(smem_u32(sm.b[bs] + h * (kBBytes / 2)));
+            for (int m = 0; m < it.nm; ++m) {
+              const int acc = m * 2 + h;
+              mbar_wait(&sm.t_empty[acc], (t_it[acc] & 1) ^ 1);
+              tc_fence_after();
+              const uint64_t adesc = make_desc_k128(smem_u32(sm.a[as][m]));
+              const uint32_t tacc = tmem_base + m * kTT + h * kTN;
+#pragma unroll
+              for (int k = 0; k < kD / 32; ++k) {
+                // +32 B along K inside the 128 B swizzle atom = +2 in the (addr >> 4) field
+                mma_i8_ss(tacc, adesc + 2 * k, bdesc + 2 * k, idesc, k > 0 ? 1u : 0u);
+              }
+              tc_commit(&sm.t_full[acc]);   // accumulator (m, h) ready for its epilogue warps
+              ++t_it[acc];
             }
-            tc_commit(&sm.t_full[m]);   // accumulator m ready for its epilogue group
-            ++t_it[m];
           }
           tc_commit(&sm.b_empty[bs]);   // smem stage free once these MMAs retire
           ++b_it;
@@ -287,11 +301,13 @@ sweep_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
     }
   } else if (warp >= kFirstEpiWarp) {
     // ------------------------------------------------------------- epilogue
-    const uint32_t ew = warp - kFirstEpiWarp;       // 0..7
+    const uint32_t ew = warp - kFirstEpiWarp;       // 0..15
     const uint32_t quad = warp & 3;                 // TMEM lane quadrant this warp may read
-    const int m = ew >> 2;                          // M-tile / accumulator of this group
+    const int m = ew >> 3;                          // M-tile
+    const int h = (ew >> 2) & 1;                    // column half
+    const int acc = m * 2 + h;
     const int rl = m * kTM + quad * 32 + lane;      // row inside the item's block
-    uint32_t t_it = 0, n_it = 0;
+    uint32_t t_it = 0, n_it = 0, item_it = 0;
     for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
       const ItemInfo it = decode_item<kKind>(p, item);
       if (!it.valid) continue;
@@ -311,14 +327,14 @@ sweep_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
         ++n_it;
         if (kKind == kPeak) {
           if (active) {
-            mbar_wait(&sm.t_full[m], t_it & 1);
+            mbar_wait(&sm.t_full[acc], t_it & 1);
             tc_fence_after();
             int v[32];
-            tmem_ld_32x32(tmem_base + ((quad * 32u) << 16) + m * kTT, v);
-            tmem_ld_wait();
+            tmem_ld_32x32(tmem_base + ((quad * 32u) << 16) + m * kTT + h * kTN, v);
+            tmem_ld_fence(v);
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(&sm.t_empty[m]);
+            if (lane == 0) mbar_arrive(&sm.t_empty[acc]);
             st.s1 = min(st.s1, v[0]);
             ++t_it;
           }
@@ -327,30 +343,22 @@ sweep_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
         mbar_wait(&sm.n_full[ns], nph);
         if (active) {
           const NormSlot& nsl = sm.norms[ns];
-          mbar_wait(&sm.t_full[m], t_it & 1);
+          mbar_wait(&sm.t_full[acc], t_it & 1);
           tc_fence_after();
-          const uint32_t taddr = tmem_base + ((quad * 32u) << 16) + m * kTT;
-          const int col0 = t * kTT;
-          // Software-pipelined drain: the tcgen05.ld of the next 32 columns is in flight while the
-          // current 32 are processed (two register buffers, loop unrolled by two).
-          int va[32], vb[32];
-          tmem_ld_32x32(taddr, va);
-          tmem_ld_fence(va);
+          const uint32_t taddr = tmem_base + ((quad * 32u) << 16) + m * kTT + h * kTN;
+          const int col0 = t * kTT + h * kTN;
 #pragma unroll 1
-          for (int c = 0; c < 8; c += 2) {
-            tmem_ld_32x32(taddr + (c + 1) * 32, vb);
-            process_chunk<kKind>(va, nsl.nb + c * 32, nsl.nbmin[c], col0 + c * 32, st);
-            tmem_ld_fence(vb);
-            if (c + 2 < 8) {
-              tmem_ld_32x32(taddr + (c + 2) * 32, va);
-            } else {
+          for (int c = 0; c < 4; ++c) {
+            int v[32];
+            tmem_ld_32x32(taddr + c * 32, v);
+            tmem_ld_fence(v);
+            if (c == 3) {
               // accumulator fully drained into registers: hand it back to the MMA warp
               tc_fence_before();
               __syncwarp();
-              if (lane == 0) mbar_arrive(&sm.t_empty[m]);
+              if (lane == 0) mbar_arrive(&sm.t_empty[acc]);
             }
-            process_chunk<kKind>(vb, nsl.nb + (c + 1) * 32, nsl.nbmin[c + 1], col0 + (c + 1) * 32, st);
-            if (c + 2 < 8) tmem_ld_fence(va);
+            process_chunk<kKind>(v, nsl.nb + h * kTN + c * 32, nsl.nbmin[h * 4 + c], col0 + c * 32, st);
           }
           ++t_it;
         }
@@ -358,12 +366,29 @@ sweep_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
         if (lane == 0) mbar_arrive(&sm.n_empty[ns]);
       }
 
-      if (active && rl < it.n_rows) {
+      // the two column halves of a row meet here: half 1 -> smem -> half 0 -> global
+      const uint32_t par = item_it & 1;
+      ++item_it;
+      if (h == 1 && active)
+        sm.rowmerge[par][rl] = kKind == kThresh ? make_int4(st.viol, 0, 0, 0) : make_int4(st.s1, st.i1, st.s2, st.i2);
+      named_bar_sync(kEpiBarrier, kEpiWarps * 32);
+      if (h == 0 && active && rl < it.n_rows) {
+        const int4 o = sm.rowmerge[par][rl];
         if (kKind == kThresh) {
-          p.surv_viol[orow] = st.viol;
+          p.surv_viol[orow] = st.viol | o.x;
         } else {
+          // merge two sorted (score, column) pairs; columns of the halves interleave tile by tile,
+          // so ties are resolved on the column index explicitly
+          int r1s, r1i, r2s, r2i;
+          if (lex_less(o.x, o.y, st.s1, st.i1)) {
+            r1s = o.x; r1i = o.y;
+            if (lex_less(o.z, o.w, st.s1, st.i1)) { r2s = o.z; r2i = o.w; } else { r2s = st.s1; r2i = st.i1; }
+          } else {
+            r1s = st.s1; r1i = st.i1;
+            if (lex_less(o.x, o.y, st.s2, st.i2)) { r2s = o.x; r2i = o.y; } else { r2s = st.s2; r2i = st.i2; }
+          }
           const int na = __ldg(p.sqnorm + it.row_img_row0 + rl);
-          p.rowres[orow] = make_int4(st.s1 + na, st.i1, st.s2 + na, st.i2);
+          p.rowres[orow] = make_int4(r1s + na, r1i, r2s + na, r2i);
         }
       }
     }
