@@ -64,6 +64,7 @@ struct SweepSmem {
   uint8_t b[kBStages][kBBytes];
   NormSlot norms[kNStages];
   int4 rowmerge[2][kRows];          // column half 1 hands its row state to column half 0
+  int2 share[2][2][kRows];          // [item parity][h][row]: running (s1, s2) published to the other half
   uint64_t a_full[kAStages], a_empty[kAStages];
   uint64_t b_full[kBStages], b_empty[kBStages];
   uint64_t n_full[kNStages], n_empty[kNStages];
@@ -146,6 +147,8 @@ __device__ __forceinline__ int max4(const int* v) { return max(__vimax3_s32(v[0]
 // Per-row epilogue state. Scores are  |col|^2 - 2 row.col  (the row's own norm is added at the end).
 struct RowState {
   int s1, i1, s2, i2;   // kTop2: running best / second best (score, column)
+  int lim;              // kTop2: insert only scores < lim = min(s2, bound from the other column half + 1)
+  int2* pub;            // kTop2: where this thread publishes (s1, s2) for the other half
   int thr, my_q, viol;  // kThresh: score to beat, the survivor's own query row, result flag
 };
 
@@ -169,21 +172,24 @@ __device__ __forceinline__ void process_chunk(const int (&v)[32], const int32_t*
 #pragma unroll
     for (int k = 0; k < 8; ++k) g[k] = max4(v + 4 * k);
     const int mx = max(__vimax3_s32(__vimax3_s32(g[0], g[1], g[2]), g[3], g[4]), __vimax3_s32(g[5], g[6], g[7]));
-    int T = (nbm - st.s2) >> 1;
+    int T = (nbm - st.lim) >> 1;
     if (mx > T) {
+      const int lim_p = st.lim;
 #pragma unroll
       for (int k = 0; k < 8; ++k) {
         if (g[k] > T) {
           const int4 nb4 = *reinterpret_cast<const int4*>(nb + 4 * k);
           const int sa = nb4.x - 2 * v[4 * k], sb = nb4.y - 2 * v[4 * k + 1];
           const int sc = nb4.z - 2 * v[4 * k + 2], sd = nb4.w - 2 * v[4 * k + 3];
-          if (sa < st.s2) top2_insert(sa, nbase + 4 * k, st.s1, st.i1, st.s2, st.i2);
-          if (sb < st.s2) top2_insert(sb, nbase + 4 * k + 1, st.s1, st.i1, st.s2, st.i2);
-          if (sc < st.s2) top2_insert(sc, nbase + 4 * k + 2, st.s1, st.i1, st.s2, st.i2);
-          if (sd < st.s2) top2_insert(sd, nbase + 4 * k + 3, st.s1, st.i1, st.s2, st.i2);
-          T = (nbm - st.s2) >> 1;
+          // lim <= s2 always, so s < lim implies the insertion precondition s < s2
+          if (sa < st.lim) { top2_insert(sa, nbase + 4 * k, st.s1, st.i1, st.s2, st.i2); st.lim = min(st.lim, st.s2); }
+          if (sb < st.lim) { top2_insert(sb, nbase + 4 * k + 1, st.s1, st.i1, st.s2, st.i2); st.lim = min(st.lim, st.s2); }
+          if (sc < st.lim) { top2_insert(sc, nbase + 4 * k + 2, st.s1, st.i1, st.s2, st.i2); st.lim = min(st.lim, st.s2); }
+          if (sd < st.lim) { top2_insert(sd, nbase + 4 * k + 3, st.s1, st.i1, st.s2, st.i2); st.lim = min(st.lim, st.s2); }
+          T = (nbm - st.lim) >> 1;
         }
       }
+      if (st.lim != lim_p) *st.pub = make_int2(st.s1, st.s2);
     }
   } else if (kKind == kThresh) {
     // violated  <=>  exists column with s < thr, or s == thr and column index < my_q
@@ -224,6 +230,11 @@ sweep_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
     fence_mbar_init();
   }
   if (warp == 2) tmem_alloc<512>(&sm.tmem_base);
+  if (warp >= kFirstEpiWarp) {
+    const int t = threadIdx.x - kFirstEpiWarp * 32;          // 0..511 -> one (h, row) slot each
+    sm.share[0][t >> 8][t & 255] = make_int2(kBig, kBig);
+    sm.share[1][t >> 8][t & 255] = make_int2(kBig, kBig);
+  }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -315,7 +326,11 @@ sweep_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
       const int64_t orow = static_cast<int64_t>(it.pair) * p.k_stride + it.blk * kRows + rl;
 
       RowState st;
-      st.s1 = kBig; st.i1 = -1; st.s2 = kBig; st.i2 = -1;
+      st.s1 = kBig; st.i1 = -1; st.s2 = kBig; st.i2 = -1; st.lim = kBig;
+      const uint32_t par = item_it & 1;
+      ++item_it;
+      st.pub = &sm.share[par][h][rl];
+      const int2* partner = &sm.share[par][h ^ 1][rl];
       st.thr = -kBig; st.my_q = 0; st.viol = 0;      // padding rows of a kThresh block can never be violated
       if (kKind == kThresh && active && rl < it.n_rows) {
         st.thr = __ldg(p.surv_thr + orow);
@@ -343,6 +358,14 @@ sweep_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
         mbar_wait(&sm.n_full[ns], nph);
         if (active) {
           const NormSlot& nsl = sm.norms[ns];
+          if (kKind == kTop2) {
+            // The union of both halves has a second best <= min(max(s1, s1'), s2'): anything at or
+            // above it (strictly above on ties, the halves interleave in column order) cannot be in
+            // the row's final top-2. Racy reads are fine: published values only ever decrease.
+            const long long raw = *reinterpret_cast<const volatile long long*>(partner);
+            const int ox = static_cast<int>(raw), oy = static_cast<int>(raw >> 32);
+            st.lim = min(st.lim, min(max(st.s1, ox), oy) + 1);
+          }
           mbar_wait(&sm.t_full[acc], t_it & 1);
           tc_fence_after();
           const uint32_t taddr = tmem_base + ((quad * 32u) << 16) + m * kTT + h * kTN;
@@ -367,10 +390,9 @@ sweep_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
       }
 
       // the two column halves of a row meet here: half 1 -> smem -> half 0 -> global
-      const uint32_t par = item_it & 1;
-      ++item_it;
       if (h == 1 && active)
         sm.rowmerge[par][rl] = kKind == kThresh ? make_int4(st.viol, 0, 0, 0) : make_int4(st.s1, st.i1, st.s2, st.i2);
+      sm.share[par ^ 1][h][rl] = make_int2(kBig, kBig);     // next item's slot; nobody reads it before the barrier
       named_bar_sync(kEpiBarrier, kEpiWarps * 32);
       if (h == 0 && active && rl < it.n_rows) {
         const int4 o = sm.rowmerge[par][rl];

@@ -46,30 +46,30 @@ __device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t by
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
                : "memory");
 }
+// try_wait with a suspend-time hint: the warp sleeps in hardware until the phase completes or the
+// hint (ns) elapses, so a waiting warp does not burn issue slots of its SM sub-partition.
 __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
   uint32_t ok;
   asm volatile(
       "{\n\t"
       ".reg .pred p;\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
       "selp.u32 %0, 1, 0, p;\n\t"
       "}\n"
       : "=r"(ok)
-      : "r"(smem_u32(bar)), "r"(parity)
+      : "r"(smem_u32(bar)), "r"(parity), "r"(200000u)
       : "memory");
   return ok != 0;
 }
 
 // Bounded wait: a pipeline bug must surface as a CUDA error, never as a hung GPU box.
-// ~4 s at 2 GHz; try_wait itself suspends the warp for a HW-defined slice, so the loop is cheap.
-#ifndef B200M_WAIT_LIMIT_CYCLES
-#define B200M_WAIT_LIMIT_CYCLES (8000000000ll)
+#ifndef B200M_WAIT_LIMIT_POLLS
+#define B200M_WAIT_LIMIT_POLLS (1u << 22)
 #endif
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-  if (mbar_try_wait(bar, parity)) return;
-  const long long t0 = clock64();
+  uint32_t polls = 0;
   while (!mbar_try_wait(bar, parity)) {
-    if (clock64() - t0 > B200M_WAIT_LIMIT_CYCLES) {
+    if (++polls > B200M_WAIT_LIMIT_POLLS) {
       printf("b200m: mbarrier wait timeout block %d thread %d bar@%u parity %u\n", (int)blockIdx.x,
              (int)threadIdx.x, smem_u32(bar), parity);
       __trap();
