@@ -18,6 +18,7 @@ struct Options {
   int64_t epilogue = 1;
   int64_t grid = 0;
   int64_t batch = 0;
+  int64_t pipeline = 1;   // 1 = top-1 sweep + ratio/mutual verify sweeps, 0 = top-2 sweep + mutual verify
 } g_opt;
 
 int fail(int code, const char* fmt, const char* detail = "") {
@@ -98,20 +99,20 @@ DeviceInfo& device_info() {
 constexpr size_t kSweepSmemBytes = sizeof(b200m::SweepSmem) + 1024;
 
 template <int kKind>
-int launch_sweep(const CUtensorMap& tmap_a, const CUtensorMap& tmap_b, const b200m::SweepParams& sp, int grid,
-                 cudaStream_t st) {
+int launch_sweep(const CUtensorMap& tmap_a, const CUtensorMap& tmap_a2, const CUtensorMap& tmap_b,
+                 const b200m::SweepParams& sp, int grid, cudaStream_t st) {
   static thread_local bool attr_set = false;
   if (!attr_set) {
     CUDA_TRY(cudaFuncSetAttribute(b200m::sweep_kernel<kKind>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   static_cast<int>(kSweepSmemBytes)));
     attr_set = true;
   }
-  b200m::sweep_kernel<kKind><<<grid, b200m::kThreads, kSweepSmemBytes, st>>>(tmap_a, tmap_b, sp);
+  b200m::sweep_kernel<kKind><<<grid, b200m::kThreads, kSweepSmemBytes, st>>>(tmap_a, tmap_a2, tmap_b, sp);
   CUDA_TRY(cudaGetLastError());
   return B200M_OK;
 }
 
-constexpr int64_t kDefaultBatchRows = int64_t(1) << 23;   // pairs * k_stride per internal batch
+constexpr int64_t kDefaultBatchRows = int64_t(1) << 22;   // pairs * k_stride per internal batch
 
 int64_t batch_pairs(int64_t k_stride, int64_t n_pairs) {
   int64_t b = g_opt.batch > 0 ? g_opt.batch : (kDefaultBatchRows / (k_stride > 0 ? k_stride : 1));
@@ -123,14 +124,17 @@ int64_t batch_pairs(int64_t k_stride, int64_t n_pairs) {
 
 // Workspace carved per batch of B pairs (R = B * k_stride rows):
 struct Workspace {
-  int4* rowres;          // R
-  int32_t* surv_q;       // R
-  int32_t* surv_t;       // R
-  float* surv_d;         // R
-  int32_t* surv_thr;     // R
-  int32_t* surv_viol;    // R
-  int32_t* surv_count;   // B (padded to 64)
-  uint8_t* gathered;     // R * 128
+  int4* rowres;             // R
+  int32_t* cand_q;          // R
+  int32_t* cand_t;          // R
+  float* cand_d;            // R
+  int32_t* cand_thr_ratio;  // R
+  int32_t* cand_thr_mut;    // R
+  int32_t* viol_ratio;      // R
+  int32_t* viol_mut;        // R
+  int32_t* cand_count;      // B (padded to 64)
+  uint8_t* gath_q;          // R * 128
+  uint8_t* gath_t;          // R * 128
 };
 
 size_t carve(Workspace* w, void* base, int64_t B, int64_t k_stride) {
@@ -140,17 +144,22 @@ size_t carve(Workspace* w, void* base, int64_t B, int64_t k_stride) {
   auto take = [&](size_t bytes) { uintptr_t r = p; p += (bytes + 255) & ~size_t(255); return r; };
   uintptr_t a = take(sizeof(int4) * R);
   uintptr_t b = take(4 * R), c = take(4 * R), d = take(4 * R), e = take(4 * R), f = take(4 * R);
+  uintptr_t f2 = take(4 * R), f3 = take(4 * R);
   uintptr_t g = take(4 * (B + 64));
   uintptr_t h = take(static_cast<size_t>(128) * R);
+  uintptr_t h2 = take(static_cast<size_t>(128) * R);
   if (w) {
     w->rowres = reinterpret_cast<int4*>(a);
-    w->surv_q = reinterpret_cast<int32_t*>(b);
-    w->surv_t = reinterpret_cast<int32_t*>(c);
-    w->surv_d = reinterpret_cast<float*>(d);
-    w->surv_thr = reinterpret_cast<int32_t*>(e);
-    w->surv_viol = reinterpret_cast<int32_t*>(f);
-    w->surv_count = reinterpret_cast<int32_t*>(g);
-    w->gathered = reinterpret_cast<uint8_t*>(h);
+    w->cand_q = reinterpret_cast<int32_t*>(b);
+    w->cand_t = reinterpret_cast<int32_t*>(c);
+    w->cand_d = reinterpret_cast<float*>(d);
+    w->cand_thr_ratio = reinterpret_cast<int32_t*>(e);
+    w->cand_thr_mut = reinterpret_cast<int32_t*>(f);
+    w->viol_ratio = reinterpret_cast<int32_t*>(f2);
+    w->viol_mut = reinterpret_cast<int32_t*>(f3);
+    w->cand_count = reinterpret_cast<int32_t*>(g);
+    w->gath_q = reinterpret_cast<uint8_t*>(h);
+    w->gath_t = reinterpret_cast<uint8_t*>(h2);
   }
   return (p - p0) + 256;
 }
@@ -184,20 +193,28 @@ b200m::SweepParams base_params(const int32_t* norm_table, int32_t n_img, const i
   sp.n_pairs = static_cast<int32_t>(nb);
   sp.blocks_per_pair = static_cast<int32_t>(k_stride / b200m::kRows);
   sp.rowres = w.rowres;
-  sp.surv_count = w.surv_count;
-  sp.surv_q = w.surv_q;
-  sp.surv_thr = w.surv_thr;
-  sp.surv_viol = w.surv_viol;
+  sp.cand_count = w.cand_count;
+  sp.cand_q = w.cand_q;
+  sp.cand_t = w.cand_t;
+  sp.cand_thr_ratio = w.cand_thr_ratio;
+  sp.cand_thr_mut = w.cand_thr_mut;
+  sp.viol_ratio = w.viol_ratio;
+  sp.viol_mut = w.viol_mut;
+  sp.do_ratio = 0;
+  sp.do_mutual = 0;
   return sp;
 }
 
-// First sweep: exact top-2 of every query row of every pair of the batch -> w.rowres
-int sweep_top2(const CUtensorMap& tmap_bank, const b200m::SweepParams& sp, cudaStream_t st) {
+// First sweep over every query row of every pair of the batch -> w.rowres.
+// exact2: the second neighbour must be exact (knnMatch output / top-2 pipeline).
+int sweep_rows(const CUtensorMap& tmap_bank, const b200m::SweepParams& sp, bool exact2, cudaStream_t st) {
   const int grid = sweep_grid(static_cast<int64_t>(sp.n_pairs) * sp.blocks_per_pair);
   switch (g_opt.epilogue) {
-    case 0: return launch_sweep<b200m::kTop2Exact>(tmap_bank, tmap_bank, sp, grid, st);
-    case 2: return launch_sweep<b200m::kPeak>(tmap_bank, tmap_bank, sp, grid, st);
-    default: return launch_sweep<b200m::kTop2>(tmap_bank, tmap_bank, sp, grid, st);
+    case 0: return launch_sweep<b200m::kTop2Exact>(tmap_bank, tmap_bank, tmap_bank, sp, grid, st);
+    case 2: return launch_sweep<b200m::kPeak>(tmap_bank, tmap_bank, tmap_bank, sp, grid, st);
+    default:
+      return exact2 ? launch_sweep<b200m::kTop2>(tmap_bank, tmap_bank, tmap_bank, sp, grid, st)
+                    : launch_sweep<b200m::kTop1>(tmap_bank, tmap_bank, tmap_bank, sp, grid, st);
   }
 }
 
@@ -223,6 +240,7 @@ int b200m_set_option(const char* name, int64_t value) {
   if (!strcmp(name, "epilogue")) { g_opt.epilogue = value; return B200M_OK; }
   if (!strcmp(name, "grid")) { g_opt.grid = value; return B200M_OK; }
   if (!strcmp(name, "batch")) { g_opt.batch = value; return B200M_OK; }
+  if (!strcmp(name, "pipeline")) { g_opt.pipeline = value; return B200M_OK; }
   return fail(B200M_E_BAD_ARG, "unknown option %s", name);
 }
 
@@ -231,6 +249,7 @@ int64_t b200m_get_option(const char* name) {
   if (!strcmp(name, "epilogue")) return g_opt.epilogue;
   if (!strcmp(name, "grid")) return g_opt.grid;
   if (!strcmp(name, "batch")) return g_opt.batch;
+  if (!strcmp(name, "pipeline")) return g_opt.pipeline;
   return -1;
 }
 
@@ -285,7 +304,7 @@ int b200m_knn2_u8(const uint8_t* bank, const int32_t* norm_table, const int32_t*
   for (int64_t p0 = 0; p0 < n_pairs; p0 += B) {
     const int64_t nb = (n_pairs - p0 < B) ? (n_pairs - p0) : B;
     const b200m::SweepParams sp = base_params(norm_table, n_img, k_per_image, k_stride, pairs + 2 * p0, nb, w);
-    rc = sweep_top2(tmap, sp, st);
+    rc = sweep_rows(tmap, sp, true, st);
     if (rc) return rc;
     dim3 grid(static_cast<unsigned>((k_stride + 255) / 256), static_cast<unsigned>(nb));
     b200m::knn2_finalize_kernel<<<grid, 256, 0, st>>>(w.rowres, pairs + 2 * p0, k_per_image, k_stride,
@@ -309,30 +328,38 @@ int b200m_match_pairs_u8(const uint8_t* bank, const int32_t* norm_table, const i
   const int64_t B = batch_pairs(k_stride, n_pairs);
   Workspace w;
   carve(&w, workspace, B, k_stride);
-  CUtensorMap tmap_bank, tmap_gath;
+  CUtensorMap tmap_bank, tmap_gq, tmap_gt;
   rc = make_row_tmap(&tmap_bank, bank, static_cast<uint64_t>(n_img) * k_stride);
   if (rc) return rc;
-  rc = make_row_tmap(&tmap_gath, w.gathered, static_cast<uint64_t>(B) * k_stride);
+  rc = make_row_tmap(&tmap_gq, w.gath_q, static_cast<uint64_t>(B) * k_stride);
   if (rc) return rc;
+  rc = make_row_tmap(&tmap_gt, w.gath_t, static_cast<uint64_t>(B) * k_stride);
+  if (rc) return rc;
+  // pipeline 1: top-1 sweep, the Lowe test is settled by a verify sweep over the candidates;
+  // pipeline 0 (and the debug epilogue): exact top-2 sweep, only the mutual check is verified.
+  const bool exact2 = g_opt.pipeline == 0 || g_opt.epilogue == 0;
+  const int do_ratio = (!exact2 && ratio > 0.0) ? 1 : 0;
+  const int do_mutual = mutual ? 1 : 0;
   for (int64_t p0 = 0; p0 < n_pairs; p0 += B) {
     const int64_t nb = (n_pairs - p0 < B) ? (n_pairs - p0) : B;
     const int32_t* pb = pairs + 2 * p0;
-    const b200m::SweepParams sp = base_params(norm_table, n_img, k_per_image, k_stride, pb, nb, w);
-    rc = sweep_top2(tmap_bank, sp, st);
+    b200m::SweepParams sp = base_params(norm_table, n_img, k_per_image, k_stride, pb, nb, w);
+    rc = sweep_rows(tmap_bank, sp, exact2, st);
     if (rc) return rc;
     b200m::select_kernel<1024><<<static_cast<unsigned>(nb), 1024, 0, st>>>(
-        w.rowres, pb, k_per_image, k_stride, ratio, bank, norm_table, mutual ? 1 : 0, w.surv_q, w.surv_t, w.surv_d,
-        w.surv_thr, w.surv_count, w.gathered);
+        w.rowres, pb, k_per_image, k_stride, ratio, exact2 ? 1 : 0, bank, norm_table, do_ratio, do_mutual, w.cand_q,
+        w.cand_t, w.cand_d, w.cand_thr_ratio, w.cand_thr_mut, w.cand_count, w.gath_q, w.gath_t);
     CUDA_TRY(cudaGetLastError());
-    if (mutual) {
-      // lazy cross-check: second sweep only over the survivors' train descriptors
-      const int grid = sweep_grid(nb * sp.blocks_per_pair);
-      rc = launch_sweep<b200m::kThresh>(tmap_gath, tmap_bank, sp, grid, st);
+    if (do_ratio || do_mutual) {
+      sp.do_ratio = do_ratio;
+      sp.do_mutual = do_mutual;
+      const int grid = sweep_grid(nb * sp.blocks_per_pair * 2);
+      rc = launch_sweep<b200m::kVerify>(tmap_gq, tmap_gt, tmap_bank, sp, grid, st);
       if (rc) return rc;
     }
     b200m::emit_kernel<1024><<<static_cast<unsigned>(nb), 1024, 0, st>>>(
-        w.surv_q, w.surv_t, w.surv_d, w.surv_viol, w.surv_count, k_stride, mutual ? 1 : 0, out_query_idx + p0 * cap,
-        out_train_idx + p0 * cap, out_dist + p0 * cap, out_count + p0, cap);
+        w.cand_q, w.cand_t, w.cand_d, w.viol_ratio, w.viol_mut, w.cand_count, k_stride, do_ratio, do_mutual,
+        out_query_idx + p0 * cap, out_train_idx + p0 * cap, out_dist + p0 * cap, out_count + p0, cap);
     CUDA_TRY(cudaGetLastError());
   }
   return B200M_OK;

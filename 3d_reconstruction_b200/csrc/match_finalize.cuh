@@ -96,29 +96,46 @@ __device__ __forceinline__ int block_compact_slot(bool keep, int* warp_sums, int
   return start + woff + prefix;
 }
 
-// Ratio test on the row results of the first sweep; survivors are compacted in ascending query
-// order into the workspace and (for the mutual check) their train descriptors are gathered so the
-// second sweep can stream them with plain TMA.
-//   keep q  <=>  has second neighbour and double(d1) < ratio * double(d2)      (ratio > 0)
+// Smallest squared distance D* at which a second neighbour no longer spoils the Lowe test of a row
+// whose best float32 distance is d1f:  D* = min { D : double(d1f) < ratio * double(sqrtf(D)) }.
+// The row passes  <=>  every other train row has d^2 >= D*  (sqrtf is monotone), which turns the
+// float-exact `m.distance < ratio * n.distance` into an integer threshold for the verify sweep.
+__device__ __forceinline__ int ratio_radius_sq(float d1f, double ratio) {
+  const double d1 = static_cast<double>(d1f);
+  double est = d1 / ratio;
+  est = est * est;
+  long long D = est > 33554432.0 ? 33554432ll : static_cast<long long>(est);
+  auto passes = [&](long long x) { return d1 < ratio * static_cast<double>(__fsqrt_rn(static_cast<float>(x))); };
+  while (D > 0 && passes(D - 1)) --D;
+  while (D < 33554432ll && !passes(D)) ++D;
+  return static_cast<int>(D);
+}
+
+// Candidate selection after the first sweep; candidates are compacted in ascending query order.
+//   exact2 != 0: rowres holds the exact second neighbour (kTop2 sweep): the Lowe test is decided here.
+//   exact2 == 0: rowres holds an upper bound (kTop1 sweep): rows that pass against the bound are a
+//                superset of the true survivors; the verify sweep decides with the exact radius.
 // The compare is done in double on the float32 distances: exactly Python's
-// `m.distance < 0.75 * n.distance` on cv2 DMatch objects.
+// `m.distance < 0.75 * n.distance` on cv2 DMatch objects. For the verify sweeps the candidates'
+// query / train descriptors are gathered so they can be streamed with plain TMA.
 template <int kBlock>
 __global__ void __launch_bounds__(kBlock)
 select_kernel(const int4* __restrict__ rowres, const int32_t* __restrict__ pairs,
-              const int32_t* __restrict__ k_per_image, int64_t k_stride, double ratio,
-              const uint8_t* __restrict__ bank, const int32_t* __restrict__ sqnorm, int do_gather,
-              int32_t* __restrict__ surv_q, int32_t* __restrict__ surv_t, float* __restrict__ surv_d,
-              int32_t* __restrict__ surv_thr, int32_t* __restrict__ surv_count,
-              uint8_t* __restrict__ gathered) {
+              const int32_t* __restrict__ k_per_image, int64_t k_stride, double ratio, int exact2,
+              const uint8_t* __restrict__ bank, const int32_t* __restrict__ sqnorm, int gather_q, int gather_t,
+              int32_t* __restrict__ cand_q, int32_t* __restrict__ cand_t, float* __restrict__ cand_d,
+              int32_t* __restrict__ cand_thr_ratio, int32_t* __restrict__ cand_thr_mut,
+              int32_t* __restrict__ cand_count, uint8_t* __restrict__ gath_q, uint8_t* __restrict__ gath_t) {
   __shared__ int warp_sums[kBlock / 32];
   __shared__ int running;
   const int pair = blockIdx.x;
-  const int ti = pairs[2 * pair + 1];
-  const int kq = k_per_image[pairs[2 * pair]];
+  const int qi = pairs[2 * pair], ti = pairs[2 * pair + 1];
+  const int kq = k_per_image[qi];
   const int kt = k_per_image[ti];
   if (threadIdx.x == 0) running = 0;
   __syncthreads();
   const int64_t base = static_cast<int64_t>(pair) * k_stride;
+  const int64_t qbase = static_cast<int64_t>(qi) * k_stride;
   const int64_t tbase = static_cast<int64_t>(ti) * k_stride;
   for (int r0 = 0; r0 < kq && kt > 0; r0 += kBlock) {
     const int r = r0 + threadIdx.x;
@@ -128,56 +145,69 @@ select_kernel(const int4* __restrict__ rowres, const int32_t* __restrict__ pairs
     if (r < kq) {
       v = rowres[base + r];
       const bool has1 = v.y >= 0 && v.y < kt;
-      const bool has2 = v.w >= 0 && v.w < kt;
       if (has1) {
         d1f = dist_from_sq(v.x);
-        keep = ratio > 0.0 ? (has2 && static_cast<double>(d1f) < ratio * static_cast<double>(dist_from_sq(v.z)))
-                           : true;
+        if (ratio > 0.0) {
+          // v.z may be a sentinel / padding value above 2^24: float rounding keeps it above every real distance
+          const bool has2 = exact2 ? (v.w >= 0 && v.w < kt) : (kt >= 2);
+          keep = has2 && static_cast<double>(d1f) < ratio * static_cast<double>(dist_from_sq(v.z));
+        } else {
+          keep = true;
+        }
       }
     }
     const int slot = block_compact_slot<kBlock>(keep, warp_sums, &running);
     if (keep) {
       const int64_t o = base + slot;
-      surv_q[o] = r;
-      surv_t[o] = v.y;
-      surv_d[o] = d1f;
-      surv_thr[o] = v.x - sqnorm[tbase + v.y];
-      if (do_gather) {
+      cand_q[o] = r;
+      cand_t[o] = v.y;
+      cand_d[o] = d1f;
+      cand_thr_mut[o] = v.x - sqnorm[tbase + v.y];
+      if (gather_q) {
+        cand_thr_ratio[o] = ratio_radius_sq(d1f, ratio) - sqnorm[qbase + r];
+        const uint4* src = reinterpret_cast<const uint4*>(bank + (qbase + r) * 128);
+        uint4* dst = reinterpret_cast<uint4*>(gath_q + o * 128);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) dst[i] = src[i];
+      }
+      if (gather_t) {
         const uint4* src = reinterpret_cast<const uint4*>(bank + (tbase + v.y) * 128);
-        uint4* dst = reinterpret_cast<uint4*>(gathered + o * 128);
+        uint4* dst = reinterpret_cast<uint4*>(gath_t + o * 128);
 #pragma unroll
         for (int i = 0; i < 8; ++i) dst[i] = src[i];
       }
     }
   }
   __syncthreads();
-  if (threadIdx.x == 0) surv_count[pair] = running;
+  if (threadIdx.x == 0) cand_count[pair] = running;
 }
 
-// Final order-preserving compaction of the survivors that passed the mutual check.
+// Final order-preserving compaction of the candidates that passed the verify sweeps.
 template <int kBlock>
 __global__ void __launch_bounds__(kBlock)
-emit_kernel(const int32_t* __restrict__ surv_q, const int32_t* __restrict__ surv_t,
-            const float* __restrict__ surv_d, const int32_t* __restrict__ surv_viol,
-            const int32_t* __restrict__ surv_count, int64_t k_stride, int mutual,
-            int32_t* __restrict__ out_q, int32_t* __restrict__ out_t, float* __restrict__ out_d,
-            int32_t* __restrict__ out_count, int64_t cap) {
+emit_kernel(const int32_t* __restrict__ cand_q, const int32_t* __restrict__ cand_t,
+            const float* __restrict__ cand_d, const int32_t* __restrict__ viol_ratio,
+            const int32_t* __restrict__ viol_mut, const int32_t* __restrict__ cand_count, int64_t k_stride,
+            int use_ratio, int use_mutual, int32_t* __restrict__ out_q, int32_t* __restrict__ out_t,
+            float* __restrict__ out_d, int32_t* __restrict__ out_count, int64_t cap) {
   __shared__ int warp_sums[kBlock / 32];
   __shared__ int running;
   const int pair = blockIdx.x;
-  const int n = surv_count[pair];
+  const int n = cand_count[pair];
   if (threadIdx.x == 0) running = 0;
   __syncthreads();
   const int64_t base = static_cast<int64_t>(pair) * k_stride;
   const int64_t obase = static_cast<int64_t>(pair) * cap;
   for (int s0 = 0; s0 < n; s0 += kBlock) {
     const int s = s0 + threadIdx.x;
-    const bool keep = s < n && (!mutual || surv_viol[base + s] == 0);
+    bool keep = s < n;
+    if (keep && use_ratio) keep = viol_ratio[base + s] == 0;
+    if (keep && use_mutual) keep = viol_mut[base + s] == 0;
     const int slot = block_compact_slot<kBlock>(keep, warp_sums, &running);
     if (keep && slot < cap) {
-      out_q[obase + slot] = surv_q[base + s];
-      out_t[obase + slot] = surv_t[base + s];
-      out_d[obase + slot] = surv_d[base + s];
+      out_q[obase + slot] = cand_q[base + s];
+      out_t[obase + slot] = cand_t[base + s];
+      out_d[obase + slot] = cand_d[base + s];
     }
   }
   __syncthreads();

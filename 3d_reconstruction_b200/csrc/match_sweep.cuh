@@ -21,13 +21,18 @@
 // 256 rows. Each epilogue thread owns one row (tcgen05.ld 32x32b: lane == row) and half of the
 // columns for the whole sweep; the two halves of a row meet once per item through shared memory.
 //
-// Two passes share the kernel (kKind):
-//   kTop2    rows = query descriptors of a pair, columns = train descriptors: exact top-2 per row.
+// Several passes share the kernel (kKind):
+//   kTop1    rows = query descriptors of a pair, columns = train descriptors: exact nearest column
+//            per row (lowest index on ties) + an upper bound on the second-nearest distance.
 //            A threshold-reject epilogue does one 3-input integer max per two accumulator values and
-//            runs the exact insertion only for 4-column groups that can change the row's top-2.
-//   kThresh  the mutual (cross) check, done lazily: rows = train descriptors of the ratio-test
-//            survivors (gathered), columns = all query descriptors; a row is violated when some
-//            query is strictly nearer (or equally near with a lower index) than its own.
+//            looks at exact scores only for 4-column groups that can beat the row's running best.
+//   kTop2    same sweep with the exact second-nearest as well (knnMatch k=2 output).
+//   kVerify  lazy checks on the few candidate rows that survive the first sweep, both of the form
+//            "does any column beat this row's threshold":
+//              ratio  rows = candidate query descriptors (gathered), columns = the train image:
+//                     violated when another train row lies inside the Lowe-ratio radius;
+//              mutual rows = the candidates' train descriptors (gathered), columns = the query
+//                     image: violated when some query is nearer (or equally near, lower index).
 //   kTop2Exact / kPeak  debugging (every element through the insertion) and MMA-only ceiling.
 #pragma once
 #include "ptx_sm100.cuh"
@@ -51,7 +56,7 @@ constexpr int kPadNorm = 1 << 23;   // > 128*255^2: norm of a padding row
 constexpr int kBig = 1 << 28;       // "no candidate yet" score; 2*acc + kBig cannot overflow
 constexpr uint32_t kEpiBarrier = 1; // named barrier of the 16 epilogue warps
 
-enum SweepKind { kTop2 = 0, kThresh = 1, kPeak = 2, kTop2Exact = 3 };
+enum SweepKind { kTop2 = 0, kVerify = 1, kPeak = 2, kTop2Exact = 3, kTop1 = 4 };
 
 struct NormSlot {
   int32_t nb[kTT];      // squared norms of the tile's 256 columns
@@ -80,13 +85,18 @@ struct SweepParams {
   int64_t k_stride;
   int32_t n_pairs;
   int32_t blocks_per_pair;      // k_stride / 256
-  // kTop2 output: per (pair, query row) (d1^2, i1, d2^2, i2)
+  // kTop1 / kTop2 output per (pair, query row): (d1^2, i1, d2^2, i2); for kTop1 d2^2 is an upper
+  // bound of the second-nearest squared distance and i2 is unused
   int4* rowres;
-  // kThresh: survivors of the ratio test, slot s of pair p lives at p * k_stride + s
-  const int32_t* surv_count;    // [n_pairs]
-  const int32_t* surv_q;        // query row of the survivor
-  const int32_t* surv_thr;      // d1^2 - |t1|^2 : the score a query must beat
-  int32_t* surv_viol;           // out: 1 when a better (or equal, lower-index) query exists
+  // kVerify: candidates of the first sweep, slot s of pair p lives at p * k_stride + s
+  const int32_t* cand_count;      // [n_pairs]
+  const int32_t* cand_q;          // query row of the candidate
+  const int32_t* cand_t;          // its nearest train row
+  const int32_t* cand_thr_ratio;  // ratio check: a train column with score < this kills the row
+  const int32_t* cand_thr_mut;    // mutual check: d1^2 - |t1|^2, the score a query must beat
+  int32_t* viol_ratio;            // out: 1 when the ratio test fails
+  int32_t* viol_mut;              // out: 1 when a better (or equal, lower-index) query exists
+  int32_t do_ratio, do_mutual;    // which of the two checks to run
 };
 
 struct ItemInfo {
@@ -96,24 +106,31 @@ struct ItemInfo {
   int n_rows;         // valid rows in this block (1..256)
   int n_cols;         // valid columns in the sweep
   int ntiles, nm;
+  int check;          // kVerify: 0 = ratio, 1 = mutual
   bool valid;
 };
 
 template <int kKind>
 __device__ __forceinline__ ItemInfo decode_item(const SweepParams& p, int item) {
   ItemInfo it;
+  it.check = 0;
+  if (kKind == kVerify) {
+    it.check = item & 1;
+    item >>= 1;
+  }
   it.pair = item / p.blocks_per_pair;
   it.blk = item - it.pair * p.blocks_per_pair;
   const int qi = __ldg(p.pairs + 2 * it.pair);
   const int ti = __ldg(p.pairs + 2 * it.pair + 1);
   const int kq = __ldg(p.k_per_image + qi);
   const int kt = __ldg(p.k_per_image + ti);
-  if (kKind == kThresh) {
-    const int s = __ldg(p.surv_count + it.pair);
+  if (kKind == kVerify) {
+    const bool on = it.check == 0 ? p.do_ratio != 0 : p.do_mutual != 0;
+    const int s = on ? __ldg(p.cand_count + it.pair) : 0;
     it.n_rows = s - it.blk * kRows;
-    it.n_cols = kq;
-    it.col_img = qi;
-    it.row_img_row0 = static_cast<int>(it.pair * p.k_stride + it.blk * kRows);   // gathered buffer
+    it.n_cols = it.check == 0 ? kt : kq;
+    it.col_img = it.check == 0 ? ti : qi;
+    it.row_img_row0 = static_cast<int>(it.pair * p.k_stride + it.blk * kRows);   // gathered buffers
   } else {
     it.n_rows = kq - it.blk * kRows;
     it.n_cols = kt;
@@ -146,10 +163,11 @@ __device__ __forceinline__ int max4(const int* v) { return max(__vimax3_s32(v[0]
 
 // Per-row epilogue state. Scores are  |col|^2 - 2 row.col  (the row's own norm is added at the end).
 struct RowState {
-  int s1, i1, s2, i2;   // kTop2: running best / second best (score, column)
-  int lim;              // kTop2: insert only scores < lim = min(s2, bound from the other column half + 1)
-  int2* pub;            // kTop2: where this thread publishes (s1, s2) for the other half
-  int thr, my_q, viol;  // kThresh: score to beat, the survivor's own query row, result flag
+  int s1, i1, s2, i2;    // running best / second best (score, column); kTop1: s2 is only an upper bound
+  int lim;               // kTop1 / kTop2: only scores < lim can matter (own state and the other column half)
+  int2* pub;             // where this thread publishes (s1, s2) for the other half
+  int thr, excl, tie;    // kVerify: violated by a column != excl with score < thr, or == thr and column < tie
+  int viol;
 };
 
 // One 32-column chunk of one row. v = raw int32 dot products, nb = the columns' squared norms,
@@ -191,8 +209,37 @@ __device__ __forceinline__ void process_chunk(const int (&v)[32], const int32_t*
       }
       if (st.lim != lim_p) *st.pub = make_int2(st.s1, st.s2);
     }
-  } else if (kKind == kThresh) {
-    // violated  <=>  exists column with s < thr, or s == thr and column index < my_q
+  } else if (kKind == kTop1) {
+    // Same threshold-reject test against the running best. A group that passes is resolved with a
+    // packed (score << 2 | j) minimum: IMADs on the FMA pipe, two integer minima on the ALU pipe.
+    int g[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) g[k] = max4(v + 4 * k);
+    const int mx = max(__vimax3_s32(__vimax3_s32(g[0], g[1], g[2]), g[3], g[4]), __vimax3_s32(g[5], g[6], g[7]));
+    int T = (nbm - st.lim) >> 1;
+    if (mx > T) {
+      const int lim_p = st.lim;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        if (g[k] > T) {
+          const int4 nb4 = *reinterpret_cast<const int4*>(nb + 4 * k);
+          const int ka = (nb4.x * 4 + 0) - 8 * v[4 * k], kb = (nb4.y * 4 + 1) - 8 * v[4 * k + 1];
+          const int kc = (nb4.z * 4 + 2) - 8 * v[4 * k + 2], kd = (nb4.w * 4 + 3) - 8 * v[4 * k + 3];
+          const int mk = min(__vimin3_s32(ka, kb, kc), kd);     // ties -> lowest j
+          const int sc = mk >> 2;
+          if (sc < st.lim) {
+            st.s2 = min(st.s2, st.s1);                          // the displaced best bounds the runner-up
+            st.s1 = sc;
+            st.i1 = nbase + 4 * k + (mk & 3);
+            st.lim = sc;
+            T = (nbm - sc) >> 1;
+          }
+        }
+      }
+      if (st.lim != lim_p) *st.pub = make_int2(st.s1, st.s2);
+    }
+  } else if (kKind == kVerify) {
+    // violated  <=>  exists column != excl with s < thr, or with s == thr and column index < tie
     //           =>   2*acc >= nb - thr  =>  acc > floor((min(nb) - thr - 1) / 2)
     int g[8];
 #pragma unroll
@@ -201,9 +248,17 @@ __device__ __forceinline__ void process_chunk(const int (&v)[32], const int32_t*
     const int T = (nbm - st.thr - 1) >> 1;
     if (mx > T) {
 #pragma unroll
-      for (int j = 0; j < 32; ++j) {
-        const int s = nb[j] - 2 * v[j];
-        if (s < st.thr || (s == st.thr && nbase + j < st.my_q)) st.viol = 1;
+      for (int k = 0; k < 8; ++k) {
+        if (g[k] > T) {
+          const int4 nb4 = *reinterpret_cast<const int4*>(nb + 4 * k);
+          const int sv[4] = {nb4.x - 2 * v[4 * k], nb4.y - 2 * v[4 * k + 1], nb4.z - 2 * v[4 * k + 2],
+                             nb4.w - 2 * v[4 * k + 3]};
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const int col = nbase + 4 * k + j;
+            if ((sv[j] < st.thr && col != st.excl) || (sv[j] == st.thr && col < st.tie)) st.viol = 1;
+          }
+        }
       }
     }
   }
@@ -211,17 +266,18 @@ __device__ __forceinline__ void process_chunk(const int (&v)[32], const int32_t*
 
 template <int kKind>
 __global__ void __launch_bounds__(kThreads, 1)
-sweep_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
-             const SweepParams p) {
+sweep_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_a2,
+             const __grid_constant__ CUtensorMap tmap_b, const SweepParams p) {
   extern __shared__ uint8_t smem_raw[];
   SweepSmem& sm = *reinterpret_cast<SweepSmem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
 
   const uint32_t warp = threadIdx.x >> 5;
   const uint32_t lane = lane_id();
-  const int n_items = p.n_pairs * p.blocks_per_pair;
+  const int n_items = p.n_pairs * p.blocks_per_pair * (kKind == kVerify ? 2 : 1);
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_a);
+    tma_prefetch_desc(&tmap_a2);
     tma_prefetch_desc(&tmap_b);
     for (int i = 0; i < kAStages; ++i) { mbar_init(&sm.a_full[i], 1); mbar_init(&sm.a_empty[i], 1); }
     for (int i = 0; i < kBStages; ++i) { mbar_init(&sm.b_full[i], 1); mbar_init(&sm.b_empty[i], 1); }
@@ -250,7 +306,8 @@ sweep_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
         const uint32_t as = a_it % kAStages, aph = (a_it / kAStages) & 1;
         mbar_wait(&sm.a_empty[as], aph ^ 1);
         mbar_arrive_expect_tx(&sm.a_full[as], it.nm * kMBytes);
-        for (int m = 0; m < it.nm; ++m) tma_load_2d(sm.a[as][m], &tmap_a, 0, it.row_img_row0 + m * kTM, &sm.a_full[as]);
+        const CUtensorMap* ta = (kKind == kVerify && it.check == 1) ? &tmap_a2 : &tmap_a;
+        for (int m = 0; m < it.nm; ++m) tma_load_2d(sm.a[as][m], ta, 0, it.row_img_row0 + m * kTM, &sm.a_full[as]);
         ++a_it;
         const int64_t crow0 = static_cast<int64_t>(it.col_img) * p.k_stride;
         for (int t = 0; t < it.ntiles; ++t) {
@@ -331,10 +388,15 @@ sweep_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
       ++item_it;
       st.pub = &sm.share[par][h][rl];
       const int2* partner = &sm.share[par][h ^ 1][rl];
-      st.thr = -kBig; st.my_q = 0; st.viol = 0;      // padding rows of a kThresh block can never be violated
-      if (kKind == kThresh && active && rl < it.n_rows) {
-        st.thr = __ldg(p.surv_thr + orow);
-        st.my_q = __ldg(p.surv_q + orow);
+      st.thr = -kBig; st.excl = -1; st.tie = -kBig; st.viol = 0;   // padding rows of a kVerify block can never be violated
+      if (kKind == kVerify && active && rl < it.n_rows) {
+        if (it.check == 0) {
+          st.thr = __ldg(p.cand_thr_ratio + orow);
+          st.excl = __ldg(p.cand_t + orow);
+        } else {
+          st.thr = __ldg(p.cand_thr_mut + orow);
+          st.tie = __ldg(p.cand_q + orow);
+        }
       }
 
       for (int t = 0; t < it.ntiles; ++t) {
@@ -358,13 +420,14 @@ sweep_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
         mbar_wait(&sm.n_full[ns], nph);
         if (active) {
           const NormSlot& nsl = sm.norms[ns];
-          if (kKind == kTop2) {
-            // The union of both halves has a second best <= min(max(s1, s1'), s2'): anything at or
-            // above it (strictly above on ties, the halves interleave in column order) cannot be in
-            // the row's final top-2. Racy reads are fine: published values only ever decrease.
+          if (kKind == kTop2 || kKind == kTop1) {
+            // Bound from the other column half of this row. kTop2: the union's second best is
+            // <= min(max(s1, s1'), s2'); kTop1: the union's best is <= s1'. Anything at or above the
+            // bound (strictly above on ties, the halves interleave in column order) cannot matter.
+            // Racy reads are fine: published values only ever decrease.
             const long long raw = *reinterpret_cast<const volatile long long*>(partner);
             const int ox = static_cast<int>(raw), oy = static_cast<int>(raw >> 32);
-            st.lim = min(st.lim, min(max(st.s1, ox), oy) + 1);
+            st.lim = min(st.lim, (kKind == kTop1 ? ox : min(max(st.s1, ox), oy)) + 1);
           }
           mbar_wait(&sm.t_full[acc], t_it & 1);
           tc_fence_after();
@@ -391,18 +454,24 @@ sweep_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
 
       // the two column halves of a row meet here: half 1 -> smem -> half 0 -> global
       if (h == 1 && active)
-        sm.rowmerge[par][rl] = kKind == kThresh ? make_int4(st.viol, 0, 0, 0) : make_int4(st.s1, st.i1, st.s2, st.i2);
+        sm.rowmerge[par][rl] = kKind == kVerify ? make_int4(st.viol, 0, 0, 0) : make_int4(st.s1, st.i1, st.s2, st.i2);
       sm.share[par ^ 1][h][rl] = make_int2(kBig, kBig);     // next item's slot; nobody reads it before the barrier
       named_bar_sync(kEpiBarrier, kEpiWarps * 32);
       if (h == 0 && active && rl < it.n_rows) {
         const int4 o = sm.rowmerge[par][rl];
-        if (kKind == kThresh) {
-          p.surv_viol[orow] = st.viol | o.x;
+        if (kKind == kVerify) {
+          (it.check == 0 ? p.viol_ratio : p.viol_mut)[orow] = st.viol | o.x;
         } else {
-          // merge two sorted (score, column) pairs; columns of the halves interleave tile by tile,
-          // so ties are resolved on the column index explicitly
+          // merge the two halves; columns of the halves interleave tile by tile, so ties are
+          // resolved on the column index explicitly
           int r1s, r1i, r2s, r2i;
-          if (lex_less(o.x, o.y, st.s1, st.i1)) {
+          if (kKind == kTop1) {
+            const bool other = lex_less(o.x, o.y, st.s1, st.i1);
+            r1s = other ? o.x : st.s1;
+            r1i = other ? o.y : st.i1;
+            r2s = min(min(o.z, st.s2), other ? st.s1 : o.x);   // the losing best bounds the runner-up
+            r2i = -1;
+          } else if (lex_less(o.x, o.y, st.s1, st.i1)) {
             r1s = o.x; r1i = o.y;
             if (lex_less(o.z, o.w, st.s1, st.i1)) { r2s = o.z; r2i = o.w; } else { r2s = st.s1; r2i = st.i1; }
           } else {

@@ -106,6 +106,8 @@ int b200m_match_pairs_u8(const uint8_t* bank, const int32_t* norm_table, const i
 /* Tuning / introspection knobs (process-global, read at launch time).
  *   "epilogue"  0 = exact insertion of every element (debug), 1 = threshold-reject (default),
  *               2 = MMA-only ceiling measurement (results invalid)
+ *   "pipeline"  1 = top-1 sweep + lazy ratio / mutual verify sweeps over the candidates (default),
+ *               0 = exact top-2 sweep + lazy mutual verify sweep
  *   "grid"      number of persistent CTAs, 0 = one per SM (default)
  *   "batch"     pairs per internal batch, 0 = default */
 int b200m_set_option(const char* name, int64_t value);

@@ -16,11 +16,15 @@ def _bits(x):
     return np.ascontiguousarray(x, dtype=np.float32).view(np.uint32)
 
 
-@pytest.fixture(scope="module", params=[1, 0], ids=["epi_reject", "epi_exact"])
+@pytest.fixture(scope="module", params=[(1, 1), (1, 0), (0, 0)], ids=["top1_verify", "top2_reject", "top2_exact"])
 def epi(pkg, request):
-    pkg.set_option("epilogue", request.param)
+    """(epilogue, pipeline): the default top-1 sweep + verify sweeps, the top-2 threshold-reject sweep
+    with only the mutual verify, and the debug epilogue that sends every element through the insertion."""
+    pkg.set_option("epilogue", request.param[0])
+    pkg.set_option("pipeline", request.param[1])
     yield request.param
     pkg.set_option("epilogue", 1)
+    pkg.set_option("pipeline", 1)
 
 
 def test_debug_dot_tile(pkg):

@@ -12,7 +12,7 @@ pkg = importlib.import_module("3d_reconstruction_b200")
 syn = importlib.import_module("3d_reconstruction_b200.synthetic")
 
 
-def run(n_img, k, modes=(1, 0, 2), reps=3, max_pairs=None, grid=0):
+def run(n_img, k, modes=((1, 1), (1, 0), (2, 1)), reps=3, max_pairs=None, grid=0):
     desc, kpi = syn.make_bank_tensor(n_img, k, seed=1234, device="cuda")
     bank = pkg.DescriptorBank.from_packed(desc, kpi)
     pairs = pkg.blocked_order(pkg.exhaustive_pairs(n_img))
@@ -23,7 +23,8 @@ def run(n_img, k, modes=(1, 0, 2), reps=3, max_pairs=None, grid=0):
     cap = k
     out = None
     for mode in modes:
-        pkg.set_option("epilogue", mode)
+        pkg.set_option("epilogue", mode[0])
+        pkg.set_option("pipeline", mode[1])
         pkg.set_option("grid", grid)
         out = pkg.match_pairs(bank, pairs_t, cap=cap, out=out)
         torch.cuda.synchronize()
@@ -42,6 +43,7 @@ def run(n_img, k, modes=(1, 0, 2), reps=3, max_pairs=None, grid=0):
                           "frac_of_4500": round(ops / t / 4.5e15, 3),
                           "matches": int(out.count.sum().item())}), flush=True)
     pkg.set_option("epilogue", 1)
+    pkg.set_option("pipeline", 1)
     pkg.set_option("grid", 0)
 
 
