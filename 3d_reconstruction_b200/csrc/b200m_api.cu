@@ -6,6 +6,8 @@
 #include <stdio.h>
 #include <string.h>
 
+#include <vector>
+
 #include "../../include/b200m.h"
 #include "match_finalize.cuh"
 #include "match_sweep.cuh"
@@ -20,6 +22,23 @@ struct Options {
   int64_t batch = 0;
   int64_t pipeline = 1;   // 1 = top-1 sweep + ratio/mutual verify sweeps, 0 = top-2 sweep + mutual verify
 } g_opt;
+
+// Optional per-launch timing of the sweeps with CUDA events on the launching stream ("profile" option).
+struct Profile {
+  bool on = false;
+  int64_t launches = 0;                                    // every kernel this library launched
+  std::vector<cudaEvent_t> pool;
+  std::vector<std::pair<int, int>> first, verify;          // (start, stop) indices into pool
+  size_t used = 0;
+  int take() {
+    if (used == pool.size()) {
+      cudaEvent_t e;
+      cudaEventCreate(&e);
+      pool.push_back(e);
+    }
+    return static_cast<int>(used++);
+  }
+} g_prof;
 
 int fail(int code, const char* fmt, const char* detail = "") {
   snprintf(g_err, sizeof(g_err), fmt, detail);
@@ -107,8 +126,19 @@ int launch_sweep(const CUtensorMap& tmap_a, const CUtensorMap& tmap_a2, const CU
                                   static_cast<int>(kSweepSmemBytes)));
     attr_set = true;
   }
+  int e0 = -1, e1 = -1;
+  if (g_prof.on) {
+    e0 = g_prof.take();
+    e1 = g_prof.take();
+    cudaEventRecord(g_prof.pool[e0], st);
+  }
   b200m::sweep_kernel<kKind><<<grid, b200m::kThreads, kSweepSmemBytes, st>>>(tmap_a, tmap_a2, tmap_b, sp);
   CUDA_TRY(cudaGetLastError());
+  ++g_prof.launches;
+  if (g_prof.on) {
+    cudaEventRecord(g_prof.pool[e1], st);
+    (kKind == b200m::kVerify ? g_prof.verify : g_prof.first).push_back({e0, e1});
+  }
   return B200M_OK;
 }
 
@@ -241,6 +271,7 @@ int b200m_set_option(const char* name, int64_t value) {
   if (!strcmp(name, "grid")) { g_opt.grid = value; return B200M_OK; }
   if (!strcmp(name, "batch")) { g_opt.batch = value; return B200M_OK; }
   if (!strcmp(name, "pipeline")) { g_opt.pipeline = value; return B200M_OK; }
+  if (!strcmp(name, "profile")) { g_prof.on = value != 0; return B200M_OK; }
   return fail(B200M_E_BAD_ARG, "unknown option %s", name);
 }
 
@@ -250,6 +281,7 @@ int64_t b200m_get_option(const char* name) {
   if (!strcmp(name, "grid")) return g_opt.grid;
   if (!strcmp(name, "batch")) return g_opt.batch;
   if (!strcmp(name, "pipeline")) return g_opt.pipeline;
+  if (!strcmp(name, "profile")) return g_prof.on ? 1 : 0;
   return -1;
 }
 
@@ -274,6 +306,7 @@ int b200m_bank_prepare_u8(uint8_t* bank, int32_t n_img, int64_t k_stride, const 
   b200m::bank_prepare_kernel<<<static_cast<int>(blocks), block, 0, st>>>(bank, n_rows, k_stride, k_per_image,
                                                                          norm_table, B200M_PAD_NORM);
   CUDA_TRY(cudaGetLastError());
+  g_prof.launches += 2;
   int64_t blocks2 = (n_rows + block - 1) / block;
   if (blocks2 > max_blocks) blocks2 = max_blocks;
   b200m::norm_chunk_min_kernel<<<static_cast<int>(blocks2), block, 0, st>>>(norm_table, n_rows, norm_table + n_rows);
@@ -310,6 +343,7 @@ int b200m_knn2_u8(const uint8_t* bank, const int32_t* norm_table, const int32_t*
     b200m::knn2_finalize_kernel<<<grid, 256, 0, st>>>(w.rowres, pairs + 2 * p0, k_per_image, k_stride,
                                                       out_train_idx + 2 * p0 * k_stride, out_dist + 2 * p0 * k_stride);
     CUDA_TRY(cudaGetLastError());
+    ++g_prof.launches;
   }
   return B200M_OK;
 }
@@ -350,6 +384,7 @@ int b200m_match_pairs_u8(const uint8_t* bank, const int32_t* norm_table, const i
         w.rowres, pb, k_per_image, k_stride, ratio, exact2 ? 1 : 0, bank, norm_table, do_ratio, do_mutual, w.cand_q,
         w.cand_t, w.cand_d, w.cand_thr_ratio, w.cand_thr_mut, w.cand_count, w.gath_q, w.gath_t);
     CUDA_TRY(cudaGetLastError());
+    ++g_prof.launches;
     if (do_ratio || do_mutual) {
       sp.do_ratio = do_ratio;
       sp.do_mutual = do_mutual;
@@ -361,7 +396,48 @@ int b200m_match_pairs_u8(const uint8_t* bank, const int32_t* norm_table, const i
         w.cand_q, w.cand_t, w.cand_d, w.viol_ratio, w.viol_mut, w.cand_count, k_stride, do_ratio, do_mutual,
         out_query_idx + p0 * cap, out_train_idx + p0 * cap, out_dist + p0 * cap, out_count + p0, cap);
     CUDA_TRY(cudaGetLastError());
+    ++g_prof.launches;
   }
+  return B200M_OK;
+}
+
+int b200m_compact_matches(const int32_t* query_idx, const int32_t* train_idx, const float* dist,
+                          const int32_t* count, const int64_t* offsets, int64_t n_pairs, int64_t cap,
+                          int32_t* flat_query_idx, int32_t* flat_train_idx, float* flat_dist, void* stream) {
+  if (n_pairs == 0) return B200M_OK;
+  if (!query_idx || !train_idx || !dist || !count || !offsets || !flat_query_idx || !flat_train_idx || !flat_dist ||
+      n_pairs < 0 || cap <= 0)
+    return fail(B200M_E_BAD_ARG, "null argument / bad sizes%s");
+  if (device_info().ok != 1) return fail(B200M_E_NO_DEVICE, "no sm_100 CUDA device available (no CPU fallback)%s");
+  b200m::compact_kernel<<<static_cast<unsigned>(n_pairs), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      query_idx, train_idx, dist, count, offsets, cap, flat_query_idx, flat_train_idx, flat_dist);
+  CUDA_TRY(cudaGetLastError());
+  ++g_prof.launches;
+  return B200M_OK;
+}
+
+int b200m_profile_read(double* first_sweep_ms, double* verify_sweep_ms, int64_t* first_sweeps, int64_t* launches) {
+  double a = 0.0, b = 0.0;
+  for (auto& pr : g_prof.first) {
+    float ms = 0.f;
+    CUDA_TRY(cudaEventSynchronize(g_prof.pool[pr.second]));
+    CUDA_TRY(cudaEventElapsedTime(&ms, g_prof.pool[pr.first], g_prof.pool[pr.second]));
+    a += ms;
+  }
+  for (auto& pr : g_prof.verify) {
+    float ms = 0.f;
+    CUDA_TRY(cudaEventSynchronize(g_prof.pool[pr.second]));
+    CUDA_TRY(cudaEventElapsedTime(&ms, g_prof.pool[pr.first], g_prof.pool[pr.second]));
+    b += ms;
+  }
+  if (first_sweep_ms) *first_sweep_ms = a;
+  if (verify_sweep_ms) *verify_sweep_ms = b;
+  if (first_sweeps) *first_sweeps = static_cast<int64_t>(g_prof.first.size());
+  if (launches) *launches = g_prof.launches;
+  g_prof.first.clear();
+  g_prof.verify.clear();
+  g_prof.used = 0;
+  g_prof.launches = 0;
   return B200M_OK;
 }
 

@@ -214,4 +214,20 @@ emit_kernel(const int32_t* __restrict__ cand_q, const int32_t* __restrict__ cand
   if (threadIdx.x == 0) out_count[pair] = running;
 }
 
+// [n_pairs, cap] slots + counts -> flat lists at offsets[pair] (exclusive scan of min(count, cap)).
+__global__ void compact_kernel(const int32_t* __restrict__ q, const int32_t* __restrict__ t,
+                               const float* __restrict__ d, const int32_t* __restrict__ count,
+                               const int64_t* __restrict__ offsets, int64_t cap, int32_t* __restrict__ fq,
+                               int32_t* __restrict__ ft, float* __restrict__ fd) {
+  const int64_t pair = blockIdx.x;
+  int64_t n = count[pair];
+  if (n > cap) n = cap;
+  const int64_t src = pair * cap, dst = offsets[pair];
+  for (int64_t i = threadIdx.x; i < n; i += blockDim.x) {
+    fq[dst + i] = q[src + i];
+    ft[dst + i] = t[src + i];
+    fd[dst + i] = d[src + i];
+  }
+}
+
 }  // namespace b200m

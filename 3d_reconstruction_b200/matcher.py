@@ -40,6 +40,26 @@ class PairMatches:
         if mx > self.cap:
             raise OverflowError(f"a pair produced {mx} matches but cap is {self.cap}; matches are never truncated silently")
 
+    def flatten(self) -> "FlatMatches":
+        """Device-side compaction into flat lists + offsets (one host sync for the total)."""
+        self.check_overflow()
+        P = int(self.count.numel())
+        offsets = torch.zeros((P + 1,), dtype=torch.int64, device=self.count.device)
+        if P:
+            torch.cumsum(self.count.to(torch.int64), 0, out=offsets[1:])
+        total = int(offsets[-1].item()) if P else 0
+        dev = self.count.device
+        fq = torch.empty((total,), dtype=torch.int32, device=dev)
+        ft = torch.empty((total,), dtype=torch.int32, device=dev)
+        fd = torch.empty((total,), dtype=torch.float32, device=dev)
+        if total:
+            with torch.cuda.device(dev):
+                st = torch.cuda.current_stream().cuda_stream
+                _lib.check(_lib.lib().b200m_compact_matches(
+                    self.query_idx.data_ptr(), self.train_idx.data_ptr(), self.dist.data_ptr(), self.count.data_ptr(),
+                    offsets.data_ptr(), P, int(self.cap), fq.data_ptr(), ft.data_ptr(), fd.data_ptr(), st))
+        return FlatMatches(fq, ft, fd, offsets)
+
     def to_lists(self):
         """-> list of (idx0 int64 [S], idx1 int64 [S], dist float32 [S]) numpy triples, one per pair."""
         self.check_overflow()
@@ -48,6 +68,22 @@ class PairMatches:
         t = self.train_idx.cpu().numpy()
         d = self.dist.cpu().numpy()
         return [(q[p, :c].astype(np.int64), t[p, :c].astype(np.int64), d[p, :c].copy()) for p, c in enumerate(cnt)]
+
+
+@dataclass
+class FlatMatches:
+    """Matches of all pairs back to back; pair p owns [offsets[p], offsets[p+1])."""
+    query_idx: torch.Tensor   # int32 [S_total]
+    train_idx: torch.Tensor   # int32 [S_total]
+    dist: torch.Tensor        # float32 [S_total]
+    offsets: torch.Tensor     # int64 [P + 1]
+
+    def cpu(self) -> "FlatMatches":
+        return FlatMatches(self.query_idx.cpu(), self.train_idx.cpu(), self.dist.cpu(), self.offsets.cpu())
+
+    def pair(self, p: int):
+        a, b = int(self.offsets[p]), int(self.offsets[p + 1])
+        return self.query_idx[a:b], self.train_idx[a:b], self.dist[a:b]
 
 
 def _pairs_tensor(pairs, device) -> torch.Tensor:
@@ -106,6 +142,19 @@ def knn2_pairs(bank: DescriptorBank, pairs, workspace: torch.Tensor | None = Non
             bank.desc.data_ptr(), bank.sqnorm.data_ptr(), bank.k_per_image.data_ptr(), bank.n_img, bank.k_stride,
             pairs_t.data_ptr(), P, idx.data_ptr(), dist.data_ptr(), ws.data_ptr(), ws.numel(), st))
     return idx, dist
+
+
+def match_pairs_host(desc_host: torch.Tensor, k_per_image, pairs, ratio: float = 0.75, mutual: bool = True,
+                     cap: int | None = None, device="cuda") -> FlatMatches:
+    """End-to-end call with HOST buffers: descriptors (uint8 [n_img, k_stride, 128], ideally pinned) and
+    the pair list go host -> device, the matches come back as flat host arrays. This is the unit the
+    reference performs per pair at matching.py:107-128 (host descriptors in, idx0 / idx1 on the host out)."""
+    dev = torch.device(device)
+    desc = desc_host.to(dev, non_blocking=True)
+    kpi = torch.as_tensor(np.asarray(k_per_image, dtype=np.int32)).to(dev, non_blocking=True)
+    bank = DescriptorBank.from_packed(desc, kpi)
+    res = match_pairs(bank, pairs, ratio=ratio, mutual=mutual, cap=cap)
+    return res.flatten().cpu()
 
 
 # ---------------------------------------------------------------------- cv2-shaped single pair

@@ -109,9 +109,23 @@ int b200m_match_pairs_u8(const uint8_t* bank, const int32_t* norm_table, const i
  *   "pipeline"  1 = top-1 sweep + lazy ratio / mutual verify sweeps over the candidates (default),
  *               0 = exact top-2 sweep + lazy mutual verify sweep
  *   "grid"      number of persistent CTAs, 0 = one per SM (default)
- *   "batch"     pairs per internal batch, 0 = default */
+ *   "batch"     pairs per internal batch, 0 = default
+ *   "profile"   1 = time sweep launches with CUDA events (see b200m_profile_read) */
 int b200m_set_option(const char* name, int64_t value);
 int64_t b200m_get_option(const char* name);
+
+/* [n_pairs, cap] slots + counts -> flat lists. offsets int64 [n_pairs] = exclusive scan of
+ * min(count, cap) (device; the caller computes it, e.g. with a cumsum). This is the device-side
+ * form of the per-pair idx0 / idx1 arrays matching.py:128 pulls back to the host. */
+int b200m_compact_matches(const int32_t* query_idx, const int32_t* train_idx, const float* dist,
+                          const int32_t* count, const int64_t* offsets, int64_t n_pairs, int64_t cap,
+                          int32_t* flat_query_idx, int32_t* flat_train_idx, float* flat_dist, void* stream);
+
+/* With option "profile" = 1 every sweep launch is bracketed by CUDA events on its stream.
+ * Reads (and resets) the accumulated device time of the first sweeps and of the verify sweeps,
+ * the number of first-sweep launches, and the number of kernels launched by the library.
+ * Blocks until the recorded events have completed. */
+int b200m_profile_read(double* first_sweep_ms, double* verify_sweep_ms, int64_t* first_sweeps, int64_t* launches);
 
 /* Diagnostics: raw 128 x 256 int32 dot-product tile through the same TMA + tcgen05 path
  * (used by the self-test to validate descriptors/swizzle independently of the epilogue). */
