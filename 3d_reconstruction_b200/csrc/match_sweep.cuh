@@ -170,59 +170,71 @@ struct RowState {
   int viol;
 };
 
-// One 32-column chunk of one row. v = raw int32 dot products, nb = the columns' squared norms,
-// nbm = min(nb) over the chunk, nbase = index of the chunk's first column.
+__device__ __forceinline__ int4 lds_v4(uint32_t saddr) {
+  int4 r;
+  asm volatile("ld.shared.v4.s32 {%0, %1, %2, %3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "r"(saddr));
+  return r;
+}
+__device__ __forceinline__ int lds_s32(uint32_t saddr) {
+  int r;
+  asm volatile("ld.shared.s32 %0, [%1];" : "=r"(r) : "r"(saddr));
+  return r;
+}
+
+// Sixteen columns of one row. v = raw int32 dot products, nb_s = shared-memory address of the
+// columns' squared norms, nbm = a lower bound of those norms (minimum over the enclosing 32-column
+// chunk), nbase = index of the first column.
 template <int kKind>
-__device__ __forceinline__ void process_chunk(const int (&v)[32], const int32_t* nb, int nbm, int nbase,
-                                              RowState& st) {
+__device__ __forceinline__ void process16(const int (&v)[16], uint32_t nb_s, int nbm, int nbase, RowState& st) {
   if (kKind == kTop2Exact) {
 #pragma unroll
-    for (int j = 0; j < 32; ++j) {
-      const int s = nb[j] - 2 * v[j];
-      if (s < st.s2) top2_insert(s, nbase + j, st.s1, st.i1, st.s2, st.i2);
+    for (int k = 0; k < 4; ++k) {
+      const int4 nb4 = lds_v4(nb_s + 16 * k);
+      const int sv[4] = {nb4.x - 2 * v[4 * k], nb4.y - 2 * v[4 * k + 1], nb4.z - 2 * v[4 * k + 2], nb4.w - 2 * v[4 * k + 3]};
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (sv[j] < st.s2) top2_insert(sv[j], nbase + 4 * k + j, st.s1, st.i1, st.s2, st.i2);
     }
-  } else if (kKind == kTop2) {
-    // s < s2  <=>  2*acc > nb - s2  <=>  acc > floor((nb - s2) / 2).  A group of columns can only
-    // change the row's top-2 if max(acc) > floor((min(nb) - s2) / 2): one 3-input max per two
-    // accumulator values, one compare per 4 columns of a chunk that passes, exact insertion only
-    // for the groups that pass.
-    int g[8];
+    return;
+  }
+  // Threshold-reject main path, shared by all kinds:  score < lim  <=>  2*acc > nb - lim  <=>
+  // acc > floor((nb - lim) / 2).  A group of columns can only matter if
+  // max(acc) > floor((min(nb) - lim) / 2): one 3-input max per two accumulator values, one compare
+  // per 4 columns of a half-chunk that passes, exact scores only for the groups that pass.
+  int g[4];
 #pragma unroll
-    for (int k = 0; k < 8; ++k) g[k] = max4(v + 4 * k);
-    const int mx = max(__vimax3_s32(__vimax3_s32(g[0], g[1], g[2]), g[3], g[4]), __vimax3_s32(g[5], g[6], g[7]));
-    int T = (nbm - st.lim) >> 1;
+  for (int k = 0; k < 4; ++k) g[k] = max4(v + 4 * k);
+  const int mx = max(__vimax3_s32(g[0], g[1], g[2]), g[3]);
+  if (kKind == kVerify) {
+    // violated  <=>  exists column != excl with s < thr, or with s == thr and column index < tie
+    //           =>   2*acc >= nb - thr  =>  acc > floor((min(nb) - thr - 1) / 2)
+    const int T = (nbm - st.thr - 1) >> 1;
     if (mx > T) {
-      const int lim_p = st.lim;
 #pragma unroll
-      for (int k = 0; k < 8; ++k) {
+      for (int k = 0; k < 4; ++k) {
         if (g[k] > T) {
-          const int4 nb4 = *reinterpret_cast<const int4*>(nb + 4 * k);
-          const int sa = nb4.x - 2 * v[4 * k], sb = nb4.y - 2 * v[4 * k + 1];
-          const int sc = nb4.z - 2 * v[4 * k + 2], sd = nb4.w - 2 * v[4 * k + 3];
-          // lim <= s2 always, so s < lim implies the insertion precondition s < s2
-          if (sa < st.lim) { top2_insert(sa, nbase + 4 * k, st.s1, st.i1, st.s2, st.i2); st.lim = min(st.lim, st.s2); }
-          if (sb < st.lim) { top2_insert(sb, nbase + 4 * k + 1, st.s1, st.i1, st.s2, st.i2); st.lim = min(st.lim, st.s2); }
-          if (sc < st.lim) { top2_insert(sc, nbase + 4 * k + 2, st.s1, st.i1, st.s2, st.i2); st.lim = min(st.lim, st.s2); }
-          if (sd < st.lim) { top2_insert(sd, nbase + 4 * k + 3, st.s1, st.i1, st.s2, st.i2); st.lim = min(st.lim, st.s2); }
-          T = (nbm - st.lim) >> 1;
+          const int4 nb4 = lds_v4(nb_s + 16 * k);
+          const int sv[4] = {nb4.x - 2 * v[4 * k], nb4.y - 2 * v[4 * k + 1], nb4.z - 2 * v[4 * k + 2],
+                             nb4.w - 2 * v[4 * k + 3]};
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const int col = nbase + 4 * k + j;
+            if ((sv[j] < st.thr && col != st.excl) || (sv[j] == st.thr && col < st.tie)) st.viol = 1;
+          }
         }
       }
-      if (st.lim != lim_p) *st.pub = make_int2(st.s1, st.s2);
     }
-  } else if (kKind == kTop1) {
-    // Same threshold-reject test against the running best. A group that passes is resolved with a
-    // packed (score << 2 | j) minimum: IMADs on the FMA pipe, two integer minima on the ALU pipe.
-    int g[8];
+    return;
+  }
+  int T = (nbm - st.lim) >> 1;
+  if (mx > T) {
+    const int lim_p = st.lim;
 #pragma unroll
-    for (int k = 0; k < 8; ++k) g[k] = max4(v + 4 * k);
-    const int mx = max(__vimax3_s32(__vimax3_s32(g[0], g[1], g[2]), g[3], g[4]), __vimax3_s32(g[5], g[6], g[7]));
-    int T = (nbm - st.lim) >> 1;
-    if (mx > T) {
-      const int lim_p = st.lim;
-#pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        if (g[k] > T) {
-          const int4 nb4 = *reinterpret_cast<const int4*>(nb + 4 * k);
+    for (int k = 0; k < 4; ++k) {
+      if (g[k] > T) {
+        const int4 nb4 = lds_v4(nb_s + 16 * k);
+        if (kKind == kTop1) {
+          // packed (score << 2 | j) minimum: IMADs on the FMA pipe, two integer minima on the ALU pipe
           const int ka = (nb4.x * 4 + 0) - 8 * v[4 * k], kb = (nb4.y * 4 + 1) - 8 * v[4 * k + 1];
           const int kc = (nb4.z * 4 + 2) - 8 * v[4 * k + 2], kd = (nb4.w * 4 + 3) - 8 * v[4 * k + 3];
           const int mk = min(__vimin3_s32(ka, kb, kc), kd);     // ties -> lowest j
@@ -234,33 +246,21 @@ __device__ __forceinline__ void process_chunk(const int (&v)[32], const int32_t*
             st.lim = sc;
             T = (nbm - sc) >> 1;
           }
-        }
-      }
-      if (st.lim != lim_p) *st.pub = make_int2(st.s1, st.s2);
-    }
-  } else if (kKind == kVerify) {
-    // violated  <=>  exists column != excl with s < thr, or with s == thr and column index < tie
-    //           =>   2*acc >= nb - thr  =>  acc > floor((min(nb) - thr - 1) / 2)
-    int g[8];
-#pragma unroll
-    for (int k = 0; k < 8; ++k) g[k] = max4(v + 4 * k);
-    const int mx = max(__vimax3_s32(__vimax3_s32(g[0], g[1], g[2]), g[3], g[4]), __vimax3_s32(g[5], g[6], g[7]));
-    const int T = (nbm - st.thr - 1) >> 1;
-    if (mx > T) {
-#pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        if (g[k] > T) {
-          const int4 nb4 = *reinterpret_cast<const int4*>(nb + 4 * k);
+        } else {   // kTop2; lim <= s2 always, so s < lim implies the insertion precondition s < s2
           const int sv[4] = {nb4.x - 2 * v[4 * k], nb4.y - 2 * v[4 * k + 1], nb4.z - 2 * v[4 * k + 2],
                              nb4.w - 2 * v[4 * k + 3]};
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
-            const int col = nbase + 4 * k + j;
-            if ((sv[j] < st.thr && col != st.excl) || (sv[j] == st.thr && col < st.tie)) st.viol = 1;
+            if (sv[j] < st.lim) {
+              top2_insert(sv[j], nbase + 4 * k + j, st.s1, st.i1, st.s2, st.i2);
+              st.lim = min(st.lim, st.s2);
+            }
           }
+          T = (nbm - st.lim) >> 1;
         }
       }
     }
+    if (st.lim != lim_p) *st.pub = make_int2(st.s1, st.s2);
   }
 }
 
@@ -433,18 +433,29 @@ sweep_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
           tc_fence_after();
           const uint32_t taddr = tmem_base + ((quad * 32u) << 16) + m * kTT + h * kTN;
           const int col0 = t * kTT + h * kTN;
-#pragma unroll 1
+          // Software-pipelined drain in half-chunks of 16 columns: the tcgen05.ld of the next half
+          // is in flight while the current one is processed (two 16-register buffers).
+          const uint32_t nb_s = smem_u32(nsl.nb) + (h * kTN) * 4;
+          const uint32_t nbm_s = smem_u32(nsl.nbmin) + (h * 4) * 4;
+          int va[16], vb[16];
+          tmem_ld_32x16(taddr, va);
+          tmem_ld_fence16(va);
+#pragma unroll
           for (int c = 0; c < 4; ++c) {
-            int v[32];
-            tmem_ld_32x32(taddr + c * 32, v);
-            tmem_ld_fence(v);
-            if (c == 3) {
+            const int nbm = lds_s32(nbm_s + 4 * c);
+            tmem_ld_32x16(taddr + c * 32 + 16, vb);
+            process16<kKind>(va, nb_s + (c * 32) * 4, nbm, col0 + c * 32, st);
+            tmem_ld_fence16(vb);
+            if (c < 3) {
+              tmem_ld_32x16(taddr + (c + 1) * 32, va);
+            } else {
               // accumulator fully drained into registers: hand it back to the MMA warp
               tc_fence_before();
               __syncwarp();
               if (lane == 0) mbar_arrive(&sm.t_empty[acc]);
             }
-            process_chunk<kKind>(v, nsl.nb + h * kTN + c * 32, nsl.nbmin[h * 4 + c], col0 + c * 32, st);
+            process16<kKind>(vb, nb_s + (c * 32 + 16) * 4, nbm, col0 + c * 32 + 16, st);
+            if (c < 3) tmem_ld_fence16(va);
           }
           ++t_it;
         }

@@ -2,6 +2,10 @@
 usage: python tools/sass_buckets.py src.csv <chunk_warps>"""
 import csv, sys
 rows = list(csv.reader(open(sys.argv[1])))
+# several captured kernels are concatenated: keep the first
+ends = [i for i, r in enumerate(rows) if r and r[0] == 'Kernel Name']
+if len(ends) > 1:
+    rows = rows[:ends[1]]
 cw = float(sys.argv[2])
 hdr = rows[1]
 ia = hdr.index('Source'); ie = hdr.index('Instructions Executed'); it = hdr.index('Avg. Threads Executed'); isamp = hdr.index('# Samples')
