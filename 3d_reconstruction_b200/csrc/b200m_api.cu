@@ -11,6 +11,7 @@
 #include "../../include/b200m.h"
 #include "match_finalize.cuh"
 #include "match_sweep.cuh"
+#include "match_sweep2.cuh"
 
 namespace {
 
@@ -20,6 +21,7 @@ struct Options {
   int64_t epilogue = 1;
   int64_t grid = 0;
   int64_t batch = 0;
+  int64_t kernel = 3;     // 3 = single-CTA sweep (four 128x128 accumulators), 4 = CTA-pair sweep (cta_group::2)
   int64_t pipeline = 1;   // 1 = top-1 sweep + ratio/mutual verify sweeps, 0 = top-2 sweep + mutual verify
 } g_opt;
 
@@ -142,6 +144,42 @@ int launch_sweep(const CUtensorMap& tmap_a, const CUtensorMap& tmap_a2, const CU
   return B200M_OK;
 }
 
+constexpr size_t kPairSmemBytes = sizeof(b200m::pair::PairSmem) + 1024;
+
+template <int kKind>
+int launch_sweep_pair(const CUtensorMap& tmap_a, const CUtensorMap& tmap_a2, const CUtensorMap& tmap_b,
+                      const b200m::SweepParams& sp, int grid, cudaStream_t st) {
+  static thread_local bool attr_set = false;
+  if (!attr_set) {
+    CUDA_TRY(cudaFuncSetAttribute(b200m::pair::sweep_pair_kernel<kKind>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  static_cast<int>(kPairSmemBytes)));
+    attr_set = true;
+  }
+  grid = (grid + 1) & ~1;   // whole CTA pairs (the kernel carries __cluster_dims__(2, 1, 1))
+  int e0 = -1, e1 = -1;
+  if (g_prof.on) {
+    e0 = g_prof.take();
+    e1 = g_prof.take();
+    cudaEventRecord(g_prof.pool[e0], st);
+  }
+  b200m::pair::sweep_pair_kernel<kKind><<<grid, b200m::pair::kThreads2, kPairSmemBytes, st>>>(tmap_a, tmap_a2, tmap_b, sp);
+  CUDA_TRY(cudaGetLastError());
+  ++g_prof.launches;
+  if (g_prof.on) {
+    cudaEventRecord(g_prof.pool[e1], st);
+    (kKind == b200m::kVerify ? g_prof.verify : g_prof.first).push_back({e0, e1});
+  }
+  return B200M_OK;
+}
+
+// dispatch on the "kernel" option
+template <int kKind>
+int launch_any(const CUtensorMap& tmap_a, const CUtensorMap& tmap_a2, const CUtensorMap& tmap_b,
+               const b200m::SweepParams& sp, int grid, cudaStream_t st) {
+  return g_opt.kernel == 4 ? launch_sweep_pair<kKind>(tmap_a, tmap_a2, tmap_b, sp, grid, st)
+                           : launch_sweep<kKind>(tmap_a, tmap_a2, tmap_b, sp, grid, st);
+}
+
 constexpr int64_t kDefaultBatchRows = int64_t(1) << 22;   // pairs * k_stride per internal batch
 
 int64_t batch_pairs(int64_t k_stride, int64_t n_pairs) {
@@ -240,11 +278,11 @@ b200m::SweepParams base_params(const int32_t* norm_table, int32_t n_img, const i
 int sweep_rows(const CUtensorMap& tmap_bank, const b200m::SweepParams& sp, bool exact2, cudaStream_t st) {
   const int grid = sweep_grid(static_cast<int64_t>(sp.n_pairs) * sp.blocks_per_pair);
   switch (g_opt.epilogue) {
-    case 0: return launch_sweep<b200m::kTop2Exact>(tmap_bank, tmap_bank, tmap_bank, sp, grid, st);
-    case 2: return launch_sweep<b200m::kPeak>(tmap_bank, tmap_bank, tmap_bank, sp, grid, st);
+    case 0: return launch_any<b200m::kTop2Exact>(tmap_bank, tmap_bank, tmap_bank, sp, grid, st);
+    case 2: return launch_any<b200m::kPeak>(tmap_bank, tmap_bank, tmap_bank, sp, grid, st);
     default:
-      return exact2 ? launch_sweep<b200m::kTop2>(tmap_bank, tmap_bank, tmap_bank, sp, grid, st)
-                    : launch_sweep<b200m::kTop1>(tmap_bank, tmap_bank, tmap_bank, sp, grid, st);
+      return exact2 ? launch_any<b200m::kTop2>(tmap_bank, tmap_bank, tmap_bank, sp, grid, st)
+                    : launch_any<b200m::kTop1>(tmap_bank, tmap_bank, tmap_bank, sp, grid, st);
   }
 }
 
@@ -271,6 +309,7 @@ int b200m_set_option(const char* name, int64_t value) {
   if (!strcmp(name, "grid")) { g_opt.grid = value; return B200M_OK; }
   if (!strcmp(name, "batch")) { g_opt.batch = value; return B200M_OK; }
   if (!strcmp(name, "pipeline")) { g_opt.pipeline = value; return B200M_OK; }
+  if (!strcmp(name, "kernel")) { g_opt.kernel = value; return B200M_OK; }
   if (!strcmp(name, "profile")) { g_prof.on = value != 0; return B200M_OK; }
   return fail(B200M_E_BAD_ARG, "unknown option %s", name);
 }
@@ -281,6 +320,7 @@ int64_t b200m_get_option(const char* name) {
   if (!strcmp(name, "grid")) return g_opt.grid;
   if (!strcmp(name, "batch")) return g_opt.batch;
   if (!strcmp(name, "pipeline")) return g_opt.pipeline;
+  if (!strcmp(name, "kernel")) return g_opt.kernel;
   if (!strcmp(name, "profile")) return g_prof.on ? 1 : 0;
   return -1;
 }
@@ -389,7 +429,7 @@ int b200m_match_pairs_u8(const uint8_t* bank, const int32_t* norm_table, const i
       sp.do_ratio = do_ratio;
       sp.do_mutual = do_mutual;
       const int grid = sweep_grid(nb * sp.blocks_per_pair * 2);
-      rc = launch_sweep<b200m::kVerify>(tmap_gq, tmap_gt, tmap_bank, sp, grid, st);
+      rc = launch_any<b200m::kVerify>(tmap_gq, tmap_gt, tmap_bank, sp, grid, st);
       if (rc) return rc;
     }
     b200m::emit_kernel<1024><<<static_cast<unsigned>(nb), 1024, 0, st>>>(

@@ -16,15 +16,22 @@ def _bits(x):
     return np.ascontiguousarray(x, dtype=np.float32).view(np.uint32)
 
 
-@pytest.fixture(scope="module", params=[(1, 1), (1, 0), (0, 0)], ids=["top1_verify", "top2_reject", "top2_exact"])
+DEFAULT_KERNEL = 3
+
+
+@pytest.fixture(scope="module", params=[(1, 1, 4), (1, 0, 4), (0, 0, 4), (1, 1, 3), (1, 0, 3), (0, 0, 3)],
+                ids=["pair_top1_verify", "pair_top2_reject", "pair_top2_exact", "top1_verify", "top2_reject", "top2_exact"])
 def epi(pkg, request):
-    """(epilogue, pipeline): the default top-1 sweep + verify sweeps, the top-2 threshold-reject sweep
-    with only the mutual verify, and the debug epilogue that sends every element through the insertion."""
+    """(epilogue, pipeline, kernel): the top-1 sweep + verify sweeps, the top-2 threshold-reject sweep
+    with only the mutual verify, and the debug epilogue that sends every element through the insertion;
+    each on the CTA-pair kernel (cta_group::2) and on the single-CTA kernel."""
     pkg.set_option("epilogue", request.param[0])
     pkg.set_option("pipeline", request.param[1])
+    pkg.set_option("kernel", request.param[2])
     yield request.param
     pkg.set_option("epilogue", 1)
     pkg.set_option("pipeline", 1)
+    pkg.set_option("kernel", DEFAULT_KERNEL)
 
 
 def test_debug_dot_tile(pkg):
