@@ -19,11 +19,14 @@ SYMBOLS = (
     "b200m_sm_count",
     "b200m_norm_table_elems",
     "b200m_bank_prepare_u8",
+    "b200m_sort_table_elems",
+    "b200m_bank_sort_u8",
     "b200m_workspace_bytes",
     "b200m_knn2_u8",
     "b200m_match_pairs_u8",
     "b200m_compact_matches",
     "b200m_profile_read",
+    "b200m_profile_detail",
     "b200m_set_option",
     "b200m_get_option",
     "b200m_debug_dot_tile_u8",
@@ -59,16 +62,22 @@ def lib() -> C.CDLL:
     L.b200m_norm_table_elems.argtypes = [i32, i64]
     L.b200m_bank_prepare_u8.restype = C.c_int
     L.b200m_bank_prepare_u8.argtypes = [vp, i32, i64, vp, vp, vp]
+    L.b200m_sort_table_elems.restype = i64
+    L.b200m_sort_table_elems.argtypes = [i32, i64]
+    L.b200m_bank_sort_u8.restype = C.c_int
+    L.b200m_bank_sort_u8.argtypes = [vp, vp, vp, i32, i64, vp, vp, vp]
     L.b200m_workspace_bytes.restype = sz
     L.b200m_workspace_bytes.argtypes = [i64, i64]
     L.b200m_knn2_u8.restype = C.c_int
     L.b200m_knn2_u8.argtypes = [vp, vp, vp, i32, i64, vp, i64, vp, vp, vp, sz, vp]
     L.b200m_match_pairs_u8.restype = C.c_int
-    L.b200m_match_pairs_u8.argtypes = [vp, vp, vp, i32, i64, vp, i64, dbl, C.c_int, vp, vp, vp, vp, i64, vp, sz, vp]
+    L.b200m_match_pairs_u8.argtypes = [vp, vp, vp, vp, vp, i32, i64, vp, i64, dbl, C.c_int, vp, vp, vp, vp, i64, vp, sz, vp]
     L.b200m_compact_matches.restype = C.c_int
     L.b200m_compact_matches.argtypes = [vp, vp, vp, vp, vp, i64, i64, vp, vp, vp, vp]
     L.b200m_profile_read.restype = C.c_int
     L.b200m_profile_read.argtypes = [C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(i64), C.POINTER(i64)]
+    L.b200m_profile_detail.restype = C.c_int
+    L.b200m_profile_detail.argtypes = [C.POINTER(C.c_double), C.c_int]
     L.b200m_set_option.restype = C.c_int
     L.b200m_set_option.argtypes = [C.c_char_p, i64]
     L.b200m_get_option.restype = i64
@@ -93,8 +102,12 @@ def get_option(name: str) -> int:
 
 
 def profile_read():
-    """-> dict(first_sweep_ms, verify_sweep_ms, first_sweeps, launches); resets the counters."""
+    """-> dict(first_sweep_ms, verify_sweep_ms, first_sweeps, launches, fallback_sweep_ms, refine_ms, select_ms,
+    emit_ms); resets the counters."""
+    det = (C.c_double * 6)()
+    check(lib().b200m_profile_detail(det, 6))
     a, b = C.c_double(0), C.c_double(0)
     n, l = C.c_int64(0), C.c_int64(0)
     check(lib().b200m_profile_read(C.byref(a), C.byref(b), C.byref(n), C.byref(l)))
-    return {"first_sweep_ms": a.value, "verify_sweep_ms": b.value, "first_sweeps": n.value, "launches": l.value}
+    return {"first_sweep_ms": a.value, "verify_sweep_ms": b.value, "first_sweeps": n.value, "launches": l.value,
+            "fallback_sweep_ms": det[2], "refine_ms": det[3], "select_ms": det[4], "emit_ms": det[5]}

@@ -40,16 +40,22 @@ def to_u8_descriptors(a) -> np.ndarray:
 class DescriptorBank:
     """Device-resident bank. Padding rows are zero with the sentinel norm (see include/b200m.h)."""
 
-    def __init__(self, desc: torch.Tensor, k_per_image: torch.Tensor, sqnorm: torch.Tensor):
+    def __init__(self, desc: torch.Tensor, k_per_image: torch.Tensor, sqnorm: torch.Tensor,
+                 sorted_desc: torch.Tensor | None = None, sort_table: torch.Tensor | None = None):
         self.desc = desc
         self.k_per_image = k_per_image
         self.sqnorm = sqnorm
+        # norm-sorted copy + perm / inv / sorted norms / chunk minima / spreads (b200m_bank_sort_u8):
+        # what the default pipeline (chunk sweep) runs on. None -> the slower pipeline 1.
+        self.sorted_desc = sorted_desc
+        self.sort_table = sort_table
         self._k_host = None
 
     # ------------------------------------------------------------------ construction
     @classmethod
-    def from_packed(cls, desc: torch.Tensor, k_per_image: torch.Tensor) -> "DescriptorBank":
-        """desc: uint8 CUDA [n_img, k_stride, 128], k_stride % 256 == 0. Padding is zeroed in place."""
+    def from_packed(cls, desc: torch.Tensor, k_per_image: torch.Tensor, sort: bool = True) -> "DescriptorBank":
+        """desc: uint8 CUDA [n_img, k_stride, 128], k_stride % 256 == 0. Padding is zeroed in place.
+        sort=True also builds the norm-sorted copy the default pipeline needs (twice the HBM footprint)."""
         if not desc.is_cuda:
             raise RuntimeError("the descriptor bank must live on a CUDA device (there is no CPU path)")
         if desc.dtype != torch.uint8 or desc.dim() != 3 or desc.shape[2] != DESC_DIM or not desc.is_contiguous():
@@ -65,7 +71,15 @@ class DescriptorBank:
             st = torch.cuda.current_stream().cuda_stream
             _lib.check(_lib.lib().b200m_bank_prepare_u8(desc.data_ptr(), desc.shape[0], desc.shape[1],
                                                         k_per_image.data_ptr(), sqnorm.data_ptr(), st))
-        return cls(desc, k_per_image, sqnorm)
+            sorted_desc = sort_table = None
+            if sort:
+                n_st = int(_lib.lib().b200m_sort_table_elems(desc.shape[0], desc.shape[1]))
+                sorted_desc = torch.empty_like(desc)
+                sort_table = torch.empty((n_st,), dtype=torch.int32, device=desc.device)
+                _lib.check(_lib.lib().b200m_bank_sort_u8(desc.data_ptr(), sqnorm.data_ptr(), k_per_image.data_ptr(),
+                                                         desc.shape[0], desc.shape[1], sorted_desc.data_ptr(),
+                                                         sort_table.data_ptr(), st))
+        return cls(desc, k_per_image, sqnorm, sorted_desc, sort_table)
 
     @classmethod
     def from_arrays(cls, arrays: Sequence, device="cuda", k_stride: int | None = None) -> "DescriptorBank":
@@ -108,7 +122,17 @@ class DescriptorBank:
         return self._k_host
 
     def nbytes(self) -> int:
-        return self.desc.numel() + 4 * self.sqnorm.numel() + 4 * self.k_per_image.numel()
+        n = self.desc.numel() + 4 * self.sqnorm.numel() + 4 * self.k_per_image.numel()
+        if self.sorted_desc is not None:
+            n += self.sorted_desc.numel() + 4 * self.sort_table.numel()
+        return n
+
+    def sort_views(self):
+        """(perm, inv, sorted norms) as int32 [n_img, k_stride] views, chunk minima [n_img, k_stride/32], spreads [n_img]."""
+        R, n, ks = self.n_img * self.k_stride, self.n_img, self.k_stride
+        t = self.sort_table
+        return (t[:R].view(n, ks), t[R:2 * R].view(n, ks), t[2 * R:3 * R].view(n, ks),
+                t[3 * R:3 * R + R // 32].view(n, ks // 32), t[3 * R + R // 32:3 * R + R // 32 + n])
 
     def norms(self) -> torch.Tensor:
         """int32 [n_img, k_stride] view of the squared norms (B200M_PAD_NORM on padding rows)."""

@@ -7,7 +7,7 @@ import sys
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 SRC = os.path.join(HERE, "csrc", "b200m_api.cu")
-DEPS = [os.path.join(HERE, "csrc", f) for f in ("b200m_api.cu", "match_sweep.cuh", "match_finalize.cuh", "ptx_sm100.cuh")]
+DEPS = [os.path.join(HERE, "csrc", f) for f in sorted(os.listdir(os.path.join(HERE, "csrc")))]
 DEPS.append(os.path.join(HERE, "..", "include", "b200m.h"))
 OUT = os.path.join(HERE, "lib", "libb200m.so")
 

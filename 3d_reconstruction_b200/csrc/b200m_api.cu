@@ -12,6 +12,9 @@
 #include "match_finalize.cuh"
 #include "match_sweep.cuh"
 #include "match_sweep2.cuh"
+#include "match_chunk.cuh"
+#include "match_refine.cuh"
+#include "match_sort.cuh"
 
 namespace {
 
@@ -22,7 +25,9 @@ struct Options {
   int64_t grid = 0;
   int64_t batch = 0;
   int64_t kernel = 3;     // 3 = single-CTA sweep (four 128x128 accumulators), 4 = CTA-pair sweep (cta_group::2)
-  int64_t pipeline = 1;   // 1 = top-1 sweep + ratio/mutual verify sweeps, 0 = top-2 sweep + mutual verify
+  // 2 = chunk sweep on the norm-sorted bank + refine + exact fallback (default, needs the sorted bank),
+  // 1 = top-1 sweep + ratio/mutual verify sweeps, 0 = top-2 sweep + mutual verify
+  int64_t pipeline = 2;
 } g_opt;
 
 // Optional per-launch timing of the sweeps with CUDA events on the launching stream ("profile" option).
@@ -31,6 +36,7 @@ struct Profile {
   int64_t launches = 0;                                    // every kernel this library launched
   std::vector<cudaEvent_t> pool;
   std::vector<std::pair<int, int>> first, verify;          // (start, stop) indices into pool
+  std::vector<std::pair<int, int>> fallback, refine, select, emit;
   size_t used = 0;
   int take() {
     if (used == pool.size()) {
@@ -41,6 +47,27 @@ struct Profile {
     return static_cast<int>(used++);
   }
 } g_prof;
+
+// brackets one launch with events when profiling is on
+struct ProfScope {
+  std::vector<std::pair<int, int>>* list;
+  cudaStream_t st;
+  int e0 = -1;
+  ProfScope(std::vector<std::pair<int, int>>* l, cudaStream_t s) : list(l), st(s) {
+    if (g_prof.on && list) {
+      e0 = g_prof.take();
+      cudaEventRecord(g_prof.pool[e0], st);
+    }
+  }
+  ~ProfScope() {
+    ++g_prof.launches;
+    if (e0 >= 0) {
+      const int e1 = g_prof.take();
+      cudaEventRecord(g_prof.pool[e1], st);
+      list->push_back({e0, e1});
+    }
+  }
+};
 
 int fail(int code, const char* fmt, const char* detail = "") {
   snprintf(g_err, sizeof(g_err), fmt, detail);
@@ -139,8 +166,25 @@ int launch_sweep(const CUtensorMap& tmap_a, const CUtensorMap& tmap_a2, const CU
   ++g_prof.launches;
   if (g_prof.on) {
     cudaEventRecord(g_prof.pool[e1], st);
-    (kKind == b200m::kVerify ? g_prof.verify : g_prof.first).push_back({e0, e1});
+    (kKind == b200m::kVerify ? g_prof.verify : kKind == b200m::kTop1G ? g_prof.fallback : g_prof.first).push_back({e0, e1});
   }
+  return B200M_OK;
+}
+
+constexpr size_t kChunkSmemBytes = sizeof(b200m::ChunkSmem) + 1024;
+
+int launch_chunk_sweep(const CUtensorMap& tmap, const b200m::ChunkParams& cp, int grid, cudaStream_t st) {
+  static thread_local bool attr_set = false;
+  if (!attr_set) {
+    CUDA_TRY(cudaFuncSetAttribute(b200m::chunk_sweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  static_cast<int>(kChunkSmemBytes)));
+    attr_set = true;
+  }
+  {
+    ProfScope ps(&g_prof.first, st);
+    b200m::chunk_sweep_kernel<<<grid, b200m::kThreads, kChunkSmemBytes, st>>>(tmap, cp);
+  }
+  CUDA_TRY(cudaGetLastError());
   return B200M_OK;
 }
 
@@ -203,6 +247,13 @@ struct Workspace {
   int32_t* cand_count;      // B (padded to 64)
   uint8_t* gath_q;          // R * 128
   uint8_t* gath_t;          // R * 128
+  // pipeline 2
+  int4* rowres_o;           // R   refined rows, original query order
+  int32_t* fb_q;            // R   rows of the fallback sweep
+  int32_t* cand_rslot;      // R   slot of a candidate in the open-ratio list, -1 = settled
+  int32_t* cand_excl;       // R   open-ratio list: the nearest train row
+  int32_t* fb_count;        // B (padded to 64)
+  int32_t* cand_count_a;    // B (padded to 64)
 };
 
 size_t carve(Workspace* w, void* base, int64_t B, int64_t k_stride) {
@@ -216,7 +267,16 @@ size_t carve(Workspace* w, void* base, int64_t B, int64_t k_stride) {
   uintptr_t g = take(4 * (B + 64));
   uintptr_t h = take(static_cast<size_t>(128) * R);
   uintptr_t h2 = take(static_cast<size_t>(128) * R);
+  uintptr_t i1 = take(sizeof(int4) * R);
+  uintptr_t i2 = take(4 * R), i3 = take(4 * R), i4 = take(4 * R);
+  uintptr_t i5 = take(4 * (B + 64)), i6 = take(4 * (B + 64));
   if (w) {
+    w->rowres_o = reinterpret_cast<int4*>(i1);
+    w->fb_q = reinterpret_cast<int32_t*>(i2);
+    w->cand_rslot = reinterpret_cast<int32_t*>(i3);
+    w->cand_excl = reinterpret_cast<int32_t*>(i4);
+    w->fb_count = reinterpret_cast<int32_t*>(i5);
+    w->cand_count_a = reinterpret_cast<int32_t*>(i6);
     w->rowres = reinterpret_cast<int4*>(a);
     w->cand_q = reinterpret_cast<int32_t*>(b);
     w->cand_t = reinterpret_cast<int32_t*>(c);
@@ -244,6 +304,34 @@ int check_common(const void* bank, const void* sqnorm, const void* kpi, int32_t 
   return B200M_OK;
 }
 
+// sort table (int32): perm[R] | inv[R] | snorm[R] | cmin[R/32] | spread[n_img rounded up to 4], R = n_img * k_stride
+struct SortTable {
+  const int32_t *perm, *inv, *snorm, *cmin, *spread;
+};
+
+int64_t sort_table_elems(int64_t n_img, int64_t k_stride) {
+  const int64_t R = n_img * k_stride;
+  return 3 * R + R / 32 + ((n_img + 3) & ~int64_t(3));
+}
+
+SortTable sort_table_view(const int32_t* t, int64_t n_img, int64_t k_stride) {
+  const int64_t R = n_img * k_stride;
+  SortTable v;
+  v.perm = t;
+  v.inv = t + R;
+  v.snorm = t + 2 * R;
+  v.cmin = t + 3 * R;
+  v.spread = t + 3 * R + R / 32;
+  return v;
+}
+
+int grid_for(int64_t work, int block) {
+  int64_t blocks = (work + block - 1) / block;
+  const int64_t max_blocks = static_cast<int64_t>(device_info().sms) * 16;
+  if (blocks > max_blocks) blocks = max_blocks;
+  return blocks < 1 ? 1 : static_cast<int>(blocks);
+}
+
 int sweep_grid(int64_t items) {
   int grid = g_opt.grid > 0 ? static_cast<int>(g_opt.grid) : device_info().sms;
   if (grid > items) grid = static_cast<int>(items);
@@ -262,8 +350,13 @@ b200m::SweepParams base_params(const int32_t* norm_table, int32_t n_img, const i
   sp.blocks_per_pair = static_cast<int32_t>(k_stride / b200m::kRows);
   sp.rowres = w.rowres;
   sp.cand_count = w.cand_count;
+  sp.cand_count_r = w.cand_count;
   sp.cand_q = w.cand_q;
   sp.cand_t = w.cand_t;
+  sp.cand_excl = w.cand_t;
+  sp.fb_count = w.fb_count;
+  sp.fb_q = w.fb_q;
+  sp.rowres_o = w.rowres_o;
   sp.cand_thr_ratio = w.cand_thr_ratio;
   sp.cand_thr_mut = w.cand_thr_mut;
   sp.viol_ratio = w.viol_ratio;
@@ -354,6 +447,56 @@ int b200m_bank_prepare_u8(uint8_t* bank, int32_t n_img, int64_t k_stride, const 
   return B200M_OK;
 }
 
+int64_t b200m_sort_table_elems(int32_t n_img, int64_t k_stride) {
+  if (n_img <= 0 || k_stride <= 0) return 0;
+  return sort_table_elems(n_img, k_stride);
+}
+
+int b200m_bank_sort_u8(const uint8_t* bank, const int32_t* norm_table, const int32_t* k_per_image, int32_t n_img,
+                       int64_t k_stride, uint8_t* sorted_bank, int32_t* sort_table, void* stream) {
+  if (!bank || !norm_table || !k_per_image || !sorted_bank || !sort_table || n_img <= 0)
+    return fail(B200M_E_BAD_ARG, "null argument or n_img <= 0%s");
+  if (k_stride <= 0 || (k_stride % B200M_TILE_T) != 0)
+    return fail(B200M_E_BAD_ARG, "k_stride must be a positive multiple of 256%s");
+  if (device_info().ok != 1) return fail(B200M_E_NO_DEVICE, "no sm_100 CUDA device available (no CPU fallback)%s");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int64_t R = static_cast<int64_t>(n_img) * k_stride;
+  int64_t n2 = b200m::kSortChunk;
+  while (n2 < k_stride) n2 <<= 1;
+  // the 64-bit sort keys live in the (not yet written) sorted bank: 8 * n2 <= 16 * k_stride bytes of each 128 * k_stride slab
+  unsigned long long* keys = reinterpret_cast<unsigned long long*>(sorted_bank);
+  const int64_t key_stride = k_stride * 16;
+  const SortTable tv = sort_table_view(sort_table, n_img, k_stride);
+  const int64_t total = static_cast<int64_t>(n_img) * n2;
+  b200m::sort_init_kernel<<<grid_for(total, 256), 256, 0, st>>>(norm_table, k_stride, n2, total, keys, key_stride);
+  CUDA_TRY(cudaGetLastError());
+  const unsigned smem_blocks = static_cast<unsigned>(total / b200m::kSortChunk);
+  b200m::sort_smem_kernel<true><<<smem_blocks, b200m::kSortThreads, 0, st>>>(keys, n2, key_stride, 0);
+  CUDA_TRY(cudaGetLastError());
+  g_prof.launches += 2;
+  for (int64_t size = 2 * b200m::kSortChunk; size <= n2; size <<= 1) {
+    for (int64_t stride = size / 2; stride >= b200m::kSortChunk; stride >>= 1) {
+      b200m::sort_global_kernel<<<grid_for(total / 2, 256), 256, 0, st>>>(keys, n2, key_stride, n_img, size, stride);
+      CUDA_TRY(cudaGetLastError());
+      ++g_prof.launches;
+    }
+    b200m::sort_smem_kernel<false><<<smem_blocks, b200m::kSortThreads, 0, st>>>(keys, n2, key_stride, size);
+    CUDA_TRY(cudaGetLastError());
+    ++g_prof.launches;
+  }
+  b200m::sort_extract_kernel<<<grid_for(R, 256), 256, 0, st>>>(keys, key_stride, k_stride, R, const_cast<int32_t*>(tv.perm),
+                                                              const_cast<int32_t*>(tv.inv), const_cast<int32_t*>(tv.snorm));
+  CUDA_TRY(cudaGetLastError());
+  b200m::sort_gather_kernel<<<grid_for(R * 32, 256), 256, 0, st>>>(bank, tv.perm, k_stride, R, sorted_bank);
+  CUDA_TRY(cudaGetLastError());
+  CUDA_TRY(cudaMemsetAsync(const_cast<int32_t*>(tv.spread), 0, sizeof(int32_t) * ((n_img + 3) & ~3), st));
+  b200m::sort_chunk_stats_kernel<<<grid_for(R / 32, 256), 256, 0, st>>>(tv.snorm, k_per_image, k_stride, R / 32,
+                                                                      const_cast<int32_t*>(tv.cmin), const_cast<int32_t*>(tv.spread));
+  CUDA_TRY(cudaGetLastError());
+  g_prof.launches += 3;
+  return B200M_OK;
+}
+
 size_t b200m_workspace_bytes(int64_t k_stride, int64_t n_pairs) {
   if (k_stride <= 0 || n_pairs <= 0) return 256;
   return carve(nullptr, nullptr, batch_pairs(k_stride, n_pairs), k_stride);
@@ -388,43 +531,124 @@ int b200m_knn2_u8(const uint8_t* bank, const int32_t* norm_table, const int32_t*
   return B200M_OK;
 }
 
-int b200m_match_pairs_u8(const uint8_t* bank, const int32_t* norm_table, const int32_t* k_per_image, int32_t n_img,
-                         int64_t k_stride, const int32_t* pairs, int64_t n_pairs, double ratio, int mutual,
-                         int32_t* out_query_idx, int32_t* out_train_idx, float* out_dist, int32_t* out_count,
-                         int64_t cap, void* workspace, size_t workspace_bytes, void* stream) {
+int b200m_match_pairs_u8(const uint8_t* bank, const int32_t* norm_table, const uint8_t* sorted_bank,
+                         const int32_t* sort_table, const int32_t* k_per_image, int32_t n_img, int64_t k_stride,
+                         const int32_t* pairs, int64_t n_pairs, double ratio, int mutual, int32_t* out_query_idx,
+                         int32_t* out_train_idx, float* out_dist, int32_t* out_count, int64_t cap, void* workspace,
+                         size_t workspace_bytes, void* stream) {
   int rc = check_common(bank, norm_table, k_per_image, n_img, k_stride, pairs, n_pairs);
   if (rc) return rc;
   if (n_pairs == 0) return B200M_OK;
   if (!out_query_idx || !out_train_idx || !out_dist || !out_count || !workspace || cap <= 0)
     return fail(B200M_E_BAD_ARG, "null output / workspace or cap <= 0%s");
   if (workspace_bytes < b200m_workspace_bytes(k_stride, n_pairs)) return fail(B200M_E_WORKSPACE, "workspace too small%s");
+  if ((sorted_bank == nullptr) != (sort_table == nullptr))
+    return fail(B200M_E_BAD_ARG, "sorted_bank and sort_table must be given together%s");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int64_t B = batch_pairs(k_stride, n_pairs);
   Workspace w;
   carve(&w, workspace, B, k_stride);
-  CUtensorMap tmap_bank, tmap_gq, tmap_gt;
+  CUtensorMap tmap_bank, tmap_sbank, tmap_gq, tmap_gt;
   rc = make_row_tmap(&tmap_bank, bank, static_cast<uint64_t>(n_img) * k_stride);
   if (rc) return rc;
   rc = make_row_tmap(&tmap_gq, w.gath_q, static_cast<uint64_t>(B) * k_stride);
   if (rc) return rc;
   rc = make_row_tmap(&tmap_gt, w.gath_t, static_cast<uint64_t>(B) * k_stride);
   if (rc) return rc;
+  const int do_mutual = mutual ? 1 : 0;
+
+  // ---------------------------------------------------------------- pipeline 2: chunk sweep on the sorted bank
+  if (g_opt.pipeline == 2 && sorted_bank && g_opt.epilogue != 0) {
+    rc = make_row_tmap(&tmap_sbank, sorted_bank, static_cast<uint64_t>(n_img) * k_stride);
+    if (rc) return rc;
+    const SortTable tv = sort_table_view(sort_table, n_img, k_stride);
+    const int do_ratio = ratio > 0.0 ? 1 : 0;
+    for (int64_t p0 = 0; p0 < n_pairs; p0 += B) {
+      const int64_t nb = (n_pairs - p0 < B) ? (n_pairs - p0) : B;
+      const int32_t* pb = pairs + 2 * p0;
+      b200m::ChunkParams cp;
+      cp.cmin = tv.cmin;
+      cp.k_per_image = k_per_image;
+      cp.pairs = pb;
+      cp.k_stride = k_stride;
+      cp.n_pairs = static_cast<int32_t>(nb);
+      cp.blocks_per_pair = static_cast<int32_t>(k_stride / b200m::kRows);
+      cp.rowres = w.rowres;
+      cp.peak = g_opt.epilogue == 2 ? 1 : 0;
+      rc = launch_chunk_sweep(tmap_sbank, cp, sweep_grid(nb * cp.blocks_per_pair), st);
+      if (rc) return rc;
+      CUDA_TRY(cudaMemsetAsync(w.fb_count, 0, sizeof(int32_t) * nb, st));
+      b200m::RefineParams rp;
+      rp.bank = bank;
+      rp.sbank = sorted_bank;
+      rp.sqnorm = norm_table;
+      rp.perm = tv.perm;
+      rp.inv = tv.inv;
+      rp.snorm = tv.snorm;
+      rp.spread = tv.spread;
+      rp.k_per_image = k_per_image;
+      rp.pairs = pb;
+      rp.k_stride = k_stride;
+      rp.rowres_s = w.rowres;
+      rp.rowres_o = w.rowres_o;
+      rp.fb_count = w.fb_count;
+      rp.fb_q = w.fb_q;
+      rp.fb_desc = w.gath_q;
+      rp.ratio = ratio;
+      {
+        ProfScope ps(&g_prof.refine, st);
+        dim3 grid(static_cast<unsigned>((k_stride + b200m::kRefineThreads - 1) / b200m::kRefineThreads), static_cast<unsigned>(nb));
+        b200m::refine_kernel<<<grid, b200m::kRefineThreads, 0, st>>>(rp);
+      }
+      CUDA_TRY(cudaGetLastError());
+      // exact fallback for the rows the bounds could not settle (usually none: the kernel finds empty lists)
+      b200m::SweepParams sp = base_params(norm_table, n_img, k_per_image, k_stride, pb, nb, w);
+      rc = launch_sweep<b200m::kTop1G>(tmap_gq, tmap_gq, tmap_bank, sp, sweep_grid(nb * sp.blocks_per_pair), st);
+      if (rc) return rc;
+      {
+        ProfScope ps(&g_prof.select, st);
+        b200m::select2_kernel<1024><<<static_cast<unsigned>(nb), 1024, 0, st>>>(
+            w.rowres_o, pb, k_per_image, k_stride, ratio, bank, norm_table, do_mutual, w.cand_q, w.cand_t, w.cand_d,
+            w.cand_thr_mut, w.cand_rslot, w.cand_count, w.cand_thr_ratio, w.cand_excl, w.cand_count_a, w.gath_q, w.gath_t);
+      }
+      CUDA_TRY(cudaGetLastError());
+      if (do_ratio || do_mutual) {
+        sp.do_ratio = do_ratio;
+        sp.do_mutual = do_mutual;
+        sp.cand_count_r = w.cand_count_a;
+        sp.cand_excl = w.cand_excl;
+        rc = launch_sweep<b200m::kVerify>(tmap_gq, tmap_gt, tmap_bank, sp, sweep_grid(nb * sp.blocks_per_pair * 2), st);
+        if (rc) return rc;
+      }
+      {
+        ProfScope ps(&g_prof.emit, st);
+        b200m::emit_kernel<1024><<<static_cast<unsigned>(nb), 1024, 0, st>>>(
+            w.cand_q, w.cand_t, w.cand_d, w.viol_ratio, w.viol_mut, w.cand_count, w.cand_rslot, k_stride, do_ratio,
+            do_mutual, out_query_idx + p0 * cap, out_train_idx + p0 * cap, out_dist + p0 * cap, out_count + p0, cap);
+      }
+      CUDA_TRY(cudaGetLastError());
+    }
+    return B200M_OK;
+  }
+
+  // ---------------------------------------------------------------- pipelines 0 / 1 (original bank only)
   // pipeline 1: top-1 sweep, the Lowe test is settled by a verify sweep over the candidates;
   // pipeline 0 (and the debug epilogue): exact top-2 sweep, only the mutual check is verified.
   const bool exact2 = g_opt.pipeline == 0 || g_opt.epilogue == 0;
   const int do_ratio = (!exact2 && ratio > 0.0) ? 1 : 0;
-  const int do_mutual = mutual ? 1 : 0;
   for (int64_t p0 = 0; p0 < n_pairs; p0 += B) {
     const int64_t nb = (n_pairs - p0 < B) ? (n_pairs - p0) : B;
     const int32_t* pb = pairs + 2 * p0;
     b200m::SweepParams sp = base_params(norm_table, n_img, k_per_image, k_stride, pb, nb, w);
     rc = sweep_rows(tmap_bank, sp, exact2, st);
     if (rc) return rc;
-    b200m::select_kernel<1024><<<static_cast<unsigned>(nb), 1024, 0, st>>>(
-        w.rowres, pb, k_per_image, k_stride, ratio, exact2 ? 1 : 0, bank, norm_table, do_ratio, do_mutual, w.cand_q,
-        w.cand_t, w.cand_d, w.cand_thr_ratio, w.cand_thr_mut, w.cand_count, w.gath_q, w.gath_t);
+    {
+      ProfScope ps(&g_prof.select, st);
+      b200m::select_kernel<1024><<<static_cast<unsigned>(nb), 1024, 0, st>>>(
+          w.rowres, pb, k_per_image, k_stride, ratio, exact2 ? 1 : 0, bank, norm_table, do_ratio, do_mutual, w.cand_q,
+          w.cand_t, w.cand_d, w.cand_thr_ratio, w.cand_thr_mut, w.cand_count, w.gath_q, w.gath_t);
+    }
     CUDA_TRY(cudaGetLastError());
-    ++g_prof.launches;
     if (do_ratio || do_mutual) {
       sp.do_ratio = do_ratio;
       sp.do_mutual = do_mutual;
@@ -432,11 +656,13 @@ int b200m_match_pairs_u8(const uint8_t* bank, const int32_t* norm_table, const i
       rc = launch_any<b200m::kVerify>(tmap_gq, tmap_gt, tmap_bank, sp, grid, st);
       if (rc) return rc;
     }
-    b200m::emit_kernel<1024><<<static_cast<unsigned>(nb), 1024, 0, st>>>(
-        w.cand_q, w.cand_t, w.cand_d, w.viol_ratio, w.viol_mut, w.cand_count, k_stride, do_ratio, do_mutual,
-        out_query_idx + p0 * cap, out_train_idx + p0 * cap, out_dist + p0 * cap, out_count + p0, cap);
+    {
+      ProfScope ps(&g_prof.emit, st);
+      b200m::emit_kernel<1024><<<static_cast<unsigned>(nb), 1024, 0, st>>>(
+          w.cand_q, w.cand_t, w.cand_d, w.viol_ratio, w.viol_mut, w.cand_count, nullptr, k_stride, do_ratio, do_mutual,
+          out_query_idx + p0 * cap, out_train_idx + p0 * cap, out_dist + p0 * cap, out_count + p0, cap);
+    }
     CUDA_TRY(cudaGetLastError());
-    ++g_prof.launches;
   }
   return B200M_OK;
 }
@@ -476,8 +702,29 @@ int b200m_profile_read(double* first_sweep_ms, double* verify_sweep_ms, int64_t*
   if (launches) *launches = g_prof.launches;
   g_prof.first.clear();
   g_prof.verify.clear();
+  g_prof.fallback.clear();
+  g_prof.refine.clear();
+  g_prof.select.clear();
+  g_prof.emit.clear();
   g_prof.used = 0;
   g_prof.launches = 0;
+  return B200M_OK;
+}
+
+int b200m_profile_detail(double* out_ms, int n) {
+  if (!out_ms || n < 6) return fail(B200M_E_BAD_ARG, "out_ms must hold 6 doubles%s");
+  std::vector<std::pair<int, int>>* lists[6] = {&g_prof.first, &g_prof.verify, &g_prof.fallback,
+                                                &g_prof.refine, &g_prof.select, &g_prof.emit};
+  for (int i = 0; i < 6; ++i) {
+    double a = 0.0;
+    for (auto& pr : *lists[i]) {
+      float ms = 0.f;
+      CUDA_TRY(cudaEventSynchronize(g_prof.pool[pr.second]));
+      CUDA_TRY(cudaEventElapsedTime(&ms, g_prof.pool[pr.first], g_prof.pool[pr.second]));
+      a += ms;
+    }
+    out_ms[i] = a;
+  }
   return B200M_OK;
 }
 

@@ -187,8 +187,8 @@ template <int kBlock>
 __global__ void __launch_bounds__(kBlock)
 emit_kernel(const int32_t* __restrict__ cand_q, const int32_t* __restrict__ cand_t,
             const float* __restrict__ cand_d, const int32_t* __restrict__ viol_ratio,
-            const int32_t* __restrict__ viol_mut, const int32_t* __restrict__ cand_count, int64_t k_stride,
-            int use_ratio, int use_mutual, int32_t* __restrict__ out_q, int32_t* __restrict__ out_t,
+            const int32_t* __restrict__ viol_mut, const int32_t* __restrict__ cand_count,
+            const int32_t* __restrict__ cand_rslot, int64_t k_stride, int use_ratio, int use_mutual, int32_t* __restrict__ out_q, int32_t* __restrict__ out_t,
             float* __restrict__ out_d, int32_t* __restrict__ out_count, int64_t cap) {
   __shared__ int warp_sums[kBlock / 32];
   __shared__ int running;
@@ -201,7 +201,11 @@ emit_kernel(const int32_t* __restrict__ cand_q, const int32_t* __restrict__ cand
   for (int s0 = 0; s0 < n; s0 += kBlock) {
     const int s = s0 + threadIdx.x;
     bool keep = s < n;
-    if (keep && use_ratio) keep = viol_ratio[base + s] == 0;
+    if (keep && use_ratio) {
+      // pipeline 2 keeps the rows with an open Lowe test in a list of their own (slot in cand_rslot, -1 = settled)
+      const int rs = cand_rslot ? cand_rslot[base + s] : s;
+      if (rs >= 0) keep = viol_ratio[base + rs] == 0;
+    }
     if (keep && use_mutual) keep = viol_mut[base + s] == 0;
     const int slot = block_compact_slot<kBlock>(keep, warp_sums, &running);
     if (keep && slot < cap) {

@@ -1,0 +1,234 @@
+// Refinement of the chunk sweep (pipeline 2): turns the per-row chunk bounds (L1, g1, L2) of
+// chunk_sweep_kernel into exact answers, row by row, in ORIGINAL query order.
+//
+// For a query row with squared norm na the sweep guarantees, in score units (d^2 - na):
+//   * every train column of chunk g1 scores >= L1, every column outside g1 scores >= L2,
+//   * chunk g1 holds a column scoring <= L1 + spread, another chunk one scoring <= L2 + spread
+//     (spread = largest norm spread of a chunk of the train image; tiny after the norm sort).
+// Step 1 (all rows, no descriptor traffic): the Lowe test needs a second neighbour outside the
+//   radius D*(d1); d1^2 >= L1 + na and two distinct columns lie within L2 + spread + na, so
+//   L2 + spread + na < D*(L1 + na) settles "rejected" for the bulk of the rows.
+// Step 2 (the remaining rows, one warp per row): the 32 columns of chunk g1 are evaluated exactly
+//   (dp4a): best (score, original index), runner-up inside the chunk. If best < L2 the row's nearest
+//   neighbour is known exactly, and the Lowe test is settled by the chunk's runner-up and L2 in all
+//   but a sliver of cases; the sliver goes to the ratio verify sweep, rows with best >= L2 to the
+//   exact fallback sweep (sweep_kernel<kTop1G>).
+// Output per (pair, original query row): int4 (d1^2, i1 (original train row), d2^2 bound, state).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "match_finalize.cuh"
+
+namespace b200m {
+
+enum RowStateCode {
+  kRowReject = 0,        // cannot be a match
+  kRowPass = 1,          // nearest neighbour exact, Lowe test settled: passed
+  kRowNeedRatio = 2,     // nearest neighbour exact, Lowe test needs the verify sweep
+  kRowFallback = 3       // written by the fallback sweep: (d1^2, i1, upper bound of d2^2)
+};
+
+struct RefineParams {
+  const uint8_t* bank;          // original order (query rows are read from here)
+  const uint8_t* sbank;         // norm-sorted copy (train chunks are read from here)
+  const int32_t* sqnorm;        // original order
+  const int32_t* perm;          // sorted position -> original row
+  const int32_t* inv;           // original row -> sorted position
+  const int32_t* snorm;         // sorted norms
+  const int32_t* spread;        // [n_img] largest chunk spread
+  const int32_t* k_per_image;
+  const int32_t* pairs;
+  int64_t k_stride;
+  const int4* rowres_s;         // chunk sweep output (sorted query rows)
+  int4* rowres_o;               // out (original query rows)
+  int32_t* fb_count;            // [n_pairs] rows sent to the fallback sweep (zeroed by the caller)
+  int32_t* fb_q;                // [n_pairs, k_stride] their original query rows
+  uint8_t* fb_desc;             // [n_pairs, k_stride, 128] their descriptors (rows of the fallback sweep)
+  double ratio;
+};
+
+constexpr int kRefineThreads = 256;
+constexpr int kBigScore = 1 << 28;
+
+__global__ void __launch_bounds__(kRefineThreads)
+refine_kernel(const RefineParams p) {
+  const int pair = blockIdx.y;
+  const int qi = p.pairs[2 * pair], ti = p.pairs[2 * pair + 1];
+  const int kq = p.k_per_image[qi], kt = p.k_per_image[ti];
+  const int lane = threadIdx.x & 31;
+  const int r_warp0 = (blockIdx.x * kRefineThreads + threadIdx.x) & ~31;
+  if (r_warp0 >= kq) return;
+  const int r = r_warp0 + lane;
+  const int64_t base = static_cast<int64_t>(pair) * p.k_stride;
+  const int64_t qbase = static_cast<int64_t>(qi) * p.k_stride;
+  const int64_t tbase = static_cast<int64_t>(ti) * p.k_stride;
+  const bool use_ratio = p.ratio > 0.0;
+
+  int4 v = make_int4(kBigScore, 0, kBigScore, 0);
+  int na = 0;
+  bool need = false;
+  if (r < kq && kt > 0) {
+    na = p.sqnorm[qbase + r];
+    v = p.rowres_s[base + p.inv[qbase + r]];
+    need = true;
+    if (use_ratio) {
+      if (kt < 2) {
+        need = false;                                   // no second neighbour: dropped by the ratio test
+      } else if (v.z < kBigScore) {
+        const int spread = p.spread[ti];
+        const int d1lb = max(v.x + na, 0);
+        const int dlow = ratio_radius_sq(dist_from_sq(d1lb), p.ratio);
+        const long long ub2 = static_cast<long long>(v.z) + spread + na;
+        if (ub2 < dlow) need = false;                   // a second column lies inside the radius for sure
+      }
+    }
+  }
+  int4 out = make_int4(0, -1, 0, kRowReject);
+  bool fallback = false;
+
+  unsigned todo = __ballot_sync(0xffffffffu, need);
+  while (todo) {
+    const int src = __ffs(todo) - 1;
+    todo &= todo - 1;
+    const int rr = r_warp0 + src;
+    const int g1 = __shfl_sync(0xffffffffu, v.y, src);
+    const int c = g1 * 32 + lane;                        // sorted train column of this lane
+    int s = 0x7fffffff, orig = 0x7fffffff;
+    if (c < kt) {
+      const uint4* colp = reinterpret_cast<const uint4*>(p.sbank + (tbase + c) * 128);
+      const uint4* rowp = reinterpret_cast<const uint4*>(p.bank + (qbase + rr) * 128);
+      uint32_t dot = 0;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const uint4 a = __ldg(rowp + i), b = __ldg(colp + i);
+        dot = __dp4a(a.x, b.x, dot);
+        dot = __dp4a(a.y, b.y, dot);
+        dot = __dp4a(a.z, b.z, dot);
+        dot = __dp4a(a.w, b.w, dot);
+      }
+      s = p.snorm[tbase + c] - 2 * static_cast<int>(dot);
+      orig = p.perm[tbase + c];
+    }
+    // best by (score, original index), then the runner-up among the other lanes
+    int bs = s, bo = orig;
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) {
+      const int os = __shfl_xor_sync(0xffffffffu, bs, off), oo = __shfl_xor_sync(0xffffffffu, bo, off);
+      if (os < bs || (os == bs && oo < bo)) { bs = os; bo = oo; }
+    }
+    int s2 = (orig == bo) ? 0x7fffffff : s;
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) s2 = min(s2, __shfl_xor_sync(0xffffffffu, s2, off));
+    if (lane == src) {
+      // v = (L1, g1, L2): columns outside chunk g1 score >= L2
+      if (!(bs < v.z)) {
+        fallback = true;                                 // another chunk may hold the nearest (or an equal) column
+      } else {
+        const int d1 = bs + na;
+        int state = kRowPass;
+        if (use_ratio) {
+          const int thr = ratio_radius_sq(dist_from_sq(d1), p.ratio) - na;   // a second column scoring < thr spoils the test
+          if (s2 < thr) state = kRowReject;
+          else if (v.z >= thr) state = kRowPass;
+          else if (static_cast<long long>(v.z) + p.spread[ti] < thr) state = kRowReject;
+          else state = kRowNeedRatio;
+        }
+        out = make_int4(d1, bo, 0, state);
+      }
+    }
+  }
+  if (r < kq) {
+    if (fallback) {
+      const int slot = atomicAdd(p.fb_count + pair, 1);
+      p.fb_q[base + slot] = r;
+      const uint4* src = reinterpret_cast<const uint4*>(p.bank + (qbase + r) * 128);
+      uint4* dst = reinterpret_cast<uint4*>(p.fb_desc + (base + slot) * 128);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) dst[i] = src[i];
+      // rowres_o of this row is written by the fallback sweep
+    } else {
+      p.rowres_o[base + r] = out;
+    }
+  }
+}
+
+// Candidate selection of pipeline 2, ascending original query order (one CTA per pair).
+//   list B (all surviving rows): cand_q / cand_t / cand_d / cand_thr_mut (+ gathered train rows for the
+//           mutual verify sweep) and cand_rslot = the row's slot in list A or -1;
+//   list A (rows whose Lowe test is still open): thr_ratio / excl (+ gathered query rows).
+template <int kBlock>
+__global__ void __launch_bounds__(kBlock)
+select2_kernel(const int4* __restrict__ rowres_o, const int32_t* __restrict__ pairs,
+               const int32_t* __restrict__ k_per_image, int64_t k_stride, double ratio,
+               const uint8_t* __restrict__ bank, const int32_t* __restrict__ sqnorm, int gather_t,
+               int32_t* __restrict__ cand_q, int32_t* __restrict__ cand_t, float* __restrict__ cand_d,
+               int32_t* __restrict__ cand_thr_mut, int32_t* __restrict__ cand_rslot, int32_t* __restrict__ cand_count,
+               int32_t* __restrict__ a_thr_ratio, int32_t* __restrict__ a_excl, int32_t* __restrict__ a_count,
+               uint8_t* __restrict__ gath_q, uint8_t* __restrict__ gath_t) {
+  __shared__ int warp_sums[kBlock / 32];
+  __shared__ int running_b, running_a;
+  const int pair = blockIdx.x;
+  const int qi = pairs[2 * pair], ti = pairs[2 * pair + 1];
+  const int kq = k_per_image[qi];
+  const int kt = k_per_image[ti];
+  if (threadIdx.x == 0) { running_b = 0; running_a = 0; }
+  __syncthreads();
+  const int64_t base = static_cast<int64_t>(pair) * k_stride;
+  const int64_t qbase = static_cast<int64_t>(qi) * k_stride;
+  const int64_t tbase = static_cast<int64_t>(ti) * k_stride;
+  for (int r0 = 0; r0 < kq && kt > 0; r0 += kBlock) {
+    const int r = r0 + threadIdx.x;
+    bool keep = false, open = false;
+    int4 v = make_int4(0, -1, 0, kRowReject);
+    float d1f = 0.f;
+    if (r < kq) {
+      v = rowres_o[base + r];
+      const bool has1 = v.y >= 0 && v.y < kt;
+      if (has1 && v.w != kRowReject) {
+        d1f = dist_from_sq(v.x);
+        if (v.w == kRowFallback) {
+          // (d1^2, i1, upper bound of d2^2): rows passing against the bound are a superset of the survivors
+          if (ratio > 0.0) {
+            keep = kt >= 2 && static_cast<double>(d1f) < ratio * static_cast<double>(dist_from_sq(v.z));
+            open = keep;
+          } else {
+            keep = true;
+          }
+        } else {
+          keep = true;
+          open = v.w == kRowNeedRatio;
+        }
+      }
+    }
+    const int slot = block_compact_slot<kBlock>(keep, warp_sums, &running_b);
+    const int aslot = block_compact_slot<kBlock>(open, warp_sums, &running_a);
+    if (keep) {
+      const int64_t o = base + slot;
+      cand_q[o] = r;
+      cand_t[o] = v.y;
+      cand_d[o] = d1f;
+      cand_thr_mut[o] = v.x - sqnorm[tbase + v.y];
+      cand_rslot[o] = open ? aslot : -1;
+      if (gather_t) {
+        const uint4* src = reinterpret_cast<const uint4*>(bank + (tbase + v.y) * 128);
+        uint4* dst = reinterpret_cast<uint4*>(gath_t + o * 128);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) dst[i] = src[i];
+      }
+    }
+    if (open) {
+      const int64_t o = base + aslot;
+      a_thr_ratio[o] = ratio_radius_sq(d1f, ratio) - sqnorm[qbase + r];
+      a_excl[o] = v.y;
+      const uint4* src = reinterpret_cast<const uint4*>(bank + (qbase + r) * 128);
+      uint4* dst = reinterpret_cast<uint4*>(gath_q + o * 128);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) dst[i] = src[i];
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) { cand_count[pair] = running_b; a_count[pair] = running_a; }
+}
+
+}  // namespace b200m

@@ -33,6 +33,8 @@
 //                     violated when another train row lies inside the Lowe-ratio radius;
 //              mutual rows = the candidates' train descriptors (gathered), columns = the query
 //                     image: violated when some query is nearer (or equally near, lower index).
+//   kTop1G   kTop1 over GATHERED query rows (the exact fallback of the chunk pipeline): rows come from a
+//            gathered buffer, results go to the rows' original slots in (d1^2, i1, d2^2 bound, state) form.
 //   kTop2Exact / kPeak  debugging (every element through the insertion) and MMA-only ceiling.
 #pragma once
 #include "ptx_sm100.cuh"
@@ -56,7 +58,9 @@ constexpr int kPadNorm = 1 << 23;   // > 128*255^2: norm of a padding row
 constexpr int kBig = 1 << 28;       // "no candidate yet" score; 2*acc + kBig cannot overflow
 constexpr uint32_t kEpiBarrier = 1; // named barrier of the 16 epilogue warps
 
-enum SweepKind { kTop2 = 0, kVerify = 1, kPeak = 2, kTop2Exact = 3, kTop1 = 4 };
+enum SweepKind { kTop2 = 0, kVerify = 1, kPeak = 2, kTop2Exact = 3, kTop1 = 4, kTop1G = 5 };
+
+__host__ __device__ constexpr bool is_top1(int kind) { return kind == kTop1 || kind == kTop1G; }
 
 struct NormSlot {
   int32_t nb[kTT];      // squared norms of the tile's 256 columns
@@ -89,14 +93,20 @@ struct SweepParams {
   // bound of the second-nearest squared distance and i2 is unused
   int4* rowres;
   // kVerify: candidates of the first sweep, slot s of pair p lives at p * k_stride + s
-  const int32_t* cand_count;      // [n_pairs]
+  const int32_t* cand_count;      // [n_pairs] candidates of the mutual check
+  const int32_t* cand_count_r;    // [n_pairs] candidates of the ratio check (same list in pipeline 1)
   const int32_t* cand_q;          // query row of the candidate
   const int32_t* cand_t;          // its nearest train row
+  const int32_t* cand_excl;       // ratio check: the train row that is allowed inside the radius
   const int32_t* cand_thr_ratio;  // ratio check: a train column with score < this kills the row
   const int32_t* cand_thr_mut;    // mutual check: d1^2 - |t1|^2, the score a query must beat
   int32_t* viol_ratio;            // out: 1 when the ratio test fails
   int32_t* viol_mut;              // out: 1 when a better (or equal, lower-index) query exists
   int32_t do_ratio, do_mutual;    // which of the two checks to run
+  // kTop1G: rows gathered by the refine kernel, slot s of pair p at p * k_stride + s
+  const int32_t* fb_count;        // [n_pairs]
+  const int32_t* fb_q;            // original query row of the gathered row
+  int4* rowres_o;                 // out, original query rows: (d1^2, i1, d2^2 bound, kRowFallback)
 };
 
 struct ItemInfo {
@@ -126,11 +136,16 @@ __device__ __forceinline__ ItemInfo decode_item(const SweepParams& p, int item) 
   const int kt = __ldg(p.k_per_image + ti);
   if (kKind == kVerify) {
     const bool on = it.check == 0 ? p.do_ratio != 0 : p.do_mutual != 0;
-    const int s = on ? __ldg(p.cand_count + it.pair) : 0;
+    const int s = on ? __ldg((it.check == 0 ? p.cand_count_r : p.cand_count) + it.pair) : 0;
     it.n_rows = s - it.blk * kRows;
     it.n_cols = it.check == 0 ? kt : kq;
     it.col_img = it.check == 0 ? ti : qi;
     it.row_img_row0 = static_cast<int>(it.pair * p.k_stride + it.blk * kRows);   // gathered buffers
+  } else if (kKind == kTop1G) {
+    it.n_rows = __ldg(p.fb_count + it.pair) - it.blk * kRows;
+    it.n_cols = kt;
+    it.col_img = ti;
+    it.row_img_row0 = static_cast<int>(it.pair * p.k_stride + it.blk * kRows);   // gathered buffer
   } else {
     it.n_rows = kq - it.blk * kRows;
     it.n_cols = kt;
@@ -233,7 +248,7 @@ __device__ __forceinline__ void process16(const int (&v)[16], uint32_t nb_s, int
     for (int k = 0; k < 4; ++k) {
       if (g[k] > T) {
         const int4 nb4 = lds_v4(nb_s + 16 * k);
-        if (kKind == kTop1) {
+        if (is_top1(kKind)) {
           // packed (score << 2 | j) minimum: IMADs on the FMA pipe, two integer minima on the ALU pipe
           const int ka = (nb4.x * 4 + 0) - 8 * v[4 * k], kb = (nb4.y * 4 + 1) - 8 * v[4 * k + 1];
           const int kc = (nb4.z * 4 + 2) - 8 * v[4 * k + 2], kd = (nb4.w * 4 + 3) - 8 * v[4 * k + 3];
@@ -392,7 +407,7 @@ sweep_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
       if (kKind == kVerify && active && rl < it.n_rows) {
         if (it.check == 0) {
           st.thr = __ldg(p.cand_thr_ratio + orow);
-          st.excl = __ldg(p.cand_t + orow);
+          st.excl = __ldg(p.cand_excl + orow);
         } else {
           st.thr = __ldg(p.cand_thr_mut + orow);
           st.tie = __ldg(p.cand_q + orow);
@@ -420,14 +435,14 @@ sweep_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
         mbar_wait(&sm.n_full[ns], nph);
         if (active) {
           const NormSlot& nsl = sm.norms[ns];
-          if (kKind == kTop2 || kKind == kTop1) {
+          if (kKind == kTop2 || is_top1(kKind)) {
             // Bound from the other column half of this row. kTop2: the union's second best is
             // <= min(max(s1, s1'), s2'); kTop1: the union's best is <= s1'. Anything at or above the
             // bound (strictly above on ties, the halves interleave in column order) cannot matter.
             // Racy reads are fine: published values only ever decrease.
             const long long raw = *reinterpret_cast<const volatile long long*>(partner);
             const int ox = static_cast<int>(raw), oy = static_cast<int>(raw >> 32);
-            st.lim = min(st.lim, (kKind == kTop1 ? ox : min(max(st.s1, ox), oy)) + 1);
+            st.lim = min(st.lim, (is_top1(kKind) ? ox : min(max(st.s1, ox), oy)) + 1);
           }
           mbar_wait(&sm.t_full[acc], t_it & 1);
           tc_fence_after();
@@ -476,7 +491,7 @@ sweep_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
           // merge the two halves; columns of the halves interleave tile by tile, so ties are
           // resolved on the column index explicitly
           int r1s, r1i, r2s, r2i;
-          if (kKind == kTop1) {
+          if (is_top1(kKind)) {
             const bool other = lex_less(o.x, o.y, st.s1, st.i1);
             r1s = other ? o.x : st.s1;
             r1i = other ? o.y : st.i1;
@@ -489,8 +504,15 @@ sweep_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
             r1s = st.s1; r1i = st.i1;
             if (lex_less(o.x, o.y, st.s2, st.i2)) { r2s = o.x; r2i = o.y; } else { r2s = st.s2; r2i = st.i2; }
           }
-          const int na = __ldg(p.sqnorm + it.row_img_row0 + rl);
-          p.rowres[orow] = make_int4(r1s + na, r1i, r2s + na, r2i);
+          if (kKind == kTop1G) {
+            const int qi = __ldg(p.pairs + 2 * it.pair);
+            const int qrow = __ldg(p.fb_q + orow);
+            const int na = __ldg(p.sqnorm + qi * p.k_stride + qrow);
+            p.rowres_o[static_cast<int64_t>(it.pair) * p.k_stride + qrow] = make_int4(r1s + na, r1i, r2s + na, 3);
+          } else {
+            const int na = __ldg(p.sqnorm + it.row_img_row0 + rl);
+            p.rowres[orow] = make_int4(r1s + na, r1i, r2s + na, r2i);
+          }
         }
       }
     }

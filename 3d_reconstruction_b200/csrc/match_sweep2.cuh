@@ -183,7 +183,7 @@ sweep_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       if (kKind == kVerify && row_ok) {
         if (it.check == 0) {
           st.thr = __ldg(p.cand_thr_ratio + orow);
-          st.excl = __ldg(p.cand_t + orow);
+          st.excl = __ldg(p.cand_excl + orow);
         } else {
           st.thr = __ldg(p.cand_thr_mut + orow);
           st.tie = __ldg(p.cand_q + orow);

@@ -119,8 +119,10 @@ def match_pairs(bank: DescriptorBank, pairs, ratio: float = 0.75, mutual: bool =
     ws = workspace if workspace is not None else _workspace(bank, P)
     with torch.cuda.device(bank.device):
         st = torch.cuda.current_stream().cuda_stream
+        sd = bank.sorted_desc.data_ptr() if bank.sorted_desc is not None else None
+        stab = bank.sort_table.data_ptr() if bank.sort_table is not None else None
         _lib.check(_lib.lib().b200m_match_pairs_u8(
-            bank.desc.data_ptr(), bank.sqnorm.data_ptr(), bank.k_per_image.data_ptr(), bank.n_img, bank.k_stride,
+            bank.desc.data_ptr(), bank.sqnorm.data_ptr(), sd, stab, bank.k_per_image.data_ptr(), bank.n_img, bank.k_stride,
             pairs_t.data_ptr(), P, float(ratio if ratio is not None else 0.0), int(bool(mutual)),
             out.query_idx.data_ptr(), out.train_idx.data_ptr(), out.dist.data_ptr(), out.count.data_ptr(),
             int(out.cap), ws.data_ptr(), ws.numel(), st))

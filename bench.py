@@ -257,13 +257,15 @@ def main():
     roofline = {
         "bound": "tensor", "achieved": achieved, "peak": int8_peak, "unit": "TFLOP/s", "frac": achieved / int8_peak,
         "traffic": None,
-        "kernel": "b200m::sweep_kernel<kTop1>",
+        "kernel": "b200m::chunk_sweep_kernel",
         "peak_source": f"2 x bf16_tflops_sustained of MEASURED_PEAKS.json ({peak_kind}): int8 tcgen05 rate is twice the bf16 rate; "
                        "nominal dense int8 is 4500",
         "frac_of_nominal_4500": achieved / 4500.0,
         "launch_ms": sweep_ms_per_launch, "launches_timed": prof["first_sweeps"],
         "share_of_step": prof["first_sweep_ms"] / (e0.elapsed_time(e1)),
         "verify_share_of_step": prof["verify_sweep_ms"] / (e0.elapsed_time(e1)),
+        "other_kernels_ms_per_step": {k: prof[k] / args.steps for k in
+                                      ("verify_sweep_ms", "fallback_sweep_ms", "refine_ms", "select_ms", "emit_ms")},
     }
     gpu_launches = prof["launches"]
 

@@ -71,6 +71,19 @@ int64_t b200m_norm_table_elems(int32_t n_img, int64_t k_stride);
 int b200m_bank_prepare_u8(uint8_t* bank, int32_t n_img, int64_t k_stride,
                           const int32_t* k_per_image, int32_t* norm_table, void* stream);
 
+/* Norm-sorted copy of the bank for the default pipeline (the chunk sweep): per image the rows
+ * ordered by (squared norm, row), so that the 32 rows of a chunk have nearly equal norms and the
+ * epilogue can rank whole chunks by max(row.col) alone.
+ *   sorted_bank  uint8 [n_img, k_stride, 128]   (also used as sort scratch while the call runs)
+ *   sort_table   int32 [b200m_sort_table_elems]: perm (sorted position -> row) | inv (row -> sorted
+ *                position) | sorted norms | per-chunk minimum norm | per-image largest chunk spread
+ * Needs the norm table of b200m_bank_prepare_u8. The original bank stays in use (exact fallback,
+ * mutual check, outputs are in original row numbers). */
+int64_t b200m_sort_table_elems(int32_t n_img, int64_t k_stride);
+int b200m_bank_sort_u8(const uint8_t* bank, const int32_t* norm_table, const int32_t* k_per_image,
+                       int32_t n_img, int64_t k_stride,
+                       uint8_t* sorted_bank, int32_t* sort_table, void* stream);
+
 /* Scratch bytes needed to process `n_pairs` pairs of images with slab stride `k_stride`.
  * Pairs are processed in internal batches, so this saturates at a fixed batch size. */
 size_t b200m_workspace_bytes(int64_t k_stride, int64_t n_pairs);
@@ -94,9 +107,12 @@ int b200m_knn2_u8(const uint8_t* bank, const int32_t* norm_table, const int32_t*
  * neighbour and is dropped by the ratio test (cv2: the `for m, n in knn` unpack needs two).
  *   out_query_idx / out_train_idx / out_dist   [n_pairs, cap], ascending query index
  *   out_count  int32 [n_pairs]: matches FOUND; if > cap only the first cap were stored and the
- *              caller must treat the pair as overflowed (never silently truncated). */
-int b200m_match_pairs_u8(const uint8_t* bank, const int32_t* norm_table, const int32_t* k_per_image,
-                         int32_t n_img, int64_t k_stride,
+ *              caller must treat the pair as overflowed (never silently truncated).
+ *   sorted_bank / sort_table: outputs of b200m_bank_sort_u8, or both NULL (then the slower
+ *              pipeline 1 runs on the original bank alone). Results are identical either way. */
+int b200m_match_pairs_u8(const uint8_t* bank, const int32_t* norm_table,
+                         const uint8_t* sorted_bank, const int32_t* sort_table,
+                         const int32_t* k_per_image, int32_t n_img, int64_t k_stride,
                          const int32_t* pairs, int64_t n_pairs,
                          double ratio, int mutual,
                          int32_t* out_query_idx, int32_t* out_train_idx, float* out_dist,
@@ -106,7 +122,8 @@ int b200m_match_pairs_u8(const uint8_t* bank, const int32_t* norm_table, const i
 /* Tuning / introspection knobs (process-global, read at launch time).
  *   "epilogue"  0 = exact insertion of every element (debug), 1 = threshold-reject (default),
  *               2 = MMA-only ceiling measurement (results invalid)
- *   "pipeline"  1 = top-1 sweep + lazy ratio / mutual verify sweeps over the candidates (default),
+ *   "pipeline"  2 = chunk sweep on the norm-sorted bank + exact refine / fallback / verify (default),
+ *               1 = top-1 sweep + lazy ratio / mutual verify sweeps over the candidates,
  *               0 = exact top-2 sweep + lazy mutual verify sweep
  *   "grid"      number of persistent CTAs, 0 = one per SM (default)
  *   "batch"     pairs per internal batch, 0 = default
@@ -126,6 +143,9 @@ int b200m_compact_matches(const int32_t* query_idx, const int32_t* train_idx, co
  * the number of first-sweep launches, and the number of kernels launched by the library.
  * Blocks until the recorded events have completed. */
 int b200m_profile_read(double* first_sweep_ms, double* verify_sweep_ms, int64_t* first_sweeps, int64_t* launches);
+/* Call BEFORE b200m_profile_read: device ms per kernel class since the last read,
+ * out_ms[0..5] = first sweep, verify sweep, fallback sweep, refine, select, emit. */
+int b200m_profile_detail(double* out_ms, int n);
 
 /* Diagnostics: raw 128 x 256 int32 dot-product tile through the same TMA + tcgen05 path
  * (used by the self-test to validate descriptors/swizzle independently of the epilogue). */

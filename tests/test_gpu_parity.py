@@ -17,21 +17,80 @@ def _bits(x):
 
 
 DEFAULT_KERNEL = 3
+DEFAULT_PIPELINE = 2
 
 
-@pytest.fixture(scope="module", params=[(1, 1, 4), (1, 0, 4), (0, 0, 4), (1, 1, 3), (1, 0, 3), (0, 0, 3)],
-                ids=["pair_top1_verify", "pair_top2_reject", "pair_top2_exact", "top1_verify", "top2_reject", "top2_exact"])
+@pytest.fixture(scope="module", params=[(1, 2, 3), (1, 1, 4), (1, 0, 4), (0, 0, 4), (1, 1, 3), (1, 0, 3), (0, 0, 3)],
+                ids=["chunk_refine", "pair_top1_verify", "pair_top2_reject", "pair_top2_exact", "top1_verify", "top2_reject",
+                     "top2_exact"])
 def epi(pkg, request):
-    """(epilogue, pipeline, kernel): the top-1 sweep + verify sweeps, the top-2 threshold-reject sweep
-    with only the mutual verify, and the debug epilogue that sends every element through the insertion;
-    each on the CTA-pair kernel (cta_group::2) and on the single-CTA kernel."""
+    """(epilogue, pipeline, kernel): the default chunk sweep on the norm-sorted bank + refine + exact
+    fallback; the top-1 sweep + verify sweeps, the top-2 threshold-reject sweep with only the mutual
+    verify, and the debug epilogue that sends every element through the insertion, each on the CTA-pair
+    kernel (cta_group::2) and on the single-CTA kernel."""
     pkg.set_option("epilogue", request.param[0])
     pkg.set_option("pipeline", request.param[1])
     pkg.set_option("kernel", request.param[2])
     yield request.param
     pkg.set_option("epilogue", 1)
-    pkg.set_option("pipeline", 1)
+    pkg.set_option("pipeline", DEFAULT_PIPELINE)
     pkg.set_option("kernel", DEFAULT_KERNEL)
+
+
+def test_bank_sort(pkg):
+    """b200m_bank_sort_u8: rows ordered by (squared norm, row), padding last; perm / inv / chunk tables."""
+    rng = np.random.default_rng(5)
+    ks = [700, 3000, 1, 0, 2049]
+    arrays = [rng.integers(0, 256, size=(k, 128)).astype(np.uint8) for k in ks]
+    arrays[0][:300] = arrays[0][300:600]          # duplicate rows: equal norms keep their original order
+    arrays[1][:, 64:] = 0
+    bank = pkg.DescriptorBank.from_arrays(arrays)
+    torch.cuda.synchronize()
+    perm, inv, snorm, cmin, spread = [x.cpu().numpy() for x in bank.sort_views()]
+    norms = bank.norms().cpu().numpy()
+    desc = bank.desc.cpu().numpy()
+    sdesc = bank.sorted_desc.cpu().numpy()
+    for i, k in enumerate(ks):
+        exp = np.argsort(norms[i], kind="stable")
+        assert np.array_equal(perm[i], exp), i
+        assert np.array_equal(inv[i][perm[i]], np.arange(bank.k_stride))
+        assert np.array_equal(snorm[i], norms[i][exp])
+        assert np.array_equal(sdesc[i], desc[i][exp])
+        assert np.array_equal(cmin[i], snorm[i][::32])
+        if k:
+            assert (perm[i][:k] < k).all() and np.array_equal(np.sort(perm[i][:k]), np.arange(k))
+            sp = max(int(snorm[i][min(c + 31, k - 1)] - snorm[i][c]) for c in range(0, k, 32))
+            assert int(spread[i]) == sp, (i, int(spread[i]), sp)
+        else:
+            assert int(spread[i]) == 0
+
+
+def test_pipelines_agree_on_fallback_heavy_data(pkg):
+    """Small-alphabet descriptors (many exact ties, distances comparable to the norm spread of a chunk)
+    push most rows of the chunk pipeline through its exact fallback; results must not change."""
+    rng = np.random.default_rng(21)
+    q = rng.integers(0, 3, size=(900, 128)).astype(np.uint8)
+    t = rng.integers(0, 3, size=(1200, 128)).astype(np.uint8)
+    t[100:400] = q[200:500]                        # planted exact matches
+    t[500:520] = q[200:220]                        # ... some of them twice (ratio test must reject those)
+    bank = pkg.DescriptorBank.from_arrays([q, t])
+    res = {}
+    for pl in (2, 1):
+        pkg.set_option("pipeline", pl)
+        try:
+            res[pl] = [pkg.match_pairs(bank, [[0, 1], [1, 0]], ratio=r, mutual=m).to_lists() for r, m in
+                       [(0.75, True), (0.75, False), (0.0, True), (0.9, True)]]
+        finally:
+            pkg.set_option("pipeline", DEFAULT_PIPELINE)
+    n = 0
+    for a, b in zip(res[2], res[1]):
+        for x, y in zip(a, b):
+            assert all(np.array_equal(u, v) for u, v in zip(x, y))
+            n += len(x[0])
+    assert n > 500
+    for (a, b), (gq, gt, gd) in zip([(q, t), (t, q)], res[2][0]):
+        eq, et, ed = oracle_int.match(a, b, 0.75, True)
+        assert np.array_equal(gq, eq) and np.array_equal(gt, et) and np.array_equal(_bits(gd), _bits(ed))
 
 
 def test_debug_dot_tile(pkg):
