@@ -24,7 +24,9 @@ struct Options {
   int64_t epilogue = 1;
   int64_t grid = 0;
   int64_t batch = 0;
-  int64_t kernel = 3;     // 3 = single-CTA sweep (four 128x128 accumulators), 4 = CTA-pair sweep (cta_group::2)
+  // chunk sweep (pipeline 2): 5 = N256 MMAs / two accumulators (default), otherwise N128 MMAs / four accumulators;
+  // exact sweeps (pipelines 0 / 1, fallback, verify): 4 = CTA-pair kernel (cta_group::2), otherwise single-CTA
+  int64_t kernel = 5;
   // 2 = chunk sweep on the norm-sorted bank + refine + exact fallback (default, needs the sorted bank),
   // 1 = top-1 sweep + ratio/mutual verify sweeps, 0 = top-2 sweep + mutual verify
   int64_t pipeline = 2;
@@ -173,16 +175,27 @@ int launch_sweep(const CUtensorMap& tmap_a, const CUtensorMap& tmap_a2, const CU
 
 constexpr size_t kChunkSmemBytes = sizeof(b200m::ChunkSmem) + 1024;
 
+constexpr size_t kChunk256SmemBytes = sizeof(b200m::Chunk256Smem) + 1024;
+
 int launch_chunk_sweep(const CUtensorMap& tmap, const b200m::ChunkParams& cp, int grid, cudaStream_t st) {
   static thread_local bool attr_set = false;
   if (!attr_set) {
     CUDA_TRY(cudaFuncSetAttribute(b200m::chunk_sweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   static_cast<int>(kChunkSmemBytes)));
+    CUDA_TRY(cudaFuncSetAttribute(b200m::chunk_sweep256_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  static_cast<int>(kChunk256SmemBytes)));
+    CUDA_TRY(cudaFuncSetAttribute(b200m::chunk_sweep256_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  static_cast<int>(kChunk256SmemBytes)));
     attr_set = true;
   }
   {
     ProfScope ps(&g_prof.first, st);
-    b200m::chunk_sweep_kernel<<<grid, b200m::kThreads, kChunkSmemBytes, st>>>(tmap, cp);
+    if (g_opt.kernel == 5 && cp.peak)
+      b200m::chunk_sweep256_kernel<true><<<grid, b200m::kThreads256, kChunk256SmemBytes, st>>>(tmap, cp);
+    else if (g_opt.kernel == 5)
+      b200m::chunk_sweep256_kernel<false><<<grid, b200m::kThreads256, kChunk256SmemBytes, st>>>(tmap, cp);
+    else
+      b200m::chunk_sweep_kernel<<<grid, b200m::kThreads, kChunkSmemBytes, st>>>(tmap, cp);
   }
   CUDA_TRY(cudaGetLastError());
   return B200M_OK;
@@ -355,6 +368,7 @@ b200m::SweepParams base_params(const int32_t* norm_table, int32_t n_img, const i
   sp.cand_t = w.cand_t;
   sp.cand_excl = w.cand_t;
   sp.fb_count = w.fb_count;
+  sp.fb_total = nullptr;
   sp.fb_q = w.fb_q;
   sp.rowres_o = w.rowres_o;
   sp.cand_thr_ratio = w.cand_thr_ratio;
@@ -577,7 +591,7 @@ int b200m_match_pairs_u8(const uint8_t* bank, const int32_t* norm_table, const u
       cp.peak = g_opt.epilogue == 2 ? 1 : 0;
       rc = launch_chunk_sweep(tmap_sbank, cp, sweep_grid(nb * cp.blocks_per_pair), st);
       if (rc) return rc;
-      CUDA_TRY(cudaMemsetAsync(w.fb_count, 0, sizeof(int32_t) * nb, st));
+      CUDA_TRY(cudaMemsetAsync(w.fb_count, 0, sizeof(int32_t) * (B + 64), st));   // per-pair counts + the batch total at [B]
       b200m::RefineParams rp;
       rp.bank = bank;
       rp.sbank = sorted_bank;
@@ -592,6 +606,7 @@ int b200m_match_pairs_u8(const uint8_t* bank, const int32_t* norm_table, const u
       rp.rowres_s = w.rowres;
       rp.rowres_o = w.rowres_o;
       rp.fb_count = w.fb_count;
+      rp.fb_total = w.fb_count + B;
       rp.fb_q = w.fb_q;
       rp.fb_desc = w.gath_q;
       rp.ratio = ratio;
@@ -603,6 +618,7 @@ int b200m_match_pairs_u8(const uint8_t* bank, const int32_t* norm_table, const u
       CUDA_TRY(cudaGetLastError());
       // exact fallback for the rows the bounds could not settle (usually none: the kernel finds empty lists)
       b200m::SweepParams sp = base_params(norm_table, n_img, k_per_image, k_stride, pb, nb, w);
+      sp.fb_total = w.fb_count + B;
       rc = launch_sweep<b200m::kTop1G>(tmap_gq, tmap_gq, tmap_bank, sp, sweep_grid(nb * sp.blocks_per_pair), st);
       if (rc) return rc;
       {

@@ -260,4 +260,230 @@ chunk_sweep_kernel(const __grid_constant__ CUtensorMap tmap, const ChunkParams p
   }
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// N = 256 variant: one tcgen05.mma covers a whole 256-column tile (M128 N256 K32), which needs 96 B
+// of shared-memory operand reads per clock instead of the 128 B of two N = 128 halves. Two
+// accumulators (one per M-tile of the row block) fill TMEM; the MMA of one M-tile overlaps the
+// epilogue of the other. All 16 epilogue warps drain every accumulator: warp (quadrant q, column
+// quarter c) owns rows 32q..32q+31 of BOTH M-tiles and chunks 2c, 2c+1 of every tile.
+struct Chunk256Smem {
+  uint8_t a[kAStages][2][kMBytes];
+  uint8_t b[kBStages][kBBytes];
+  int4 rowmerge[2][3][kRows];       // column quarters 1..3 hand their row states to quarter 0
+  uint64_t a_full[kAStages], a_empty[kAStages];
+  uint64_t b_full[kBStages], b_empty[kBStages];
+  uint64_t t_full[2], t_empty[2];   // accumulator m
+  uint32_t tmem_base;
+};
+
+// Registers are allocated per SM sub-partition: 5 warps each at 640 threads -> 96 per thread, enough
+// for the 64-register drain buffer below. (setmaxnreg cannot help: the CTA's pool is what it was
+// launched with, 5 x 96 per sub-partition.)
+constexpr int kFirstEpiWarp256 = kFirstEpiWarp;
+constexpr int kThreads256 = kThreads;
+
+// 64 columns (two chunks) of one row, drained in halves of 16 columns through two register buffers so
+// that the tcgen05.ld of the next half is in flight while the current one goes through the max tree.
+// (Measured: pulling all 64 columns first and releasing the accumulator before the max trees is
+// 17 % SLOWER than this interleaved form, although it frees the accumulator earlier.)
+template <bool kPeakOnly>
+__device__ __forceinline__ void drain64(uint32_t taddr, int cm0, int cm1, int g, ChunkState& st, uint64_t* t_empty,
+                                        uint32_t lane) {
+  int va[16], vb[16];
+  tmem_ld_32x16(taddr, va);
+  tmem_ld_fence16(va);
+  if (kPeakOnly) {
+    tc_fence_before();
+    __syncwarp();
+    if (lane == 0) mbar_arrive(t_empty);
+    chunk_update(st, cm0 - 2 * max16(va), g);
+    return;
+  }
+  tmem_ld_32x16(taddr + 16, vb);
+  const int m0 = max16(va);
+  tmem_ld_fence16(vb);
+  tmem_ld_32x16(taddr + 32, va);
+  const int m1 = max17(vb, m0);
+  tmem_ld_fence16(va);
+  tmem_ld_32x16(taddr + 48, vb);
+  chunk_update(st, cm0 - 2 * m1, g);
+  const int m2 = max16(va);
+  tmem_ld_fence16(vb);
+  // this warp's part of the accumulator is in registers: hand it back to the MMA warp
+  tc_fence_before();
+  __syncwarp();
+  if (lane == 0) mbar_arrive(t_empty);
+  const int m3 = max17(vb, m2);
+  chunk_update(st, cm1 - 2 * m3, g + 1);
+}
+
+template <bool kPeakOnly>
+__global__ void __launch_bounds__(kThreads256, 1)
+chunk_sweep256_kernel(const __grid_constant__ CUtensorMap tmap, const ChunkParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  Chunk256Smem& sm = *reinterpret_cast<Chunk256Smem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+
+  const uint32_t warp = threadIdx.x >> 5;
+  const uint32_t lane = lane_id();
+  const int n_items = p.n_pairs * p.blocks_per_pair;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmap);
+    for (int i = 0; i < kAStages; ++i) { mbar_init(&sm.a_full[i], 1); mbar_init(&sm.a_empty[i], 1); }
+    for (int i = 0; i < kBStages; ++i) { mbar_init(&sm.b_full[i], 1); mbar_init(&sm.b_empty[i], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&sm.t_full[i], 1); mbar_init(&sm.t_empty[i], kEpiWarps); }
+    fence_mbar_init();
+  }
+  if (warp == 2) tmem_alloc<512>(&sm.tmem_base);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = sm.tmem_base;
+
+  auto decode = [&](int item, int& pair, int& blk, int& row0, int& col_img, int& n_rows, int& ntiles, int& nm) {
+    pair = item / p.blocks_per_pair;
+    blk = item - pair * p.blocks_per_pair;
+    const int qi = __ldg(p.pairs + 2 * pair);
+    const int ti = __ldg(p.pairs + 2 * pair + 1);
+    const int kq = __ldg(p.k_per_image + qi);
+    const int kt = __ldg(p.k_per_image + ti);
+    n_rows = min(kq - blk * kRows, kRows);
+    col_img = ti;
+    row0 = static_cast<int>(qi * p.k_stride + blk * kRows);
+    ntiles = (kt + kTT - 1) / kTT;
+    nm = n_rows > kTM ? 2 : 1;
+    return n_rows > 0 && ntiles > 0;
+  };
+
+  if (warp == 0) {
+    // ------------------------------------------------------------- TMA producer
+    if (lane == 0) {
+      uint32_t a_it = 0, b_it = 0;
+      for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+        int pair, blk, row0, col_img, n_rows, ntiles, nm;
+        if (!decode(item, pair, blk, row0, col_img, n_rows, ntiles, nm)) continue;
+        const uint32_t as = a_it % kAStages, aph = (a_it / kAStages) & 1;
+        mbar_wait(&sm.a_empty[as], aph ^ 1);
+        mbar_arrive_expect_tx(&sm.a_full[as], nm * kMBytes);
+        for (int m = 0; m < nm; ++m) tma_load_2d(sm.a[as][m], &tmap, 0, row0 + m * kTM, &sm.a_full[as]);
+        ++a_it;
+        const int64_t crow0 = static_cast<int64_t>(col_img) * p.k_stride;
+        for (int t = 0; t < ntiles; ++t) {
+          const int32_t crow = static_cast<int32_t>(crow0 + t * kTT);
+          const uint32_t bs = b_it % kBStages, bph = (b_it / kBStages) & 1;
+          mbar_wait(&sm.b_empty[bs], bph ^ 1);
+          mbar_arrive_expect_tx(&sm.b_full[bs], kBBytes);
+          tma_load_2d(sm.b[bs], &tmap, 0, crow, &sm.b_full[bs]);
+          tma_load_2d(sm.b[bs] + kBBytes / 2, &tmap, 0, crow + 128, &sm.b_full[bs]);
+          ++b_it;
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------- MMA issuer
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_u8(kTM, kTT);
+      uint32_t a_it = 0, b_it = 0, t_it0 = 0, t_it1 = 0;
+      for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+        int pair, blk, row0, col_img, n_rows, ntiles, nm;
+        if (!decode(item, pair, blk, row0, col_img, n_rows, ntiles, nm)) continue;
+        const uint32_t as = a_it % kAStages, aph = (a_it / kAStages) & 1;
+        mbar_wait(&sm.a_full[as], aph);
+        const uint64_t adesc0 = make_desc_k128(smem_u32(sm.a[as][0]));
+        const uint64_t adesc1 = make_desc_k128(smem_u32(sm.a[as][1]));
+        for (int t = 0; t < ntiles; ++t) {
+          const uint32_t bs = b_it % kBStages, bph = (b_it / kBStages) & 1;
+          mbar_wait(&sm.b_full[bs], bph);
+          const uint64_t bdesc = make_desc_k128(smem_u32(sm.b[bs]));
+          mbar_wait(&sm.t_empty[0], (t_it0 & 1) ^ 1);
+          tc_fence_after();
+#pragma unroll
+          for (int k = 0; k < kD / 32; ++k) mma_i8_ss(tmem_base, adesc0 + 2 * k, bdesc + 2 * k, idesc, k > 0 ? 1u : 0u);
+          tc_commit(&sm.t_full[0]);
+          ++t_it0;
+          if (nm > 1) {
+            mbar_wait(&sm.t_empty[1], (t_it1 & 1) ^ 1);
+            tc_fence_after();
+#pragma unroll
+            for (int k = 0; k < kD / 32; ++k)
+              mma_i8_ss(tmem_base + kTT, adesc1 + 2 * k, bdesc + 2 * k, idesc, k > 0 ? 1u : 0u);
+            tc_commit(&sm.t_full[1]);
+            ++t_it1;
+          }
+          tc_commit(&sm.b_empty[bs]);
+          ++b_it;
+        }
+        tc_commit(&sm.a_empty[as]);
+        ++a_it;
+      }
+    }
+  } else if (warp >= kFirstEpiWarp256) {
+    // ------------------------------------------------------------- epilogue
+    const uint32_t quad = warp & 3;                   // TMEM lane quadrant this warp may read
+    const int cq = (warp - kFirstEpiWarp256) >> 2;       // column quarter: chunks 2 cq, 2 cq + 1 of every tile
+    const int rl = quad * 32 + lane;                  // row inside an M-tile
+    const uint32_t taddr0 = tmem_base + ((quad * 32u) << 16) + cq * 64;
+    uint32_t t_it0 = 0, t_it1 = 0, item_it = 0;
+    for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+      int pair, blk, row0, col_img, n_rows, ntiles, nm;
+      if (!decode(item, pair, blk, row0, col_img, n_rows, ntiles, nm)) continue;
+      const uint32_t par = item_it & 1;
+      ++item_it;
+      ChunkState s0, s1;
+      s0.L1 = kBig; s0.g1 = 0; s0.L2 = kBig;
+      s1 = s0;
+      const int2* cm = reinterpret_cast<const int2*>(p.cmin + (static_cast<int64_t>(col_img) * p.k_stride) / kChunk) + cq;
+      int2 cm_next = __ldg(cm);
+      for (int t = 0; t < ntiles; ++t) {
+        const int2 c2 = cm_next;
+        if (t + 1 < ntiles) cm_next = __ldg(cm + 4 * (t + 1));
+        const int g = t * kChunksPerTile + cq * 2;
+        mbar_wait(&sm.t_full[0], t_it0 & 1);
+        tc_fence_after();
+        ++t_it0;
+        drain64<kPeakOnly>(taddr0, c2.x, c2.y, g, s0, &sm.t_empty[0], lane);
+        if (nm > 1) {
+          mbar_wait(&sm.t_full[1], t_it1 & 1);
+          tc_fence_after();
+          ++t_it1;
+          drain64<kPeakOnly>(taddr0 + kTT, c2.x, c2.y, g, s1, &sm.t_empty[1], lane);
+        }
+      }
+      // the four column quarters of a row meet here: quarters 1..3 -> smem -> quarter 0 -> global
+      if (cq > 0) {
+        sm.rowmerge[par][cq - 1][rl] = make_int4(s0.L1, s0.g1, s0.L2, 0);
+        sm.rowmerge[par][cq - 1][kTM + rl] = make_int4(s1.L1, s1.g1, s1.L2, 0);
+      }
+      named_bar_sync(kEpiBarrier, kEpiWarps * 32);
+      if (cq == 0) {
+#pragma unroll
+        for (int m = 0; m < 2; ++m) {
+          const int row = m * kTM + rl;
+          if (row >= n_rows) continue;
+          ChunkState st = m == 0 ? s0 : s1;
+#pragma unroll
+          for (int o = 0; o < 3; ++o) {
+            const int4 q = sm.rowmerge[par][o][row];
+            // chunks of the quarters interleave tile by tile: order the pair (L, g) explicitly
+            const bool other = lex_less(q.x, q.y, st.L1, st.g1);
+            st.L2 = min(min(q.z, st.L2), other ? st.L1 : q.x);
+            st.g1 = other ? q.y : st.g1;
+            st.L1 = other ? q.x : st.L1;
+          }
+          p.rowres[static_cast<int64_t>(pair) * p.k_stride + blk * kRows + row] = make_int4(st.L1, st.g1, st.L2, 0);
+        }
+      }
+    }
+  }
+
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc<512>(tmem_base);
+  }
+}
+
 }  // namespace b200m

@@ -43,6 +43,7 @@ struct RefineParams {
   const int4* rowres_s;         // chunk sweep output (sorted query rows)
   int4* rowres_o;               // out (original query rows)
   int32_t* fb_count;            // [n_pairs] rows sent to the fallback sweep (zeroed by the caller)
+  int32_t* fb_total;            // [1] != 0 when any row of the batch fell back (zeroed by the caller)
   int32_t* fb_q;                // [n_pairs, k_stride] their original query rows
   uint8_t* fb_desc;             // [n_pairs, k_stride, 128] their descriptors (rows of the fallback sweep)
   double ratio;
@@ -50,6 +51,7 @@ struct RefineParams {
 
 constexpr int kRefineThreads = 256;
 constexpr int kBigScore = 1 << 28;
+constexpr int kPadScore = 1 << 23;   // bound of an all-padding chunk (B200M_PAD_NORM - 0): no real column behind it
 
 __global__ void __launch_bounds__(kRefineThreads)
 refine_kernel(const RefineParams p) {
@@ -75,7 +77,7 @@ refine_kernel(const RefineParams p) {
     if (use_ratio) {
       if (kt < 2) {
         need = false;                                   // no second neighbour: dropped by the ratio test
-      } else if (v.z < kBigScore) {
+      } else if (v.z < kPadScore) {                     // a second chunk with real columns exists
         const int spread = p.spread[ti];
         const int d1lb = max(v.x + na, 0);
         const int dlow = ratio_radius_sq(dist_from_sq(d1lb), p.ratio);
@@ -131,7 +133,7 @@ refine_kernel(const RefineParams p) {
           const int thr = ratio_radius_sq(dist_from_sq(d1), p.ratio) - na;   // a second column scoring < thr spoils the test
           if (s2 < thr) state = kRowReject;
           else if (v.z >= thr) state = kRowPass;
-          else if (static_cast<long long>(v.z) + p.spread[ti] < thr) state = kRowReject;
+          else if (v.z < kPadScore && static_cast<long long>(v.z) + p.spread[ti] < thr) state = kRowReject;
           else state = kRowNeedRatio;
         }
         out = make_int4(d1, bo, 0, state);
@@ -141,6 +143,7 @@ refine_kernel(const RefineParams p) {
   if (r < kq) {
     if (fallback) {
       const int slot = atomicAdd(p.fb_count + pair, 1);
+      if (slot == 0) atomicOr(p.fb_total, 1);
       p.fb_q[base + slot] = r;
       const uint4* src = reinterpret_cast<const uint4*>(p.bank + (qbase + r) * 128);
       uint4* dst = reinterpret_cast<uint4*>(p.fb_desc + (base + slot) * 128);

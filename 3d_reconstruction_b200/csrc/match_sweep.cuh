@@ -105,6 +105,7 @@ struct SweepParams {
   int32_t do_ratio, do_mutual;    // which of the two checks to run
   // kTop1G: rows gathered by the refine kernel, slot s of pair p at p * k_stride + s
   const int32_t* fb_count;        // [n_pairs]
+  const int32_t* fb_total;        // [1] 0 = no row of the batch fell back: the launch has nothing to do
   const int32_t* fb_q;            // original query row of the gathered row
   int4* rowres_o;                 // out, original query rows: (d1^2, i1, d2^2 bound, kRowFallback)
 };
@@ -285,6 +286,7 @@ sweep_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
              const __grid_constant__ CUtensorMap tmap_b, const SweepParams p) {
   extern __shared__ uint8_t smem_raw[];
   SweepSmem& sm = *reinterpret_cast<SweepSmem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  if (kKind == kTop1G && __ldg(p.fb_total) == 0) return;   // the usual case: the bounds settled every row
 
   const uint32_t warp = threadIdx.x >> 5;
   const uint32_t lane = lane_id();

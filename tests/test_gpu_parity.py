@@ -16,12 +16,12 @@ def _bits(x):
     return np.ascontiguousarray(x, dtype=np.float32).view(np.uint32)
 
 
-DEFAULT_KERNEL = 3
+DEFAULT_KERNEL = 5
 DEFAULT_PIPELINE = 2
 
 
-@pytest.fixture(scope="module", params=[(1, 2, 3), (1, 1, 4), (1, 0, 4), (0, 0, 4), (1, 1, 3), (1, 0, 3), (0, 0, 3)],
-                ids=["chunk_refine", "pair_top1_verify", "pair_top2_reject", "pair_top2_exact", "top1_verify", "top2_reject",
+@pytest.fixture(scope="module", params=[(1, 2, 3), (1, 2, 5), (1, 1, 4), (1, 0, 4), (0, 0, 4), (1, 1, 3), (1, 0, 3), (0, 0, 3)],
+                ids=["chunk_refine", "chunk256_refine", "pair_top1_verify", "pair_top2_reject", "pair_top2_exact", "top1_verify", "top2_reject",
                      "top2_exact"])
 def epi(pkg, request):
     """(epilogue, pipeline, kernel): the default chunk sweep on the norm-sorted bank + refine + exact

@@ -12,7 +12,7 @@ pkg = importlib.import_module("3d_reconstruction_b200")
 syn = importlib.import_module("3d_reconstruction_b200.synthetic")
 
 
-def run(n_img, k, modes=((1, 2, 3), (1, 1, 3), (2, 2, 3), (2, 1, 3)), reps=3, max_pairs=None, grid=0):
+def run(n_img, k, modes=((1, 2, 3), (1, 2, 5), (2, 2, 3), (2, 2, 5)), reps=3, max_pairs=None, grid=0):
     desc, kpi = syn.make_bank_tensor(n_img, k, seed=1234, device="cuda")
     bank = pkg.DescriptorBank.from_packed(desc, kpi)
     pairs = pkg.blocked_order(pkg.exhaustive_pairs(n_img))
@@ -45,10 +45,10 @@ def run(n_img, k, modes=((1, 2, 3), (1, 1, 3), (2, 2, 3), (2, 1, 3)), reps=3, ma
                           "matches": int(out.count.sum().item())}), flush=True)
     pkg.set_option("epilogue", 1)
     pkg.set_option("pipeline", 2)
-    pkg.set_option("kernel", 3)
+    pkg.set_option("kernel", 5)
     pkg.set_option("grid", 0)
 
 
 if __name__ == "__main__":
     run(16, 8192)
-    run(12, 16384)
+    run(24, 16384)
