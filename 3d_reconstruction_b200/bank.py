@@ -137,3 +137,56 @@ class DescriptorBank:
     def norms(self) -> torch.Tensor:
         """int32 [n_img, k_stride] view of the squared norms (B200M_PAD_NORM on padding rows)."""
         return self.sqnorm[: self.n_img * self.k_stride].view(self.n_img, self.k_stride)
+
+
+class FloatBank:
+    """Device-resident bf16 bank for the float path: bf16 [n_img, k_stride, D], D in {128, 256}
+    (DISK is 128-d, lightglue/disk.py:12; SuperPoint 256-d, lightglue/superpoint.py:99).
+    Rows >= k_per_image[i] are padding and never compete."""
+
+    def __init__(self, desc: torch.Tensor, k_per_image: torch.Tensor):
+        if not desc.is_cuda:
+            raise RuntimeError("the descriptor bank must live on a CUDA device (there is no CPU path)")
+        if desc.dtype != torch.bfloat16 or desc.dim() != 3 or desc.shape[2] not in (128, 256) or not desc.is_contiguous():
+            raise ValueError("desc must be contiguous bfloat16 [n_img, k_stride, 128 or 256]")
+        if desc.shape[1] % TILE_T != 0:
+            raise ValueError("k_stride must be a multiple of 256")
+        self.desc = desc
+        self.k_per_image = k_per_image.to(device=desc.device, dtype=torch.int32).contiguous()
+        if self.k_per_image.numel() != desc.shape[0]:
+            raise ValueError("k_per_image must have one entry per image")
+
+    @classmethod
+    def from_arrays(cls, arrays: Sequence, device="cuda", k_stride: int | None = None) -> "FloatBank":
+        """arrays: one float [K_i, D] array / tensor per image; rounded to bf16 on the device."""
+        ts = [a.detach() if isinstance(a, torch.Tensor) else torch.as_tensor(np.asarray(a)) for a in arrays]
+        if not ts:
+            raise ValueError("empty descriptor list")
+        dim = int(ts[0].shape[1])
+        if dim not in (128, 256) or any(t.dim() != 2 or t.shape[1] != dim for t in ts):
+            raise ValueError("descriptors must be [K, 128] or [K, 256], the same length for every image")
+        dev = torch.device(device)
+        if dev.type != "cuda":
+            raise RuntimeError("the descriptor bank must live on a CUDA device (there is no CPU path)")
+        kmax = max(int(t.shape[0]) for t in ts)
+        ks = round_up(max(kmax, 1), TILE_T) if k_stride is None else int(k_stride)
+        desc = torch.zeros((len(ts), ks, dim), dtype=torch.bfloat16, device=dev)
+        for i, t in enumerate(ts):
+            desc[i, :t.shape[0]] = t.to(device=dev, dtype=torch.bfloat16)
+        return cls(desc, torch.tensor([int(t.shape[0]) for t in ts], dtype=torch.int32))
+
+    @property
+    def n_img(self) -> int:
+        return int(self.desc.shape[0])
+
+    @property
+    def k_stride(self) -> int:
+        return int(self.desc.shape[1])
+
+    @property
+    def dim(self) -> int:
+        return int(self.desc.shape[2])
+
+    @property
+    def device(self) -> torch.device:
+        return self.desc.device

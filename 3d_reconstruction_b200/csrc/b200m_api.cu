@@ -15,6 +15,7 @@
 #include "match_chunk.cuh"
 #include "match_refine.cuh"
 #include "match_sort.cuh"
+#include "match_float.cuh"
 
 namespace {
 
@@ -114,6 +115,24 @@ int make_row_tmap(CUtensorMap* tm, const void* base, uint64_t n_rows) {
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     snprintf(g_err, sizeof(g_err), "cuTensorMapEncodeTiled failed with CUresult %d", static_cast<int>(r));
+    return B200M_E_CUDA;
+  }
+  return B200M_OK;
+}
+
+// [n_rows, dim] bf16 row-major, box = 128 rows x 64 elements (one 128-byte swizzle atom along K)
+int make_row_tmap_bf16(CUtensorMap* tm, const void* base, uint64_t n_rows, uint32_t dim) {
+  EncodeTiledFn enc = get_encode_fn();
+  if (!enc) return fail(B200M_E_NO_DEVICE, "cuTensorMapEncodeTiled entry point unavailable%s");
+  cuuint64_t dims[2] = {dim, n_rows};
+  cuuint64_t strides[1] = {static_cast<cuuint64_t>(dim) * 2};
+  cuuint32_t box[2] = {64, 128};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    snprintf(g_err, sizeof(g_err), "cuTensorMapEncodeTiled (bf16) failed with CUresult %d", static_cast<int>(r));
     return B200M_E_CUDA;
   }
   return B200M_OK;
@@ -391,6 +410,23 @@ int sweep_rows(const CUtensorMap& tmap_bank, const b200m::SweepParams& sp, bool 
       return exact2 ? launch_any<b200m::kTop2>(tmap_bank, tmap_bank, tmap_bank, sp, grid, st)
                     : launch_any<b200m::kTop1>(tmap_bank, tmap_bank, tmap_bank, sp, grid, st);
   }
+}
+
+template <int kDim>
+int launch_ip_sweep(const CUtensorMap& tmap, const b200m::ip::IpParams& ip, int grid, cudaStream_t st) {
+  constexpr size_t smem = sizeof(b200m::ip::IpSmem<kDim>) + 1024;
+  static thread_local bool attr_set = false;
+  if (!attr_set) {
+    CUDA_TRY(cudaFuncSetAttribute(b200m::ip::ip_sweep_kernel<kDim>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  static_cast<int>(smem)));
+    attr_set = true;
+  }
+  {
+    ProfScope ps(&g_prof.first, st);
+    b200m::ip::ip_sweep_kernel<kDim><<<grid, b200m::kThreads, smem, st>>>(tmap, ip);
+  }
+  CUDA_TRY(cudaGetLastError());
+  return B200M_OK;
 }
 
 }  // namespace
@@ -677,6 +713,57 @@ int b200m_match_pairs_u8(const uint8_t* bank, const int32_t* norm_table, const u
       b200m::emit_kernel<1024><<<static_cast<unsigned>(nb), 1024, 0, st>>>(
           w.cand_q, w.cand_t, w.cand_d, w.viol_ratio, w.viol_mut, w.cand_count, nullptr, k_stride, do_ratio, do_mutual,
           out_query_idx + p0 * cap, out_train_idx + p0 * cap, out_dist + p0 * cap, out_count + p0, cap);
+    }
+    CUDA_TRY(cudaGetLastError());
+  }
+  return B200M_OK;
+}
+
+size_t b200m_workspace_bytes_bf16(int64_t k_stride, int64_t n_pairs) {
+  if (k_stride <= 0 || n_pairs <= 0) return 256;
+  return static_cast<size_t>(2) * batch_pairs(k_stride, n_pairs) * k_stride * sizeof(float2) + 512;
+}
+
+int b200m_match_pairs_bf16(const void* bank_bf16, const int32_t* k_per_image, int32_t n_img, int64_t k_stride,
+                           int32_t dim, const int32_t* pairs, int64_t n_pairs, float score_threshold,
+                           int use_threshold, int mutual, int32_t* out_query_idx, int32_t* out_train_idx,
+                           float* out_score, int32_t* out_count, int64_t cap, void* workspace,
+                           size_t workspace_bytes, void* stream) {
+  if (!bank_bf16 || !k_per_image || n_img <= 0) return fail(B200M_E_BAD_ARG, "null bank / k_per_image or n_img <= 0%s");
+  if (dim != 128 && dim != 256) return fail(B200M_E_BAD_DIM, "the bf16 path handles descriptor lengths 128 and 256%s");
+  if (k_stride <= 0 || (k_stride % B200M_TILE_T) != 0)
+    return fail(B200M_E_BAD_ARG, "k_stride must be a positive multiple of 256%s");
+  if (n_pairs < 0 || (n_pairs > 0 && !pairs)) return fail(B200M_E_BAD_ARG, "bad pairs / n_pairs%s");
+  if (static_cast<int64_t>(n_img) * k_stride >= (int64_t(1) << 31)) return fail(B200M_E_BAD_ARG, "bank has more than 2^31 rows%s");
+  if (device_info().ok != 1) return fail(B200M_E_NO_DEVICE, "no sm_100 CUDA device available (no CPU fallback)%s");
+  if (n_pairs == 0) return B200M_OK;
+  if (!out_query_idx || !out_train_idx || !out_score || !out_count || !workspace || cap <= 0)
+    return fail(B200M_E_BAD_ARG, "null output / workspace or cap <= 0%s");
+  if (workspace_bytes < b200m_workspace_bytes_bf16(k_stride, n_pairs)) return fail(B200M_E_WORKSPACE, "workspace too small%s");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  CUtensorMap tmap;
+  int rc = make_row_tmap_bf16(&tmap, bank_bf16, static_cast<uint64_t>(n_img) * k_stride, static_cast<uint32_t>(dim));
+  if (rc) return rc;
+  const int64_t B = batch_pairs(k_stride, n_pairs);
+  float2* rowbest = reinterpret_cast<float2*>((reinterpret_cast<uintptr_t>(workspace) + 255) & ~uintptr_t(255));
+  for (int64_t p0 = 0; p0 < n_pairs; p0 += B) {
+    const int64_t nb = (n_pairs - p0 < B) ? (n_pairs - p0) : B;
+    b200m::ip::IpParams ip;
+    ip.k_per_image = k_per_image;
+    ip.pairs = pairs + 2 * p0;
+    ip.k_stride = k_stride;
+    ip.n_pairs = static_cast<int32_t>(nb);
+    ip.n_dirs = mutual ? 2 : 1;
+    ip.blocks_per_image = static_cast<int32_t>(k_stride / b200m::ip::kRowsF);
+    ip.rowbest = rowbest;
+    const int grid = sweep_grid(static_cast<int64_t>(ip.n_dirs) * nb * ip.blocks_per_image);
+    rc = dim == 256 ? launch_ip_sweep<256>(tmap, ip, grid, st) : launch_ip_sweep<128>(tmap, ip, grid, st);
+    if (rc) return rc;
+    {
+      ProfScope ps(&g_prof.emit, st);
+      b200m::ip::ip_finalize_kernel<1024><<<static_cast<unsigned>(nb), 1024, 0, st>>>(
+          rowbest, pairs + 2 * p0, k_per_image, k_stride, static_cast<int32_t>(nb), score_threshold, use_threshold,
+          mutual ? 1 : 0, out_query_idx + p0 * cap, out_train_idx + p0 * cap, out_score + p0 * cap, out_count + p0, cap);
     }
     CUDA_TRY(cudaGetLastError());
   }

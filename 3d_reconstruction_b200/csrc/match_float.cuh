@@ -1,0 +1,312 @@
+// Float path: mutual nearest neighbours by inner product for SuperPoint / DISK style descriptors
+// (D = 128 or 256), bf16 operands on tcgen05 (kind::f16, fp32 accumulate in TMEM).
+//
+// Stands in for the reference's matcher head in its raw-similarity form:
+//   lightglue/lightglue.py:223      sim = einsum('bmd,bnd->bmn')              (dense contraction)
+//   lightglue/lightglue.py:237      scores.max(2), scores.max(1)              (row / column arg-best)
+//   lightglue/lightglue.py:239-250  mutual check + score threshold            (filter_matches)
+//   lightglue/lightglue.py:417-426  match list, ascending query index
+// The column arg-best of a pair is the row arg-best of the transposed pair, so every pair is swept in
+// both directions by the same kernel (row arg-max fused into the TMEM epilogue, the similarity matrix
+// never reaches HBM) and ip_finalize_kernel applies mutual check, threshold and packing.
+//
+// ip_sweep_kernel<kDim>: one CTA per SM, persistent over work items (pair direction, block of 128 rows).
+//   warp 0       TMA producer: the row block (kDim/64 K-blocks of 128 rows x 128 B, double buffered) and
+//                the column image as a stream of (128 columns x 64 elements) K-blocks through a ring
+//   warp 1       MMA issuer: per column tile kDim/16 tcgen05.mma.kind::f16 (M128 N128 K16, bf16 -> f32)
+//                into one of four 128 x 128 fp32 accumulators (all 512 TMEM columns), round robin
+//   warps 4-19   epilogue: warp (lane quadrant q, accumulator e) drains every 4th column tile for rows
+//                32q..32q+31: running (best value, lowest column) per row; the four partial results of a
+//                row meet through shared memory at the end of the item.
+#pragma once
+#include <cuda_bf16.h>
+
+#include "match_sweep.cuh"
+
+namespace b200m {
+namespace ip {
+
+constexpr int kKB = 64;                     // bf16 elements per K-block (one 128-byte swizzle atom)
+constexpr int kRowsF = 128;                 // rows per work item (one UMMA M-tile)
+constexpr int kColsF = 128;                 // columns per tile / accumulator (UMMA N)
+constexpr int kBlockBytes = 128 * 128;      // 16 KiB: 128 rows x one K-block
+constexpr int kAStagesF = 2;
+constexpr int kBStagesF = 5;
+constexpr int kAccs = 4;
+constexpr float kNegInf = -3.0e38f;
+
+template <int kDim>
+struct IpSmem {
+  uint8_t a[kAStagesF][kDim / kKB][kBlockBytes];
+  uint8_t b[kBStagesF][kBlockBytes];
+  float2 rowmerge[2][kAccs - 1][kRowsF];    // (value, column as int bits)
+  uint64_t a_full[kAStagesF], a_empty[kAStagesF];
+  uint64_t b_full[kBStagesF], b_empty[kBStagesF];
+  uint64_t t_full[kAccs], t_empty[kAccs];
+  uint32_t tmem_base;
+};
+
+struct IpParams {
+  const int32_t* k_per_image;   // [n_img]
+  const int32_t* pairs;         // [n_pairs, 2] (query image, train image)
+  int64_t k_stride;
+  int32_t n_pairs;
+  int32_t n_dirs;               // 2: both directions (mutual check), 1: rows = query image only
+  int32_t blocks_per_image;     // k_stride / 128
+  // out: [n_dirs][n_pairs][k_stride] (best similarity, best column); direction 0: rows = query image
+  float2* rowbest;
+};
+
+// kind::f16 instruction descriptor: bf16 A and B (K-major), fp32 accumulator
+__host__ __device__ constexpr uint32_t make_idesc_bf16(uint32_t m, uint32_t n) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((n >> 3) << 17) | ((m >> 4) << 24);
+}
+
+__device__ __forceinline__ void mma_bf16_ss(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                            uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "}\n" ::"r"(tmem_d),
+      "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+
+__device__ __forceinline__ float fmax16(const int (&v)[16]) {
+  float m[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) m[i] = fmaxf(__int_as_float(v[2 * i]), __int_as_float(v[2 * i + 1]));
+#pragma unroll
+  for (int i = 0; i < 4; ++i) m[i] = fmaxf(m[i], m[i + 4]);
+  return fmaxf(fmaxf(m[0], m[1]), fmaxf(m[2], m[3]));
+}
+
+// sixteen columns of one row starting at column c0; n_cols = valid columns of the sweep
+__device__ __forceinline__ void ip_process16(int (&v)[16], int c0, int n_cols, float& best, int& bidx) {
+  if (c0 + 16 > n_cols) {   // ragged end (and padding columns: zero vectors must not compete)
+#pragma unroll
+    for (int j = 0; j < 16; ++j)
+      if (c0 + j >= n_cols) v[j] = __float_as_int(kNegInf);
+  }
+  const float m = fmax16(v);
+  if (m > best) {           // strict: an equal value further right never replaces the lowest column
+    best = m;
+    int j = 15;
+#pragma unroll
+    for (int jj = 14; jj >= 0; --jj)
+      if (__int_as_float(v[jj]) == m) j = jj;
+    bidx = c0 + j;
+  }
+}
+
+template <int kDim>
+__global__ void __launch_bounds__(kThreads, 1)
+ip_sweep_kernel(const __grid_constant__ CUtensorMap tmap, const IpParams p) {
+  constexpr int kNKB = kDim / kKB;          // K-blocks per descriptor
+  extern __shared__ uint8_t smem_raw[];
+  IpSmem<kDim>& sm = *reinterpret_cast<IpSmem<kDim>*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+
+  const uint32_t warp = threadIdx.x >> 5;
+  const uint32_t lane = lane_id();
+  const int n_items = p.n_dirs * p.n_pairs * p.blocks_per_image;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmap);
+    for (int i = 0; i < kAStagesF; ++i) { mbar_init(&sm.a_full[i], 1); mbar_init(&sm.a_empty[i], 1); }
+    for (int i = 0; i < kBStagesF; ++i) { mbar_init(&sm.b_full[i], 1); mbar_init(&sm.b_empty[i], 1); }
+    for (int i = 0; i < kAccs; ++i) { mbar_init(&sm.t_full[i], 1); mbar_init(&sm.t_empty[i], 4); }
+    fence_mbar_init();
+  }
+  if (warp == 2) tmem_alloc<512>(&sm.tmem_base);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = sm.tmem_base;
+
+  // item -> (pair, direction, row block); rows of direction 0 are the query image's
+  auto decode = [&](int item, int& pair, int& dir, int& blk, int& row_img, int& col_img, int& n_rows, int& n_cols) {
+    const int pd = item / p.blocks_per_image;
+    blk = item - pd * p.blocks_per_image;
+    pair = pd / p.n_dirs;
+    dir = pd - pair * p.n_dirs;
+    const int qi = __ldg(p.pairs + 2 * pair), ti = __ldg(p.pairs + 2 * pair + 1);
+    row_img = dir ? ti : qi;
+    col_img = dir ? qi : ti;
+    n_rows = min(__ldg(p.k_per_image + row_img) - blk * kRowsF, kRowsF);
+    n_cols = __ldg(p.k_per_image + col_img);
+    return n_rows > 0 && n_cols > 0;
+  };
+
+  if (warp == 0) {
+    // ------------------------------------------------------------- TMA producer
+    if (lane == 0) {
+      uint32_t a_it = 0, b_it = 0;
+      for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+        int pair, dir, blk, row_img, col_img, n_rows, n_cols;
+        if (!decode(item, pair, dir, blk, row_img, col_img, n_rows, n_cols)) continue;
+        const uint32_t as = a_it % kAStagesF, aph = (a_it / kAStagesF) & 1;
+        mbar_wait(&sm.a_empty[as], aph ^ 1);
+        mbar_arrive_expect_tx(&sm.a_full[as], kNKB * kBlockBytes);
+        const int32_t arow = static_cast<int32_t>(row_img * p.k_stride + blk * kRowsF);
+        for (int kb = 0; kb < kNKB; ++kb) tma_load_2d(sm.a[as][kb], &tmap, kb * kKB, arow, &sm.a_full[as]);
+        ++a_it;
+        const int ntiles = (n_cols + kColsF - 1) / kColsF;
+        for (int t = 0; t < ntiles; ++t) {
+          const int32_t crow = static_cast<int32_t>(col_img * p.k_stride + t * kColsF);
+          for (int kb = 0; kb < kNKB; ++kb) {
+            const uint32_t bs = b_it % kBStagesF, bph = (b_it / kBStagesF) & 1;
+            mbar_wait(&sm.b_empty[bs], bph ^ 1);
+            mbar_arrive_expect_tx(&sm.b_full[bs], kBlockBytes);
+            tma_load_2d(sm.b[bs], &tmap, kb * kKB, crow, &sm.b_full[bs]);
+            ++b_it;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------- MMA issuer
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(kRowsF, kColsF);
+      uint32_t a_it = 0, b_it = 0, t_it = 0;
+      for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+        int pair, dir, blk, row_img, col_img, n_rows, n_cols;
+        if (!decode(item, pair, dir, blk, row_img, col_img, n_rows, n_cols)) continue;
+        const uint32_t as = a_it % kAStagesF, aph = (a_it / kAStagesF) & 1;
+        mbar_wait(&sm.a_full[as], aph);
+        const int ntiles = (n_cols + kColsF - 1) / kColsF;
+        for (int t = 0; t < ntiles; ++t) {
+          const uint32_t acc = t_it % kAccs, tph = (t_it / kAccs) & 1;
+          mbar_wait(&sm.t_empty[acc], tph ^ 1);
+          tc_fence_after();
+          const uint32_t tacc = tmem_base + acc * kColsF;
+#pragma unroll
+          for (int kb = 0; kb < kNKB; ++kb) {
+            const uint32_t bs = b_it % kBStagesF, bph = (b_it / kBStagesF) & 1;
+            mbar_wait(&sm.b_full[bs], bph);
+            tc_fence_after();
+            const uint64_t adesc = make_desc_k128(smem_u32(sm.a[as][kb]));
+            const uint64_t bdesc = make_desc_k128(smem_u32(sm.b[bs]));
+#pragma unroll
+            for (int k = 0; k < kKB / 16; ++k)
+              mma_bf16_ss(tacc, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) > 0 ? 1u : 0u);
+            tc_commit(&sm.b_empty[bs]);
+            ++b_it;
+          }
+          tc_commit(&sm.t_full[acc]);
+          ++t_it;
+        }
+        tc_commit(&sm.a_empty[as]);
+        ++a_it;
+      }
+    }
+  } else if (warp >= kFirstEpiWarp) {
+    // ------------------------------------------------------------- epilogue
+    const uint32_t quad = warp & 3;                   // TMEM lane quadrant this warp may read
+    const uint32_t e = (warp - kFirstEpiWarp) >> 2;   // accumulator this warp drains
+    const int rl = quad * 32 + lane;                  // row inside the item's block
+    const uint32_t taddr = tmem_base + ((quad * 32u) << 16) + e * kColsF;
+    uint32_t t_seen = 0;                              // tiles of all items so far (round robin over accumulators)
+    uint32_t my_it = 0, item_it = 0;
+    for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+      int pair, dir, blk, row_img, col_img, n_rows, n_cols;
+      if (!decode(item, pair, dir, blk, row_img, col_img, n_rows, n_cols)) continue;
+      const uint32_t par = item_it & 1;
+      ++item_it;
+      const int ntiles = (n_cols + kColsF - 1) / kColsF;
+      float best = kNegInf;
+      int bidx = -1;
+      // this warp owns the tiles whose global sequence number is e modulo 4
+      int t = static_cast<int>((e + kAccs - (t_seen % kAccs)) % kAccs);
+      for (; t < ntiles; t += kAccs) {
+        mbar_wait(&sm.t_full[e], my_it & 1);
+        tc_fence_after();
+        ++my_it;
+        const int col0 = t * kColsF;
+        int va[16], vb[16];
+        tmem_ld_32x16(taddr, va);
+        tmem_ld_fence16(va);
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          tmem_ld_32x16(taddr + c * 32 + 16, vb);
+          ip_process16(va, col0 + c * 32, n_cols, best, bidx);
+          tmem_ld_fence16(vb);
+          if (c < 3) {
+            tmem_ld_32x16(taddr + (c + 1) * 32, va);
+          } else {
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&sm.t_empty[e]);
+          }
+          ip_process16(vb, col0 + c * 32 + 16, n_cols, best, bidx);
+          if (c < 3) tmem_ld_fence16(va);
+        }
+      }
+      t_seen += ntiles;
+      // the four partial results of a row meet here
+      if (e > 0) sm.rowmerge[par][e - 1][rl] = make_float2(best, __int_as_float(bidx));
+      named_bar_sync(kEpiBarrier, kEpiWarps * 32);
+      if (e == 0 && rl < n_rows) {
+#pragma unroll
+        for (int o = 0; o < kAccs - 1; ++o) {
+          const float2 q = sm.rowmerge[par][o][rl];
+          const int qi = __float_as_int(q.y);
+          if (qi >= 0 && (q.x > best || (q.x == best && qi < bidx) || bidx < 0)) { best = q.x; bidx = qi; }
+        }
+        const int64_t o = (static_cast<int64_t>(dir) * p.n_pairs + pair) * p.k_stride + blk * kRowsF + rl;
+        p.rowbest[o] = make_float2(best, __int_as_float(bidx));
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc<512>(tmem_base);
+  }
+}
+
+// Mutual check + threshold + ascending-query packing (lightglue.py:239-250, 417-426), one CTA per pair.
+template <int kBlock>
+__global__ void __launch_bounds__(kBlock)
+ip_finalize_kernel(const float2* __restrict__ rowbest, const int32_t* __restrict__ pairs,
+                   const int32_t* __restrict__ k_per_image, int64_t k_stride, int32_t n_pairs, float threshold,
+                   int use_threshold, int mutual, int32_t* __restrict__ out_q, int32_t* __restrict__ out_t,
+                   float* __restrict__ out_s, int32_t* __restrict__ out_count, int64_t cap) {
+  __shared__ int warp_sums[kBlock / 32];
+  __shared__ int running;
+  const int pair = blockIdx.x;
+  const int kq = k_per_image[pairs[2 * pair]], kt = k_per_image[pairs[2 * pair + 1]];
+  if (threadIdx.x == 0) running = 0;
+  __syncthreads();
+  const float2* fwd = rowbest + static_cast<int64_t>(pair) * k_stride;
+  const float2* bwd = rowbest + (static_cast<int64_t>(n_pairs) + pair) * k_stride;
+  const int64_t obase = static_cast<int64_t>(pair) * cap;
+  for (int r0 = 0; r0 < kq && kt > 0; r0 += kBlock) {
+    const int r = r0 + threadIdx.x;
+    bool keep = false;
+    float s = 0.f;
+    int j = -1;
+    if (r < kq) {
+      const float2 v = fwd[r];
+      s = v.x;
+      j = __float_as_int(v.y);
+      keep = j >= 0 && j < kt;
+      if (keep && use_threshold) keep = s > threshold;
+      if (keep && mutual) keep = __float_as_int(bwd[j].y) == r;
+    }
+    const int slot = block_compact_slot<kBlock>(keep, warp_sums, &running);
+    if (keep && slot < cap) {
+      out_q[obase + slot] = r;
+      out_t[obase + slot] = j;
+      out_s[obase + slot] = s;
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) out_count[pair] = running;
+}
+
+}  // namespace ip
+}  // namespace b200m

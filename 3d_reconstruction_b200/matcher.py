@@ -15,15 +15,16 @@ import numpy as np
 import torch
 
 from . import _lib
-from .bank import DescriptorBank
+from .bank import DescriptorBank, FloatBank
 
 
 @dataclass
 class MatchConfig:
-    ratio: float = 0.75      # Lowe ratio on float32 distances (<= 0 disables)
+    ratio: float = 0.75      # l2_u8: Lowe ratio on float32 distances (<= 0 disables)
     mutual: bool = True      # cross-check
-    metric: str = "l2_u8"    # the exact integer path; the bf16 inner-product path is a later row
+    metric: str = "l2_u8"    # "l2_u8": exact integer path (SIFT); "ip_bf16": inner product, bf16 tensor cores (DISK / SuperPoint)
     k: int = 2
+    score_threshold: float | None = None   # ip_bf16: keep matches whose similarity exceeds it (lightglue.py:243-246)
 
 
 @dataclass
@@ -129,6 +130,44 @@ def match_pairs(bank: DescriptorBank, pairs, ratio: float = 0.75, mutual: bool =
     return out
 
 
+def match_pairs_float(bank: FloatBank, pairs, score_threshold: float | None = None, mutual: bool = True,
+                      cap: int | None = None, out: PairMatches | None = None,
+                      workspace: torch.Tensor | None = None) -> PairMatches:
+    """Float path: mutual arg-max of the inner product for every (query_img, train_img) pair
+    (lightglue.py:223 + :235-254 in raw-similarity form). `dist` of the result holds the similarity."""
+    pairs_t = _pairs_tensor(pairs, bank.device)
+    P = int(pairs_t.shape[0])
+    if cap is None:
+        cap = bank.k_stride
+    dev = bank.device
+    if out is None:
+        out = PairMatches(torch.empty((P, cap), dtype=torch.int32, device=dev),
+                          torch.empty((P, cap), dtype=torch.int32, device=dev),
+                          torch.empty((P, cap), dtype=torch.float32, device=dev),
+                          torch.zeros((P,), dtype=torch.int32, device=dev), int(cap))
+    if P == 0:
+        return out
+    L = _lib.lib()
+    if workspace is None:
+        workspace = torch.empty(int(L.b200m_workspace_bytes_bf16(bank.k_stride, P)), dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev):
+        st = torch.cuda.current_stream().cuda_stream
+        _lib.check(L.b200m_match_pairs_bf16(
+            bank.desc.data_ptr(), bank.k_per_image.data_ptr(), bank.n_img, bank.k_stride, bank.dim,
+            pairs_t.data_ptr(), P, float(score_threshold if score_threshold is not None else 0.0),
+            int(score_threshold is not None), int(bool(mutual)),
+            out.query_idx.data_ptr(), out.train_idx.data_ptr(), out.dist.data_ptr(), out.count.data_ptr(),
+            int(out.cap), workspace.data_ptr(), workspace.numel(), st))
+    return out
+
+
+def match_float(desc_q, desc_t, score_threshold: float | None = None, mutual: bool = True, device="cuda"):
+    """Single pair, float path: (query_idx int32 [S], train_idx int32 [S], similarity float32 [S])."""
+    bank = FloatBank.from_arrays([desc_q, desc_t], device=device)
+    q, t, s = match_pairs_float(bank, [[0, 1]], score_threshold, mutual).to_lists()[0]
+    return q.astype(np.int32), t.astype(np.int32), s
+
+
 def knn2_pairs(bank: DescriptorBank, pairs, workspace: torch.Tensor | None = None):
     """knnMatch(k=2) for every pair -> (train_idx int32 [P,k_stride,2], dist float32 [P,k_stride,2])."""
     pairs_t = _pairs_tensor(pairs, bank.device)
@@ -193,8 +232,8 @@ class B200Matcher:
     def __init__(self, config: MatchConfig | None = None, device="cuda"):
         self.conf = config or MatchConfig()
         self.device = torch.device(device)
-        if self.conf.metric != "l2_u8":
-            raise NotImplementedError("only the exact u8 L2 path is built so far")
+        if self.conf.metric not in ("l2_u8", "ip_bf16"):
+            raise NotImplementedError(f"unknown metric {self.conf.metric}")
 
     def eval(self):
         return self
@@ -209,10 +248,15 @@ class B200Matcher:
         d0 = data["image0"]["descriptors"]
         d1 = data["image1"]["descriptors"]
         assert d0.dim() == 3 and d1.dim() == 3 and d0.shape[0] == 1 and d1.shape[0] == 1, "batch size must be 1"
-        assert d0.shape[-1] == 128 and d1.shape[-1] == 128            # lightglue.py:365-366
         m, n = d0.shape[1], d1.shape[1]
-        bank = DescriptorBank.from_arrays([d0[0], d1[0]], device=self.device)
-        res = match_pairs(bank, [[0, 1]], ratio=self.conf.ratio, mutual=self.conf.mutual)
+        if self.conf.metric == "ip_bf16":
+            assert d0.shape[-1] == d1.shape[-1] and d0.shape[-1] in (128, 256)   # lightglue.py:365-366 (DISK 128, SuperPoint 256)
+            fbank = FloatBank.from_arrays([d0[0], d1[0]], device=self.device)
+            res = match_pairs_float(fbank, [[0, 1]], self.conf.score_threshold, self.conf.mutual)
+        else:
+            assert d0.shape[-1] == 128 and d1.shape[-1] == 128        # lightglue.py:365-366
+            bank = DescriptorBank.from_arrays([d0[0], d1[0]], device=self.device)
+            res = match_pairs(bank, [[0, 1]], ratio=self.conf.ratio, mutual=self.conf.mutual)
         res.check_overflow()
         s = int(res.count[0].item())
         q = res.query_idx[0, :s].long()

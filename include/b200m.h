@@ -119,6 +119,22 @@ int b200m_match_pairs_u8(const uint8_t* bank, const int32_t* norm_table,
                          int32_t* out_count, int64_t cap,
                          void* workspace, size_t workspace_bytes, void* stream);
 
+/* Float path (SuperPoint / DISK style descriptors, lightglue/lightglue.py:223-250 in raw-similarity
+ * form): similarity = inner product, bf16 operands with fp32 accumulation on the tensor cores.
+ *   bank_bf16  bf16 [n_img, k_stride, dim], dim 128 or 256, rows >= k_per_image[i] ignored
+ * A query row q matches train row t when t is q's arg-max similarity, (mutual != 0) q is t's
+ * arg-max similarity (lowest index on exact ties, both ways), and (use_threshold != 0)
+ * similarity > score_threshold. Outputs as b200m_match_pairs_u8, out_score = the fp32 similarity.
+ * Not bit-comparable with an fp32 reference: the stated tolerance is index agreement (tests/). */
+size_t b200m_workspace_bytes_bf16(int64_t k_stride, int64_t n_pairs);
+int b200m_match_pairs_bf16(const void* bank_bf16, const int32_t* k_per_image, int32_t n_img,
+                           int64_t k_stride, int32_t dim,
+                           const int32_t* pairs, int64_t n_pairs,
+                           float score_threshold, int use_threshold, int mutual,
+                           int32_t* out_query_idx, int32_t* out_train_idx, float* out_score,
+                           int32_t* out_count, int64_t cap,
+                           void* workspace, size_t workspace_bytes, void* stream);
+
 /* Tuning / introspection knobs (process-global, read at launch time).
  *   "epilogue"  0 = exact insertion of every element (debug), 1 = threshold-reject (default),
  *               2 = MMA-only ceiling measurement (results invalid)

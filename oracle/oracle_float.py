@@ -1,0 +1,69 @@
+"""CPU restatement of the reference's mutual-arg-best rule on a raw similarity matrix -- TEST INFRASTRUCTURE ONLY.
+
+Follows lightglue/lightglue.py of the reference:
+  * similarity()       :223      sim = einsum('bmd,bnd->bmn', mdesc0, mdesc1)   (fp32)
+  * filter_matches()   :235-254  row / column arg-max (:237), mutual check (:239-242), threshold on the
+                                 winning score (:243-250), -1 for rejected rows (:252-253)
+  * match_list()       :417-426  valid = m0 > -1; matches = stack([where(valid), m0[valid]]) -- ascending query index
+Pinned against the reference itself: tests/golden/float_mutual_*.npz hold the outputs of the reference's
+own filter_matches (imported from /root/reference/lightglue/lightglue.py by tests/golden/make_golden_float.py)
+for seeded inputs, and tests/test_oracle.py checks this restatement against them.
+The threshold here applies to the raw similarity (the reference exponentiates log-scores first, :243).
+"""
+from __future__ import annotations
+
+import numpy as np
+
+
+def similarity(d0: np.ndarray, d1: np.ndarray) -> np.ndarray:
+    return np.asarray(d0, np.float32) @ np.asarray(d1, np.float32).T
+
+
+def filter_matches(sim: np.ndarray, threshold=None):
+    """-> (m0 int64 [M] (-1 = rejected), m1 int64 [N], mscores0 float32 [M]); first index wins ties (np.argmax)."""
+    m, n = sim.shape
+    if m == 0 or n == 0:
+        return np.full(m, -1, np.int64), np.full(n, -1, np.int64), np.zeros(m, np.float32)
+    a0 = sim.argmax(1)
+    a1 = sim.argmax(0)
+    mutual0 = np.arange(m) == a1[a0]
+    mutual1 = np.arange(n) == a0[a1]
+    best0 = sim[np.arange(m), a0]
+    ms0 = np.where(mutual0, best0, 0).astype(np.float32)
+    valid0 = mutual0 & (best0 > threshold) if threshold is not None else mutual0
+    valid1 = mutual1 & valid0[a1]
+    return np.where(valid0, a0, -1), np.where(valid1, a1, -1), ms0
+
+
+def match_list(m0: np.ndarray):
+    valid = m0 > -1
+    return np.nonzero(valid)[0], m0[valid]
+
+
+def match(d0, d1, threshold=None, mutual: bool = True):
+    """(query idx, train idx, similarity) ascending in query index."""
+    sim = similarity(d0, d1)
+    if mutual:
+        m0, _, _ = filter_matches(sim, threshold)
+    else:
+        a0 = sim.argmax(1) if sim.size else np.zeros(0, np.int64)
+        best = sim[np.arange(len(a0)), a0] if sim.size else np.zeros(0, np.float32)
+        m0 = np.where(best > threshold, a0, -1) if threshold is not None else a0
+    q, t = match_list(np.asarray(m0))
+    return q.astype(np.int32), t.astype(np.int32), sim[q, t].astype(np.float32)
+
+
+def agreement(sim: np.ndarray, got_q, got_t, exp_q, exp_t):
+    """Index agreement of two match lists + the largest similarity gap on rows where they differ
+    (gap = how far the row's chosen similarity is from the row maximum): the float path's tolerance."""
+    got = dict(zip(np.asarray(got_q).tolist(), np.asarray(got_t).tolist()))
+    exp = dict(zip(np.asarray(exp_q).tolist(), np.asarray(exp_t).tolist()))
+    rows = set(got) | set(exp)
+    same = sum(1 for r in rows if got.get(r, -1) == exp.get(r, -1))
+    gap = 0.0
+    for r in rows:
+        if got.get(r, -1) != exp.get(r, -1):
+            for lst in (got, exp):
+                if r in lst:
+                    gap = max(gap, float(sim[r].max() - sim[r, lst[r]]))
+    return same / max(len(rows), 1), gap

@@ -1,0 +1,99 @@
+"""GPU: the bf16 float path (mutual arg-max of the inner product) against the oracle and the fixtures
+produced by the reference's own filter_matches.
+
+Stated tolerance (the bf16 MMA accumulates in fp32 in a different order than an fp32 GEMM, and the
+inputs are rounded to bf16):
+  * inputs already bf16-representable: >= 99.5 % of the rows get the same partner as the fp32 oracle, and
+    on the rows that differ the chosen similarity is within 1e-5 of the row maximum (near-ties only);
+  * arbitrary fp32 inputs (rounded to bf16 on the way in): >= 97 % agreement, similarity gap <= 0.02.
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import oracle_float
+
+pytestmark = pytest.mark.gpu
+
+
+def bf16_bits_to_f32(x):
+    return (x.astype(np.uint16).astype(np.uint32) << 16).view(np.float32)
+
+
+def _planted(m, n, dim, seed, noise=0.05):
+    g = torch.Generator().manual_seed(seed)
+    w = torch.nn.functional.normalize(torch.randn(max(m, n), dim, generator=g), dim=1)
+    d0 = torch.nn.functional.normalize(w[torch.randperm(max(m, n), generator=g)[:m]] + noise * torch.randn(m, dim, generator=g), dim=1)
+    d1 = torch.nn.functional.normalize(w[torch.randperm(max(m, n), generator=g)[:n]] + noise * torch.randn(n, dim, generator=g), dim=1)
+    return d0, d1
+
+
+@pytest.mark.parametrize("dim", [128, 256])
+def test_float_fixture_from_reference(pkg, golden_dir, dim):
+    g = np.load(os.path.join(golden_dir, f"float_mutual_{dim}.npz"))
+    d0, d1 = bf16_bits_to_f32(g["d0_bf16"]), bf16_bits_to_f32(g["d1_bf16"])
+    sim = oracle_float.similarity(d0, d1)
+    for name, thr in (("none", None), ("thr", float(g["threshold"]))):
+        q, t, s = pkg.match_float(d0, d1, score_threshold=thr, mutual=True)
+        assert np.all(np.diff(q) > 0)                                   # ascending query index (lightglue.py:419-425)
+        agree, gap = oracle_float.agreement(sim, q, t, g[f"q_{name}"], g[f"t_{name}"])
+        assert agree >= 0.995 and gap <= 1e-5, (name, agree, gap)
+        assert np.allclose(s, sim[q, t], atol=1e-5)
+        assert len(q) > 100
+
+
+@pytest.mark.parametrize("m,n,dim", [(1, 1, 128), (3, 700, 256), (700, 3, 128), (129, 257, 256), (2048, 2048, 256),
+                                     (2048, 1999, 128)])
+def test_float_shapes_vs_oracle(pkg, m, n, dim):
+    d0, d1 = _planted(m, n, dim, seed=m * 31 + n)
+    b0, b1 = d0.to(torch.bfloat16).float().numpy(), d1.to(torch.bfloat16).float().numpy()
+    sim_b = oracle_float.similarity(b0, b1)          # what the kernel sees
+    sim_f = oracle_float.similarity(d0.numpy(), d1.numpy())
+    for mutual, thr in ((True, None), (True, 0.5), (False, 0.3)):
+        q, t, s = pkg.match_float(d0, d1, score_threshold=thr, mutual=mutual)
+        eq, et, _ = oracle_float.match(b0, b1, thr, mutual)
+        agree, gap = oracle_float.agreement(sim_b, q, t, eq, et)
+        assert agree >= 0.995 and gap <= 1e-5, (mutual, thr, agree, gap)
+        fq, ft, _ = oracle_float.match(d0.numpy(), d1.numpy(), thr, mutual)
+        agree_f, gap_f = oracle_float.agreement(sim_f, q, t, fq, ft)
+        assert agree_f >= 0.97 and gap_f <= 0.02, (mutual, thr, agree_f, gap_f)
+        assert np.allclose(s, sim_b[q, t], atol=2e-5)
+
+
+def test_float_batched_config5(pkg):
+    """BASELINE.json config 5: 2,048 keypoints, 256-d (and 128-d) float descriptors, many pairs per launch."""
+    for dim in (256, 128):
+        n_img, k = 6, 2048
+        g = torch.Generator().manual_seed(dim)
+        w = torch.nn.functional.normalize(torch.randn(k * 2, dim, generator=g), dim=1)
+        imgs = []
+        for i in range(n_img):
+            sel = torch.randperm(k * 2, generator=g)[:k]
+            imgs.append(torch.nn.functional.normalize(w[sel] + 0.05 * torch.randn(k, dim, generator=g), dim=1))
+        bank = pkg.FloatBank.from_arrays(imgs)
+        pairs = pkg.exhaustive_pairs(n_img)
+        res = pkg.match_pairs_float(bank, pairs, score_threshold=0.5, mutual=True).to_lists()
+        total = 0
+        for (a, b), (q, t, s) in zip(pairs.tolist(), res):
+            b0, b1 = imgs[a].to(torch.bfloat16).float().numpy(), imgs[b].to(torch.bfloat16).float().numpy()
+            eq, et, _ = oracle_float.match(b0, b1, 0.5, True)
+            agree, gap = oracle_float.agreement(oracle_float.similarity(b0, b1), q, t, eq, et)
+            assert agree >= 0.995 and gap <= 1e-5, (a, b, agree, gap)
+            total += len(q)
+        assert total > 1000
+
+
+def test_float_lightglue_shaped(pkg):
+    d0, d1 = _planted(500, 450, 256, seed=3)
+    m = pkg.B200Matcher(pkg.MatchConfig(metric="ip_bf16", score_threshold=0.4))
+    out = m({"image0": {"descriptors": d0[None], "keypoints": torch.zeros(1, 500, 2)},
+             "image1": {"descriptors": d1[None], "keypoints": torch.zeros(1, 450, 2)}})
+    matches = out["matches"][0].cpu().numpy()                 # what matching.py:124-128 reads
+    b0, b1 = d0.to(torch.bfloat16).float().numpy(), d1.to(torch.bfloat16).float().numpy()
+    eq, et, _ = oracle_float.match(b0, b1, 0.4, True)
+    agree, gap = oracle_float.agreement(oracle_float.similarity(b0, b1), matches[:, 0], matches[:, 1], eq, et)
+    assert agree >= 0.995 and gap <= 1e-5
+    m0 = out["matches0"][0].cpu().numpy()
+    assert (m0[matches[:, 0]] == matches[:, 1]).all()
