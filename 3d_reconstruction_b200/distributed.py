@@ -83,3 +83,33 @@ def gather_flat(offsets: torch.Tensor, payload: list[torch.Tensor], dst: int = 0
     torch.cumsum(all_counts, 0, out=goff[1:])
     out = [torch.cat([pb[r][: n_match[r]] for r in range(ws)]) for pb in pbufs]
     return goff, out
+
+
+def scatter_bank_window(desc: torch.Tensor | None, k_per_image: torch.Tensor | None, n_img: int, k_stride: int, dim: int,
+                        window: int, device, dtype=torch.uint8, src: int = 0):
+    """Sharded bank + halo for the sequential-window schedule (config 4: 2,000 images, each against the next
+    32): instead of broadcasting the whole bank, rank `src` sends every rank only the images it needs
+    (its query range + `window` halo images, scheduler.window_shard). Point-to-point over NCCL / gloo.
+
+    -> (local desc [halo_hi - lo, k_stride, dim], local k_per_image, local pairs int32 [P_r,2], global pairs)"""
+    from .scheduler import window_shard
+    rank, ws = world()
+    lo, hi, halo_hi, local_pairs, global_pairs = window_shard(n_img, window, ws, rank)
+    if ws == 1:
+        return desc.to(device), k_per_image.to(device=device, dtype=torch.int32), local_pairs, global_pairs
+    if rank == src:
+        for r in range(ws):
+            rlo, _, rhalo, _, _ = window_shard(n_img, window, ws, r)
+            if r == src or rhalo <= rlo:
+                continue
+            dist.send(desc[rlo:rhalo].contiguous().to(device), dst=r)
+            dist.send(k_per_image[rlo:rhalo].to(device=device, dtype=torch.int32).contiguous(), dst=r)
+        return (desc[lo:halo_hi].contiguous().to(device), k_per_image[lo:halo_hi].to(device=device, dtype=torch.int32),
+                local_pairs, global_pairs)
+    n_loc = max(halo_hi - lo, 0)
+    d = torch.empty((n_loc, k_stride, dim), dtype=dtype, device=device)
+    k = torch.empty((n_loc,), dtype=torch.int32, device=device)
+    if n_loc:
+        dist.recv(d, src=src)
+        dist.recv(k, src=src)
+    return d, k, local_pairs, global_pairs

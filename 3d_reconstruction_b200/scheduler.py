@@ -57,3 +57,23 @@ def partition(pairs: np.ndarray, world_size: int, rank: int, k_per_image=None):
     lo, hi = int(bounds[rank]), int(bounds[rank + 1])
     idx = np.arange(lo, hi)
     return pairs[lo:hi], idx
+
+
+def window_shard(n_img: int, window: int, world_size: int, rank: int):
+    """Sharding of the sequential-window schedule (BASELINE.json config 4) WITHOUT a full bank broadcast:
+    rank r owns a contiguous range of query images and needs only those plus a halo of `window`
+    following images. Ranges are balanced on pair counts (the last `window` images have fewer pairs).
+
+    -> (img_lo, img_hi, halo_hi, local_pairs int32 [P_r,2] indexed relative to img_lo, global_pairs int32 [P_r,2])
+    The concatenation of global_pairs over the ranks is window_pairs(n_img, window) in order."""
+    per_img = np.minimum(window, np.maximum(n_img - 1 - np.arange(n_img), 0)).astype(np.int64)
+    csum = np.concatenate([[0], np.cumsum(per_img)])
+    total = csum[-1]
+    bounds = np.searchsorted(csum, total * np.arange(world_size + 1) / max(world_size, 1), side="left")
+    bounds[0], bounds[-1] = 0, n_img
+    bounds = np.maximum.accumulate(bounds)
+    lo, hi = int(bounds[rank]), int(bounds[rank + 1])
+    halo_hi = min(n_img, hi + window) if hi > lo else hi
+    rows = [(i, j) for i in range(lo, hi) for j in range(i + 1, min(n_img, i + 1 + window))]
+    gp = np.asarray(rows, dtype=np.int32).reshape(-1, 2)
+    return lo, hi, halo_hi, gp - lo, gp

@@ -63,3 +63,38 @@ def test_two_rank_partition_and_gather(tmp_path):
         assert np.array_equal(r["d"][lo:hi].numpy().view(np.uint32), ed.view(np.uint32))
         total += hi - lo
     assert total == len(r["q"]) and total > 0
+
+
+def _worker_window(rank, world, port, out_dir):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    dmod = importlib.import_module("3d_reconstruction_b200.distributed")
+    syn = importlib.import_module("3d_reconstruction_b200.synthetic")
+    n_img, window, k = 9, 3, 200
+    if rank == 0:
+        desc, kpi = syn.make_bank_tensor(n_img, k, seed=8, device="cpu")
+    else:
+        desc = kpi = None
+    d, kp, lp, gp = dmod.scatter_bank_window(desc, kpi, n_img, 256, 128, window, "cpu")
+    torch.save({"d": d, "k": kp, "lp": torch.from_numpy(lp), "gp": torch.from_numpy(gp)}, os.path.join(out_dir, f"w{rank}.pt"))
+    if rank == 0:
+        torch.save({"desc": desc, "kpi": kpi}, os.path.join(out_dir, "full.pt"))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_two_rank_window_shard_with_halo(tmp_path, pkg):
+    """config-4 style sharding: every rank holds only its images + halo, and its local pair list addresses
+    exactly the same descriptors as the global schedule does in the full bank."""
+    mp.spawn(_worker_window, args=(2, _free_port(), str(tmp_path)), nprocs=2, join=True)
+    full = torch.load(str(tmp_path / "full.pt"))
+    gps = []
+    for r in range(2):
+        w = torch.load(str(tmp_path / f"w{r}.pt"))
+        assert w["d"].shape[0] < full["desc"].shape[0]                      # a shard, not the whole bank
+        for (la, lb), (ga, gb) in zip(w["lp"].tolist(), w["gp"].tolist()):
+            assert torch.equal(w["d"][la], full["desc"][ga]) and torch.equal(w["d"][lb], full["desc"][gb])
+            assert int(w["k"][la]) == int(full["kpi"][ga])
+        gps.append(w["gp"].numpy())
+    assert np.array_equal(np.concatenate(gps), pkg.window_pairs(9, 3))

@@ -1,0 +1,88 @@
+"""GPU: BASELINE.json configs 2 and 4 at their full sizes (parity-test cases, not bench lines):
+size-independent properties + sampled pairs against the oracle; config 4 also checks that the
+halo-sharded bank (what 8 ranks would hold) gives the same lists as the whole bank."""
+import importlib
+import time
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import oracle_int
+
+pytestmark = pytest.mark.gpu
+
+
+def _check_sampled(desc, k, pairs, lists, sample):
+    for p in sample:
+        a, b = map(int, pairs[p])
+        eq, et, ed = oracle_int.match(desc[a, :k].cpu().numpy(), desc[b, :k].cpu().numpy(), 0.75, True)
+        q, t, d = lists[p]
+        assert np.array_equal(q, eq) and np.array_equal(t, et), (a, b)
+        assert np.array_equal(d.view(np.uint32), ed.view(np.uint32)), (a, b)
+
+
+def test_config2_64_images_8192_exhaustive(pkg):
+    syn = importlib.import_module("3d_reconstruction_b200.synthetic")
+    n_img, k = 64, 8192
+    desc, kpi = syn.make_bank_tensor(n_img, k, seed=1234, device="cuda")
+    bank = pkg.DescriptorBank.from_packed(desc, kpi)
+    pairs = pkg.blocked_order(pkg.exhaustive_pairs(n_img))
+    assert len(pairs) == 2016
+    out = pkg.match_pairs(bank, pairs, cap=4096)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    out = pkg.match_pairs(bank, pairs, cap=4096, out=out)
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    print(f"config 2: {len(pairs) / dt:.0f} pairs/s ({2.0 * k * k * 128 * len(pairs) / dt / 1e12:.0f} TOP/s)")
+    lists = out.to_lists()
+    n = sum(len(q) for q, _, _ in lists)
+    assert n > 10000
+    for q, t, d in lists:
+        assert len(set(t.tolist())) == len(t) and np.all(np.diff(q) > 0)      # one-to-one, ascending
+    neighbours = [p for p, (a, b) in enumerate(pairs) if b - a == 1][:2]
+    _check_sampled(desc, k, pairs, lists, neighbours + [len(pairs) // 2])
+
+
+def test_config4_window_schedule_and_halo_shards(pkg):
+    syn = importlib.import_module("3d_reconstruction_b200.synthetic")
+    n_img, k, window = 2000, 8192, 32
+    desc, kpi = syn.make_bank_tensor(n_img, k, seed=77, device="cuda")
+    pairs = pkg.window_pairs(n_img, window)
+    assert len(pairs) == 63472
+    bank = pkg.DescriptorBank.from_packed(desc, kpi)
+    cap = 3072
+    out = pkg.match_pairs(bank, pairs, cap=cap)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    out = pkg.match_pairs(bank, pairs, cap=cap, out=out)
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    print(f"config 4: {len(pairs) / dt:.0f} pairs/s on one GPU ({2.0 * k * k * 128 * len(pairs) / dt / 1e12:.0f} TOP/s)")
+    out.check_overflow()
+    cnt = out.count.cpu().numpy()
+    assert cnt.sum() > 100000
+    q_all, t_all, d_all = out.query_idx.cpu().numpy(), out.train_idx.cpu().numpy(), out.dist.cpu().numpy()
+    del bank
+    # what ranks 0, 3 and 7 of an 8-GPU run hold (own images + 32-image halo) must reproduce their slice
+    first = 0
+    offs = {}
+    for r in range(8):
+        lo, hi, halo, lp, gp = pkg.window_shard(n_img, window, 8, r)
+        offs[r] = (first, lo, halo, lp)
+        first += len(gp)
+    for r in (0, 3, 7):
+        p0, lo, halo, lp = offs[r]
+        sbank = pkg.DescriptorBank.from_packed(desc[lo:halo].clone(), kpi[lo:halo].clone())
+        so = pkg.match_pairs(sbank, lp, cap=cap)
+        sc = so.count.cpu().numpy()
+        assert np.array_equal(sc, cnt[p0:p0 + len(lp)])
+        sq, st_, sd = so.query_idx.cpu().numpy(), so.train_idx.cpu().numpy(), so.dist.cpu().numpy()
+        for i in range(0, len(lp), 97):
+            c = sc[i]
+            assert np.array_equal(sq[i, :c], q_all[p0 + i, :c]) and np.array_equal(st_[i, :c], t_all[p0 + i, :c])
+            assert np.array_equal(sd[i, :c].view(np.uint32), d_all[p0 + i, :c].view(np.uint32))
+        del sbank, so
+    lists = {p: (q_all[p, :cnt[p]].astype(np.int64), t_all[p, :cnt[p]].astype(np.int64), d_all[p, :cnt[p]]) for p in (0, 31337)}
+    _check_sampled(desc, k, pairs, lists, [0, 31337])

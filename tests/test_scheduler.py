@@ -44,3 +44,22 @@ def test_synthetic_bank_has_planted_matches(pkg):
     assert len(q) > 20
     desc2, _ = syn.make_bank_tensor(3, 600, seed=1, device="cpu")
     assert (desc == desc2).all()
+
+
+def test_window_shard_covers_the_schedule(pkg):
+    for n, w in ((2000, 32), (40, 8), (5, 32), (33, 32)):
+        full = pkg.window_pairs(n, w)
+        for ws in (1, 2, 3, 8):
+            got, counts = [], []
+            for r in range(ws):
+                lo, hi, halo, lp, gp = pkg.window_shard(n, w, ws, r)
+                assert halo <= n and (len(gp) == 0 or (gp.max() < halo and gp.min() >= lo))
+                assert np.array_equal(lp + lo, gp)
+                assert len(lp) == 0 or lp.max() < halo - lo
+                got.append(gp)
+                counts.append(len(gp))
+            assert np.array_equal(np.concatenate(got), full)
+            if n == 2000:
+                assert max(counts) - min(counts) <= 2 * w          # balanced on pair counts
+                lo, hi, halo, _, _ = pkg.window_shard(n, w, 8, 3)
+                assert halo - lo <= 2000 // 8 + w + 2                 # ~282 images per rank instead of 2,000
