@@ -86,3 +86,45 @@ def test_config4_window_schedule_and_halo_shards(pkg):
         del sbank, so
     lists = {p: (q_all[p, :cnt[p]].astype(np.int64), t_all[p, :cnt[p]].astype(np.int64), d_all[p, :cnt[p]]) for p in (0, 31337)}
     _check_sampled(desc, k, pairs, lists, [0, 31337])
+
+
+def test_config1_native_size_ragged(pkg):
+    """BASELINE.json config 1 at cv2.SIFT's default nfeatures=0 sizes (56,041 x 52,421 keypoints for
+    DSC_0001/DSC_0002): k_stride 56,064 exercises the global passes of the norm sort and the ragged last
+    blocks / tiles. The real images are not on the GPU box, so SIFT-like synthetic rows stand in; rows are
+    sampled against the oracle, the mutual list is checked for the properties cv2's cross-check guarantees."""
+    syn = importlib.import_module("3d_reconstruction_b200.synthetic")
+    ks = [56041, 52421]
+    desc, kpi = syn.make_bank_tensor(2, max(ks), seed=5, device="cuda", k_per_image=ks)
+    bank = pkg.DescriptorBank.from_packed(desc, kpi)
+    perm, inv, snorm, cmin, spread = bank.sort_views()
+    norms = bank.norms()
+    for i, k in enumerate(ks):
+        assert torch.equal(snorm[i], torch.sort(norms[i], stable=True).values)
+        assert torch.equal(perm[i].long(), torch.sort(norms[i], stable=True).indices)
+    res = {}
+    for pl in (2, 1):
+        pkg.set_option("pipeline", pl)
+        try:
+            res[pl] = pkg.match_pairs(bank, [[0, 1], [1, 0]], ratio=0.75, mutual=True).to_lists()
+        finally:
+            pkg.set_option("pipeline", 2)
+    for a, b in zip(res[2], res[1]):
+        assert all(np.array_equal(u, v) for u, v in zip(a, b))
+    q, t, d = res[2][0]
+    assert len(q) > 5000 and len(set(t.tolist())) == len(t) and np.all(np.diff(q) > 0)
+    # sampled matched and unmatched query rows against the oracle's knn (ratio + forward direction)
+    qd, td = desc[0, :ks[0]].cpu().numpy(), desc[1, :ks[1]].cpu().numpy()
+    rng = np.random.default_rng(0)
+    rows = np.unique(np.concatenate([rng.choice(q, 128, replace=False), rng.choice(ks[0], 128, replace=False)]))
+    eidx, edist, _ = oracle_int.knn2(qd[rows], td)
+    matched = dict(zip(q.tolist(), zip(t.tolist(), d.tolist())))
+    for r, (i1, _), (d1, d2) in zip(rows.tolist(), eidx.tolist(), edist.tolist()):
+        passes = float(d1) < 0.75 * float(d2)
+        if r in matched:
+            assert passes and matched[r][0] == i1 and np.float32(matched[r][1]) == np.float32(d1)
+        elif passes:
+            # rejected by the cross-check only: some other query must be at least as near to i1
+            dq = ((qd.astype(np.int64) - td[i1].astype(np.int64)) ** 2).sum(1)
+            best = int(np.argmin(dq))
+            assert best != r
