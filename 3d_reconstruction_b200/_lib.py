@@ -26,6 +26,7 @@ SYMBOLS = (
     "b200m_match_pairs_u8",
     "b200m_workspace_bytes_bf16",
     "b200m_match_pairs_bf16",
+    "b200m_vq_f32",
     "b200m_compact_matches",
     "b200m_profile_read",
     "b200m_profile_detail",
@@ -79,6 +80,8 @@ def lib() -> C.CDLL:
     L.b200m_match_pairs_bf16.restype = C.c_int
     L.b200m_match_pairs_bf16.argtypes = [vp, vp, i32, i64, i32, vp, i64, C.c_float, C.c_int, C.c_int, vp, vp, vp, vp, i64,
                                          vp, sz, vp]
+    L.b200m_vq_f32.restype = C.c_int
+    L.b200m_vq_f32.argtypes = [vp, i64, i32, vp, i32, vp, vp, vp, vp]
     L.b200m_compact_matches.restype = C.c_int
     L.b200m_compact_matches.argtypes = [vp, vp, vp, vp, vp, i64, i64, vp, vp, vp, vp]
     L.b200m_profile_read.restype = C.c_int

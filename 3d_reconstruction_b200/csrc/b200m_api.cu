@@ -16,6 +16,7 @@
 #include "match_refine.cuh"
 #include "match_sort.cuh"
 #include "match_float.cuh"
+#include "match_vq.cuh"
 
 namespace {
 
@@ -767,6 +768,30 @@ int b200m_match_pairs_bf16(const void* bank_bf16, const int32_t* k_per_image, in
     }
     CUDA_TRY(cudaGetLastError());
   }
+  return B200M_OK;
+}
+
+int b200m_vq_f32(const float* obs, int64_t n_obs, int32_t dim, const double* codebook, int32_t n_codes,
+                 int32_t* out_code, double* out_dist, double* code_sqr_scratch, void* stream) {
+  if (n_obs == 0) return B200M_OK;
+  if (!obs || !codebook || !out_code || !code_sqr_scratch || n_obs < 0 || n_codes <= 0)
+    return fail(B200M_E_BAD_ARG, "null argument / bad sizes%s");
+  if (dim <= 0 || dim > 256) return fail(B200M_E_BAD_DIM, "vq handles descriptor lengths up to 256%s");
+  if (device_info().ok != 1) return fail(B200M_E_NO_DEVICE, "no sm_100 CUDA device available (no CPU fallback)%s");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  b200m::vq_code_sqr_kernel<<<(n_codes + 127) / 128, 128, 0, st>>>(codebook, dim, n_codes, code_sqr_scratch);
+  CUDA_TRY(cudaGetLastError());
+  const size_t smem = sizeof(double) * b200m::kVqObsPerBlock * dim;
+  static thread_local bool attr_set = false;
+  if (!attr_set) {
+    CUDA_TRY(cudaFuncSetAttribute(b200m::vq_argmin_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536));
+    attr_set = true;
+  }
+  const int64_t blocks = (n_obs + b200m::kVqObsPerBlock - 1) / b200m::kVqObsPerBlock;
+  b200m::vq_argmin_kernel<<<static_cast<unsigned>(blocks), b200m::kVqThreads, smem, st>>>(
+      obs, n_obs, dim, codebook, code_sqr_scratch, n_codes, out_code, out_dist);
+  CUDA_TRY(cudaGetLastError());
+  g_prof.launches += 2;
   return B200M_OK;
 }
 

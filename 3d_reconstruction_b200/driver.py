@@ -59,16 +59,46 @@ def save_matches(img_pairs, all_matches, output_dir: str = "output") -> None:
 
 
 # ---------------------------------------------------------------------- pair scheduler (matching.py:24-82)
-def bow_view_graph(all_descriptors, k: int, codebook: np.ndarray, top_k: int = 10, cos_thr: float = 0.75):
-    """BoW view graph of the reference: visual words (scipy vq, as the reference calls it), word
-    histograms, idf, cosine similarity, each image's 9 best neighbours kept when cosine > 0.75,
-    symmetric adjacency in insertion order, start = first image of maximum degree."""
-    from scipy.cluster.vq import vq
+def vq_words(all_descriptors, codebook: np.ndarray, device="cuda"):
+    """Visual word of every descriptor of every image (matching.py:26-28) in ONE GPU call:
+    all images' descriptors are stacked, b200m_vq_f32 assigns words, the result is split per image."""
+    import torch
+
+    from . import _lib
+    dev = torch.device(device)
+    if dev.type != "cuda":
+        raise RuntimeError("vq_words runs on a CUDA device (there is no CPU path)")
+    sizes = [int(np.asarray(d).shape[0]) for d in all_descriptors]
+    stack = np.ascontiguousarray(np.concatenate([np.asarray(d, dtype=np.float32).reshape(s, -1)
+                                                 for d, s in zip(all_descriptors, sizes)], 0))
+    obs = torch.from_numpy(stack).to(dev)
+    cb = torch.from_numpy(np.ascontiguousarray(codebook, dtype=np.float64)).to(dev)
+    out = torch.empty((obs.shape[0],), dtype=torch.int32, device=dev)
+    scratch = torch.empty((cb.shape[0],), dtype=torch.float64, device=dev)
+    with torch.cuda.device(dev):
+        _lib.check(_lib.lib().b200m_vq_f32(obs.data_ptr(), obs.shape[0], obs.shape[1], cb.data_ptr(), cb.shape[0],
+                                           out.data_ptr(), None, scratch.data_ptr(),
+                                           torch.cuda.current_stream().cuda_stream))
+    words = out.cpu().numpy()
+    return np.split(words, np.cumsum(sizes)[:-1])
+
+
+def bow_view_graph(all_descriptors, k: int, codebook: np.ndarray, top_k: int = 10, cos_thr: float = 0.75,
+                   device=None):
+    """BoW view graph of the reference: visual words, word histograms, idf, cosine similarity, each
+    image's 9 best neighbours kept when cosine > 0.75, symmetric adjacency in insertion order,
+    start = first image of maximum degree. device=None: words from scipy's vq on the host, exactly
+    as the reference calls it; device="cuda": words from the GPU kernel (vq_words)."""
     n = len(all_descriptors)
     hist = np.zeros((n, k))
-    for i, d in enumerate(all_descriptors):
-        words, _ = vq(np.asarray(d).astype("float"), codebook)
-        hist[i] = np.bincount(words, minlength=k)[:k]
+    if device is not None:
+        for i, words in enumerate(vq_words(all_descriptors, codebook, device)):
+            hist[i] = np.bincount(words, minlength=k)[:k]
+    else:
+        from scipy.cluster.vq import vq
+        for i, d in enumerate(all_descriptors):
+            words, _ = vq(np.asarray(d).astype("float"), codebook)
+            hist[i] = np.bincount(words, minlength=k)[:k]
     df = np.sum(hist > 0, axis=0)
     with np.errstate(divide="ignore", invalid="ignore"):
         tfidf = hist * np.log(n / df)
@@ -205,7 +235,7 @@ def run_matching_stage(output_dir: str = "output", conf: MatchConfig | None = No
     """The whole stage: stage files in -> img_pairs.npy / all_matches.npy out (matching.py as a function)."""
     all_descriptors, all_points, _ = load_features(output_dir)
     k, codebook = load_codebook(output_dir)
-    connection, start = bow_view_graph(all_descriptors, k, codebook)
+    connection, start = bow_view_graph(all_descriptors, k, codebook, device=device)
     pairs, matches = match_view_graph(all_descriptors, all_points, connection, start, conf, gates, device=device)
     save_matches(pairs, matches, output_dir)
     return pairs, matches

@@ -135,6 +135,14 @@ int b200m_match_pairs_bf16(const void* bank_bf16, const int32_t* k_per_image, in
                            int32_t* out_count, int64_t cap,
                            void* workspace, size_t workspace_bytes, void* stream);
 
+/* Visual-word assignment of the BoW pair scheduler, `vq(descriptors, codebook)` at matching.py:26-28:
+ * out_code[i] = arg-min over codebook rows of the L2 distance to obs[i] (first minimum on ties),
+ * out_dist[i] = that distance (may be NULL). fp64 arithmetic in scipy's form (|x|^2 + |c|^2 - 2 x.c).
+ *   obs float32 [n_obs, dim] (dim <= 256), codebook float64 [n_codes, dim],
+ *   code_sqr_scratch float64 [n_codes] (caller-allocated scratch). */
+int b200m_vq_f32(const float* obs, int64_t n_obs, int32_t dim, const double* codebook, int32_t n_codes,
+                 int32_t* out_code, double* out_dist, double* code_sqr_scratch, void* stream);
+
 /* Tuning / introspection knobs (process-global, read at launch time).
  *   "epilogue"  0 = exact insertion of every element (debug), 1 = threshold-reject (default),
  *               2 = MMA-only ceiling measurement (results invalid)

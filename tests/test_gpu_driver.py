@@ -39,3 +39,28 @@ def test_driver_equals_reference_loop(pkg, tmp_path):
     drv.save_matches(*got, output_dir=str(tmp_path))
     all_matches = np.load(os.path.join(str(tmp_path), "all_matches.npy"), allow_pickle=True)
     assert len(all_matches) == len(ref[1]) and len(all_matches[0]) == 3
+
+
+def test_vq_words_equal_scipy(pkg):
+    """b200m_vq_f32 against scipy.cluster.vq.vq (what matching.py:27 calls): identical words, hence an
+    identical view graph; float (DISK-like) and integer-valued (SIFT-like) descriptors, 200 words as bow.py:7."""
+    from scipy.cluster.vq import kmeans, vq
+    drv = importlib.import_module("3d_reconstruction_b200.driver")
+    rng = np.random.default_rng(3)
+    imgs_f = [rng.standard_normal((int(n), 128)).astype(np.float32) for n in (2048, 1500, 1, 777)]
+    imgs_i = [np.abs(rng.standard_normal((int(n), 128)) * 60).clip(0, 255).round().astype(np.float32) for n in (900, 2048, 33)]
+    for imgs in (imgs_f, imgs_i):
+        np.random.seed(0)
+        codebook, _ = kmeans(np.vstack(imgs).astype("float"), 200, 1)
+        got = drv.vq_words(imgs, codebook)
+        total = same = 0
+        for g, d in zip(got, imgs):
+            exp, _ = vq(d.astype("float"), codebook)
+            assert g.shape == exp.shape
+            same += int((g == exp).sum())
+            total += len(exp)
+        assert same == total, (same, total)
+    desc, pts, size, k, codebook = make_scene()
+    c0, s0 = oracle_driver.view_graph(desc, k, codebook, cos_thr=0.2)
+    c1, s1 = drv.bow_view_graph(desc, k, codebook, cos_thr=0.2, device="cuda")
+    assert s0 == s1 and [list(map(int, a)) for a in c0] == [list(map(int, a)) for a in c1]
