@@ -287,6 +287,7 @@ struct Workspace {
   int32_t* cand_excl;       // R   open-ratio list: the nearest train row
   int32_t* fb_count;        // B (padded to 64)
   int32_t* cand_count_a;    // B (padded to 64)
+  int32_t* vitems;          // 2 * (2 * B * k_stride / 256): compact work list of the verify sweep
 };
 
 size_t carve(Workspace* w, void* base, int64_t B, int64_t k_stride) {
@@ -303,7 +304,9 @@ size_t carve(Workspace* w, void* base, int64_t B, int64_t k_stride) {
   uintptr_t i1 = take(sizeof(int4) * R);
   uintptr_t i2 = take(4 * R), i3 = take(4 * R), i4 = take(4 * R);
   uintptr_t i5 = take(4 * (B + 64)), i6 = take(4 * (B + 64));
+  uintptr_t i7 = take(sizeof(int32_t) * 2 * (2 * R / 256 + 64));
   if (w) {
+    w->vitems = reinterpret_cast<int32_t*>(i7);
     w->rowres_o = reinterpret_cast<int4*>(i1);
     w->fb_q = reinterpret_cast<int32_t*>(i2);
     w->cand_rslot = reinterpret_cast<int32_t*>(i3);
@@ -397,6 +400,8 @@ b200m::SweepParams base_params(const int32_t* norm_table, int32_t n_img, const i
   sp.viol_mut = w.viol_mut;
   sp.do_ratio = 0;
   sp.do_mutual = 0;
+  sp.vitems = nullptr;
+  sp.vitem_count = nullptr;
   return sp;
 }
 
@@ -628,7 +633,7 @@ int b200m_match_pairs_u8(const uint8_t* bank, const int32_t* norm_table, const u
       cp.peak = g_opt.epilogue == 2 ? 1 : 0;
       rc = launch_chunk_sweep(tmap_sbank, cp, sweep_grid(nb * cp.blocks_per_pair), st);
       if (rc) return rc;
-      CUDA_TRY(cudaMemsetAsync(w.fb_count, 0, sizeof(int32_t) * (B + 64), st));   // per-pair counts + the batch total at [B]
+      CUDA_TRY(cudaMemsetAsync(w.fb_count, 0, sizeof(int32_t) * (B + 64), st));   // per-pair counts, the batch total at [B], the verify work-list length at [B + 1]
       b200m::RefineParams rp;
       rp.bank = bank;
       rp.sbank = sorted_bank;
@@ -661,8 +666,9 @@ int b200m_match_pairs_u8(const uint8_t* bank, const int32_t* norm_table, const u
       {
         ProfScope ps(&g_prof.select, st);
         b200m::select2_kernel<1024><<<static_cast<unsigned>(nb), 1024, 0, st>>>(
-            w.rowres_o, pb, k_per_image, k_stride, ratio, bank, norm_table, do_mutual, w.cand_q, w.cand_t, w.cand_d,
-            w.cand_thr_mut, w.cand_rslot, w.cand_count, w.cand_thr_ratio, w.cand_excl, w.cand_count_a, w.gath_q, w.gath_t);
+            w.rowres_o, pb, k_per_image, k_stride, ratio, bank, norm_table, do_ratio, do_mutual, w.cand_q, w.cand_t,
+            w.cand_d, w.cand_thr_mut, w.cand_rslot, w.cand_count, w.cand_thr_ratio, w.cand_excl, w.cand_count_a,
+            w.gath_q, w.gath_t, w.vitems, w.fb_count + B + 1);
       }
       CUDA_TRY(cudaGetLastError());
       if (do_ratio || do_mutual) {
@@ -670,6 +676,8 @@ int b200m_match_pairs_u8(const uint8_t* bank, const int32_t* norm_table, const u
         sp.do_mutual = do_mutual;
         sp.cand_count_r = w.cand_count_a;
         sp.cand_excl = w.cand_excl;
+        sp.vitems = w.vitems;                 // only the non-empty blocks (written by select2_kernel)
+        sp.vitem_count = w.fb_count + B + 1;
         rc = launch_sweep<b200m::kVerify>(tmap_gq, tmap_gt, tmap_bank, sp, sweep_grid(nb * sp.blocks_per_pair * 2), st);
         if (rc) return rc;
       }

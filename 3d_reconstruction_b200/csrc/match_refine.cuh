@@ -160,78 +160,150 @@ refine_kernel(const RefineParams p) {
 //   list B (all surviving rows): cand_q / cand_t / cand_d / cand_thr_mut (+ gathered train rows for the
 //           mutual verify sweep) and cand_rslot = the row's slot in list A or -1;
 //   list A (rows whose Lowe test is still open): thr_ratio / excl (+ gathered query rows).
+// Every warp owns a contiguous run of rows, so ballots inside the warp plus ONE block-wide scan of the
+// warp totals give every kept row its ordered slot (one barrier per pair instead of six per 1024 rows). The non-empty
+// 256-row blocks of both lists are appended to the verify sweep's compact work list.
+struct RowClass {
+  bool keep, open;
+  float d1f;
+};
+
+__device__ __forceinline__ RowClass classify_row(const int4 v, int kt, double ratio) {
+  RowClass c;
+  c.keep = false; c.open = false; c.d1f = 0.f;
+  const bool has1 = v.y >= 0 && v.y < kt;
+  if (has1 && v.w != kRowReject) {
+    c.d1f = dist_from_sq(v.x);
+    if (v.w == kRowFallback) {
+      // (d1^2, i1, upper bound of d2^2): rows passing against the bound are a superset of the survivors
+      if (ratio > 0.0) {
+        c.keep = kt >= 2 && static_cast<double>(c.d1f) < ratio * static_cast<double>(dist_from_sq(v.z));
+        c.open = c.keep;
+      } else {
+        c.keep = true;
+      }
+    } else {
+      c.keep = true;
+      c.open = v.w == kRowNeedRatio;
+    }
+  }
+  return c;
+}
+
+// exclusive block scan of (x, y); returns this thread's offsets, totals through tot_x / tot_y
+template <int kBlock>
+__device__ __forceinline__ void block_scan2(int x, int y, int& off_x, int& off_y, int& tot_x, int& tot_y, int2* warp_tot) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  int ix = x, iy = y;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const int ox = __shfl_up_sync(0xffffffffu, ix, d), oy = __shfl_up_sync(0xffffffffu, iy, d);
+    if (lane >= d) { ix += ox; iy += oy; }
+  }
+  if (lane == 31) warp_tot[warp] = make_int2(ix, iy);
+  __syncthreads();
+  int bx = 0, by = 0, sx = 0, sy = 0;
+#pragma unroll
+  for (int w = 0; w < kBlock / 32; ++w) {
+    const int2 t = warp_tot[w];
+    if (w < warp) { bx += t.x; by += t.y; }
+    sx += t.x; sy += t.y;
+  }
+  off_x = bx + ix - x;
+  off_y = by + iy - y;
+  tot_x = sx;
+  tot_y = sy;
+}
+
 template <int kBlock>
 __global__ void __launch_bounds__(kBlock)
 select2_kernel(const int4* __restrict__ rowres_o, const int32_t* __restrict__ pairs,
                const int32_t* __restrict__ k_per_image, int64_t k_stride, double ratio,
-               const uint8_t* __restrict__ bank, const int32_t* __restrict__ sqnorm, int gather_t,
+               const uint8_t* __restrict__ bank, const int32_t* __restrict__ sqnorm, int do_ratio, int gather_t,
                int32_t* __restrict__ cand_q, int32_t* __restrict__ cand_t, float* __restrict__ cand_d,
                int32_t* __restrict__ cand_thr_mut, int32_t* __restrict__ cand_rslot, int32_t* __restrict__ cand_count,
                int32_t* __restrict__ a_thr_ratio, int32_t* __restrict__ a_excl, int32_t* __restrict__ a_count,
-               uint8_t* __restrict__ gath_q, uint8_t* __restrict__ gath_t) {
-  __shared__ int warp_sums[kBlock / 32];
-  __shared__ int running_b, running_a;
+               uint8_t* __restrict__ gath_q, uint8_t* __restrict__ gath_t, int32_t* __restrict__ vitems,
+               int32_t* __restrict__ vitem_count) {
+  __shared__ int2 warp_tot[kBlock / 32];
   const int pair = blockIdx.x;
   const int qi = pairs[2 * pair], ti = pairs[2 * pair + 1];
   const int kq = k_per_image[qi];
   const int kt = k_per_image[ti];
-  if (threadIdx.x == 0) { running_b = 0; running_a = 0; }
-  __syncthreads();
   const int64_t base = static_cast<int64_t>(pair) * k_stride;
   const int64_t qbase = static_cast<int64_t>(qi) * k_stride;
   const int64_t tbase = static_cast<int64_t>(ti) * k_stride;
-  for (int r0 = 0; r0 < kq && kt > 0; r0 += kBlock) {
-    const int r = r0 + threadIdx.x;
-    bool keep = false, open = false;
-    int4 v = make_int4(0, -1, 0, kRowReject);
-    float d1f = 0.f;
-    if (r < kq) {
-      v = rowres_o[base + r];
-      const bool has1 = v.y >= 0 && v.y < kt;
-      if (has1 && v.w != kRowReject) {
-        d1f = dist_from_sq(v.x);
-        if (v.w == kRowFallback) {
-          // (d1^2, i1, upper bound of d2^2): rows passing against the bound are a superset of the survivors
-          if (ratio > 0.0) {
-            keep = kt >= 2 && static_cast<double>(d1f) < ratio * static_cast<double>(dist_from_sq(v.z));
-            open = keep;
-          } else {
-            keep = true;
-          }
-        } else {
-          keep = true;
-          open = v.w == kRowNeedRatio;
+  // warp w owns the contiguous rows [w * seg, (w + 1) * seg), seg = 32 * iters; iteration i of a warp
+  // covers 32 consecutive rows (coalesced), ordered slots come from ballots + one block scan of warp totals
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int iters = kt > 0 ? (kq + kBlock - 1) / kBlock : 0;
+  const int row0 = warp * iters * 32;
+  int n_keep = 0, n_open = 0;                                   // warp totals (same value in every lane)
+#pragma unroll 4
+  for (int i = 0; i < iters; ++i) {
+    const int r = row0 + i * 32 + lane;
+    RowClass c;
+    c.keep = false; c.open = false;
+    if (r < kq) c = classify_row(rowres_o[base + r], kt, ratio);
+    n_keep += __popc(__ballot_sync(0xffffffffu, c.keep));
+    n_open += __popc(__ballot_sync(0xffffffffu, c.open));
+  }
+  int slot, aslot, tot_b, tot_a;
+  block_scan2<kBlock>(lane == 0 ? n_keep : 0, lane == 0 ? n_open : 0, slot, aslot, tot_b, tot_a, warp_tot);
+  slot = __shfl_sync(0xffffffffu, slot, 0);                     // offset of this warp's first kept row
+  aslot = __shfl_sync(0xffffffffu, aslot, 0);
+  if (n_keep) {
+    const unsigned below = (1u << lane) - 1u;
+    for (int i = 0; i < iters; ++i) {
+      const int r = row0 + i * 32 + lane;
+      int4 v = make_int4(0, -1, 0, kRowReject);
+      RowClass c;
+      c.keep = false; c.open = false; c.d1f = 0.f;
+      if (r < kq) {
+        v = rowres_o[base + r];
+        c = classify_row(v, kt, ratio);
+      }
+      const unsigned mk = __ballot_sync(0xffffffffu, c.keep), mo = __ballot_sync(0xffffffffu, c.open);
+      if (c.keep) {
+        const int64_t o = base + slot + __popc(mk & below);
+        const int my_a = aslot + __popc(mo & below);
+        cand_q[o] = r;
+        cand_t[o] = v.y;
+        cand_d[o] = c.d1f;
+        cand_thr_mut[o] = v.x - sqnorm[tbase + v.y];
+        cand_rslot[o] = c.open ? my_a : -1;
+        if (gather_t) {
+          const uint4* src = reinterpret_cast<const uint4*>(bank + (tbase + v.y) * 128);
+          uint4* dst = reinterpret_cast<uint4*>(gath_t + o * 128);
+#pragma unroll
+          for (int k = 0; k < 8; ++k) dst[k] = src[k];
+        }
+        if (c.open) {
+          const int64_t oa = base + my_a;
+          a_thr_ratio[oa] = ratio_radius_sq(c.d1f, ratio) - sqnorm[qbase + r];
+          a_excl[oa] = v.y;
+          const uint4* src = reinterpret_cast<const uint4*>(bank + (qbase + r) * 128);
+          uint4* dst = reinterpret_cast<uint4*>(gath_q + oa * 128);
+#pragma unroll
+          for (int k = 0; k < 8; ++k) dst[k] = src[k];
         }
       }
-    }
-    const int slot = block_compact_slot<kBlock>(keep, warp_sums, &running_b);
-    const int aslot = block_compact_slot<kBlock>(open, warp_sums, &running_a);
-    if (keep) {
-      const int64_t o = base + slot;
-      cand_q[o] = r;
-      cand_t[o] = v.y;
-      cand_d[o] = d1f;
-      cand_thr_mut[o] = v.x - sqnorm[tbase + v.y];
-      cand_rslot[o] = open ? aslot : -1;
-      if (gather_t) {
-        const uint4* src = reinterpret_cast<const uint4*>(bank + (tbase + v.y) * 128);
-        uint4* dst = reinterpret_cast<uint4*>(gath_t + o * 128);
-#pragma unroll
-        for (int i = 0; i < 8; ++i) dst[i] = src[i];
-      }
-    }
-    if (open) {
-      const int64_t o = base + aslot;
-      a_thr_ratio[o] = ratio_radius_sq(d1f, ratio) - sqnorm[qbase + r];
-      a_excl[o] = v.y;
-      const uint4* src = reinterpret_cast<const uint4*>(bank + (qbase + r) * 128);
-      uint4* dst = reinterpret_cast<uint4*>(gath_q + o * 128);
-#pragma unroll
-      for (int i = 0; i < 8; ++i) dst[i] = src[i];
+      slot += __popc(mk);
+      aslot += __popc(mo);
     }
   }
-  __syncthreads();
-  if (threadIdx.x == 0) { cand_count[pair] = running_b; a_count[pair] = running_a; }
+  if (threadIdx.x == 0) {
+    cand_count[pair] = tot_b;
+    a_count[pair] = tot_a;
+    // verify work list: 256-row blocks of list A (check 0, ratio) and list B (check 1, mutual)
+    const int na = do_ratio ? (tot_a + 255) / 256 : 0;
+    const int nb = gather_t ? (tot_b + 255) / 256 : 0;
+    if (na + nb > 0) {
+      int w = atomicAdd(vitem_count, na + nb);
+      for (int b = 0; b < na; ++b, ++w) reinterpret_cast<int2*>(vitems)[w] = make_int2(pair, b * 2);
+      for (int b = 0; b < nb; ++b, ++w) reinterpret_cast<int2*>(vitems)[w] = make_int2(pair, b * 2 + 1);
+    }
+  }
 }
 
 }  // namespace b200m

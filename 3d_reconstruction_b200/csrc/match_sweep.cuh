@@ -103,6 +103,8 @@ struct SweepParams {
   int32_t* viol_ratio;            // out: 1 when the ratio test fails
   int32_t* viol_mut;              // out: 1 when a better (or equal, lower-index) query exists
   int32_t do_ratio, do_mutual;    // which of the two checks to run
+  const int32_t* vitems;          // optional compact work list [n][2] = (pair, blk * 2 + check); NULL = enumerate all
+  const int32_t* vitem_count;     // [1] entries of vitems
   // kTop1G: rows gathered by the refine kernel, slot s of pair p at p * k_stride + s
   const int32_t* fb_count;        // [n_pairs]
   const int32_t* fb_total;        // [1] 0 = no row of the batch fell back: the launch has nothing to do
@@ -125,12 +127,20 @@ template <int kKind>
 __device__ __forceinline__ ItemInfo decode_item(const SweepParams& p, int item) {
   ItemInfo it;
   it.check = 0;
-  if (kKind == kVerify) {
-    it.check = item & 1;
-    item >>= 1;
+  if (kKind == kVerify && p.vitems) {
+    // compact work list written by select2_kernel: (pair, blk * 2 + check) of the non-empty blocks only
+    const int2 w = __ldg(reinterpret_cast<const int2*>(p.vitems) + item);
+    it.pair = w.x;
+    it.blk = w.y >> 1;
+    it.check = w.y & 1;
+  } else {
+    if (kKind == kVerify) {
+      it.check = item & 1;
+      item >>= 1;
+    }
+    it.pair = item / p.blocks_per_pair;
+    it.blk = item - it.pair * p.blocks_per_pair;
   }
-  it.pair = item / p.blocks_per_pair;
-  it.blk = item - it.pair * p.blocks_per_pair;
   const int qi = __ldg(p.pairs + 2 * it.pair);
   const int ti = __ldg(p.pairs + 2 * it.pair + 1);
   const int kq = __ldg(p.k_per_image + qi);
@@ -290,7 +300,8 @@ sweep_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
 
   const uint32_t warp = threadIdx.x >> 5;
   const uint32_t lane = lane_id();
-  const int n_items = p.n_pairs * p.blocks_per_pair * (kKind == kVerify ? 2 : 1);
+  const int n_items = (kKind == kVerify && p.vitems) ? __ldg(p.vitem_count)
+                                                     : p.n_pairs * p.blocks_per_pair * (kKind == kVerify ? 2 : 1);
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_a);

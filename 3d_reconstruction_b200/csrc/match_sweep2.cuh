@@ -67,7 +67,8 @@ sweep_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   const uint32_t rank = cluster_ctarank();
   const bool leader = rank == 0;
   const int cluster_id = blockIdx.x >> 1, n_clusters = gridDim.x >> 1;
-  const int n_items = p.n_pairs * p.blocks_per_pair * (kKind == kVerify ? 2 : 1);
+  const int n_items = (kKind == kVerify && p.vitems) ? __ldg(p.vitem_count)
+                                                     : p.n_pairs * p.blocks_per_pair * (kKind == kVerify ? 2 : 1);
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_a);
