@@ -32,6 +32,7 @@ struct Options {
   // 2 = chunk sweep on the norm-sorted bank + refine + exact fallback (default, needs the sorted bank),
   // 1 = top-1 sweep + ratio/mutual verify sweeps, 0 = top-2 sweep + mutual verify
   int64_t pipeline = 2;
+  int64_t chunk = 64;     // columns per chunk of the chunk sweep (64 needs kernel 5, else 32 is used)
 } g_opt;
 
 // Optional per-launch timing of the sweeps with CUDA events on the launching stream ("profile" option).
@@ -202,18 +203,22 @@ int launch_chunk_sweep(const CUtensorMap& tmap, const b200m::ChunkParams& cp, in
   if (!attr_set) {
     CUDA_TRY(cudaFuncSetAttribute(b200m::chunk_sweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   static_cast<int>(kChunkSmemBytes)));
-    CUDA_TRY(cudaFuncSetAttribute(b200m::chunk_sweep256_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    CUDA_TRY(cudaFuncSetAttribute(b200m::chunk_sweep256_kernel<false, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   static_cast<int>(kChunk256SmemBytes)));
-    CUDA_TRY(cudaFuncSetAttribute(b200m::chunk_sweep256_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    CUDA_TRY(cudaFuncSetAttribute(b200m::chunk_sweep256_kernel<false, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  static_cast<int>(kChunk256SmemBytes)));
+    CUDA_TRY(cudaFuncSetAttribute(b200m::chunk_sweep256_kernel<true, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   static_cast<int>(kChunk256SmemBytes)));
     attr_set = true;
   }
   {
     ProfScope ps(&g_prof.first, st);
     if (g_opt.kernel == 5 && cp.peak)
-      b200m::chunk_sweep256_kernel<true><<<grid, b200m::kThreads256, kChunk256SmemBytes, st>>>(tmap, cp);
+      b200m::chunk_sweep256_kernel<true, 32><<<grid, b200m::kThreads256, kChunk256SmemBytes, st>>>(tmap, cp);
+    else if (g_opt.kernel == 5 && cp.chunk_cols == 64)
+      b200m::chunk_sweep256_kernel<false, 64><<<grid, b200m::kThreads256, kChunk256SmemBytes, st>>>(tmap, cp);
     else if (g_opt.kernel == 5)
-      b200m::chunk_sweep256_kernel<false><<<grid, b200m::kThreads256, kChunk256SmemBytes, st>>>(tmap, cp);
+      b200m::chunk_sweep256_kernel<false, 32><<<grid, b200m::kThreads256, kChunk256SmemBytes, st>>>(tmap, cp);
     else
       b200m::chunk_sweep_kernel<<<grid, b200m::kThreads, kChunkSmemBytes, st>>>(tmap, cp);
   }
@@ -340,14 +345,14 @@ int check_common(const void* bank, const void* sqnorm, const void* kpi, int32_t 
   return B200M_OK;
 }
 
-// sort table (int32): perm[R] | inv[R] | snorm[R] | cmin[R/32] | spread[n_img rounded up to 4], R = n_img * k_stride
+// sort table (int32): perm[R] | inv[R] | snorm[R] | cmin[R/32] | spread[n4] | spread64[n4], R = n_img * k_stride, n4 = n_img rounded up to 4
 struct SortTable {
-  const int32_t *perm, *inv, *snorm, *cmin, *spread;
+  const int32_t *perm, *inv, *snorm, *cmin, *spread, *spread64;
 };
 
 int64_t sort_table_elems(int64_t n_img, int64_t k_stride) {
   const int64_t R = n_img * k_stride;
-  return 3 * R + R / 32 + ((n_img + 3) & ~int64_t(3));
+  return 3 * R + R / 32 + 2 * ((n_img + 3) & ~int64_t(3));
 }
 
 SortTable sort_table_view(const int32_t* t, int64_t n_img, int64_t k_stride) {
@@ -358,6 +363,7 @@ SortTable sort_table_view(const int32_t* t, int64_t n_img, int64_t k_stride) {
   v.snorm = t + 2 * R;
   v.cmin = t + 3 * R;
   v.spread = t + 3 * R + R / 32;
+  v.spread64 = v.spread + ((n_img + 3) & ~int64_t(3));
   return v;
 }
 
@@ -459,6 +465,11 @@ int b200m_set_option(const char* name, int64_t value) {
   if (!strcmp(name, "batch")) { g_opt.batch = value; return B200M_OK; }
   if (!strcmp(name, "pipeline")) { g_opt.pipeline = value; return B200M_OK; }
   if (!strcmp(name, "kernel")) { g_opt.kernel = value; return B200M_OK; }
+  if (!strcmp(name, "chunk")) {
+    if (value != 32 && value != 64) return fail(B200M_E_BAD_ARG, "chunk must be 32 or 64%s");
+    g_opt.chunk = value;
+    return B200M_OK;
+  }
   if (!strcmp(name, "profile")) { g_prof.on = value != 0; return B200M_OK; }
   return fail(B200M_E_BAD_ARG, "unknown option %s", name);
 }
@@ -470,6 +481,7 @@ int64_t b200m_get_option(const char* name) {
   if (!strcmp(name, "batch")) return g_opt.batch;
   if (!strcmp(name, "pipeline")) return g_opt.pipeline;
   if (!strcmp(name, "kernel")) return g_opt.kernel;
+  if (!strcmp(name, "chunk")) return g_opt.chunk;
   if (!strcmp(name, "profile")) return g_prof.on ? 1 : 0;
   return -1;
 }
@@ -545,9 +557,10 @@ int b200m_bank_sort_u8(const uint8_t* bank, const int32_t* norm_table, const int
   CUDA_TRY(cudaGetLastError());
   b200m::sort_gather_kernel<<<grid_for(R * 32, 256), 256, 0, st>>>(bank, tv.perm, k_stride, R, sorted_bank);
   CUDA_TRY(cudaGetLastError());
-  CUDA_TRY(cudaMemsetAsync(const_cast<int32_t*>(tv.spread), 0, sizeof(int32_t) * ((n_img + 3) & ~3), st));
+  CUDA_TRY(cudaMemsetAsync(const_cast<int32_t*>(tv.spread), 0, sizeof(int32_t) * 2 * ((n_img + 3) & ~3), st));
   b200m::sort_chunk_stats_kernel<<<grid_for(R / 32, 256), 256, 0, st>>>(tv.snorm, k_per_image, k_stride, R / 32,
-                                                                      const_cast<int32_t*>(tv.cmin), const_cast<int32_t*>(tv.spread));
+                                                                      const_cast<int32_t*>(tv.cmin), const_cast<int32_t*>(tv.spread),
+                                                                      const_cast<int32_t*>(tv.spread64));
   CUDA_TRY(cudaGetLastError());
   g_prof.launches += 3;
   return B200M_OK;
@@ -631,6 +644,7 @@ int b200m_match_pairs_u8(const uint8_t* bank, const int32_t* norm_table, const u
       cp.blocks_per_pair = static_cast<int32_t>(k_stride / b200m::kRows);
       cp.rowres = w.rowres;
       cp.peak = g_opt.epilogue == 2 ? 1 : 0;
+      cp.chunk_cols = (g_opt.kernel == 5 && g_opt.chunk == 64 && !cp.peak) ? 64 : 32;
       rc = launch_chunk_sweep(tmap_sbank, cp, sweep_grid(nb * cp.blocks_per_pair), st);
       if (rc) return rc;
       CUDA_TRY(cudaMemsetAsync(w.fb_count, 0, sizeof(int32_t) * (B + 64), st));   // per-pair counts, the batch total at [B], the verify work-list length at [B + 1]
@@ -641,7 +655,8 @@ int b200m_match_pairs_u8(const uint8_t* bank, const int32_t* norm_table, const u
       rp.perm = tv.perm;
       rp.inv = tv.inv;
       rp.snorm = tv.snorm;
-      rp.spread = tv.spread;
+      rp.spread = cp.chunk_cols == 64 ? tv.spread64 : tv.spread;
+      rp.chunk_cols = cp.chunk_cols;
       rp.k_per_image = k_per_image;
       rp.pairs = pb;
       rp.k_stride = k_stride;
@@ -652,6 +667,7 @@ int b200m_match_pairs_u8(const uint8_t* bank, const int32_t* norm_table, const u
       rp.fb_q = w.fb_q;
       rp.fb_desc = w.gath_q;
       rp.ratio = ratio;
+      rp.inv_ratio_sq = ratio > 0.0 ? 1.0 / (ratio * ratio) : 0.0;
       {
         ProfScope ps(&g_prof.refine, st);
         dim3 grid(static_cast<unsigned>((k_stride + b200m::kRefineThreads - 1) / b200m::kRefineThreads), static_cast<unsigned>(nb));

@@ -45,6 +45,7 @@ struct ChunkParams {
   // the second smallest chunk bound (kBig when the train image has a single chunk)
   int4* rowres;
   int32_t peak;                 // != 0: MMA/TMA ceiling measurement, the epilogue reads one chunk per tile
+  int32_t chunk_cols;           // 32, or 64 (chunk_sweep256_kernel only): g1 then counts 64-column chunks
 };
 
 // max of 16 values (7 three-input maxima + 1), and of 16 values and a carried one (8 three-input maxima):
@@ -287,7 +288,7 @@ constexpr int kThreads256 = kThreads;
 // that the tcgen05.ld of the next half is in flight while the current one goes through the max tree.
 // (Measured: pulling all 64 columns first and releasing the accumulator before the max trees is
 // 17 % SLOWER than this interleaved form, although it frees the accumulator earlier.)
-template <bool kPeakOnly>
+template <bool kPeakOnly, int kChunkCols>
 __device__ __forceinline__ void drain64(uint32_t taddr, int cm0, int cm1, int g, ChunkState& st, uint64_t* t_empty,
                                         uint32_t lane) {
   int va[16], vb[16];
@@ -307,18 +308,19 @@ __device__ __forceinline__ void drain64(uint32_t taddr, int cm0, int cm1, int g,
   const int m1 = max17(vb, m0);
   tmem_ld_fence16(va);
   tmem_ld_32x16(taddr + 48, vb);
-  chunk_update(st, cm0 - 2 * m1, g);
-  const int m2 = max16(va);
+  if (kChunkCols == 32) chunk_update(st, cm0 - 2 * m1, g);
+  const int m2 = kChunkCols == 32 ? max16(va) : max17(va, m1);
   tmem_ld_fence16(vb);
   // this warp's part of the accumulator is in registers: hand it back to the MMA warp
   tc_fence_before();
   __syncwarp();
   if (lane == 0) mbar_arrive(t_empty);
   const int m3 = max17(vb, m2);
-  chunk_update(st, cm1 - 2 * m3, g + 1);
+  if (kChunkCols == 32) chunk_update(st, cm1 - 2 * m3, g + 1);
+  else chunk_update(st, cm0 - 2 * m3, g);       // sorted norms: the 64-column chunk's minimum is its first
 }
 
-template <bool kPeakOnly>
+template <bool kPeakOnly, int kChunkCols>
 __global__ void __launch_bounds__(kThreads256, 1)
 chunk_sweep256_kernel(const __grid_constant__ CUtensorMap tmap, const ChunkParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -438,16 +440,16 @@ chunk_sweep256_kernel(const __grid_constant__ CUtensorMap tmap, const ChunkParam
       for (int t = 0; t < ntiles; ++t) {
         const int2 c2 = cm_next;
         if (t + 1 < ntiles) cm_next = __ldg(cm + 4 * (t + 1));
-        const int g = t * kChunksPerTile + cq * 2;
+        const int g = kChunkCols == 32 ? t * kChunksPerTile + cq * 2 : t * (kTT / 64) + cq;
         mbar_wait(&sm.t_full[0], t_it0 & 1);
         tc_fence_after();
         ++t_it0;
-        drain64<kPeakOnly>(taddr0, c2.x, c2.y, g, s0, &sm.t_empty[0], lane);
+        drain64<kPeakOnly, kChunkCols>(taddr0, c2.x, c2.y, g, s0, &sm.t_empty[0], lane);
         if (nm > 1) {
           mbar_wait(&sm.t_full[1], t_it1 & 1);
           tc_fence_after();
           ++t_it1;
-          drain64<kPeakOnly>(taddr0 + kTT, c2.x, c2.y, g, s1, &sm.t_empty[1], lane);
+          drain64<kPeakOnly, kChunkCols>(taddr0 + kTT, c2.x, c2.y, g, s1, &sm.t_empty[1], lane);
         }
       }
       // the four column quarters of a row meet here: quarters 1..3 -> smem -> quarter 0 -> global

@@ -47,6 +47,8 @@ struct RefineParams {
   int32_t* fb_q;                // [n_pairs, k_stride] their original query rows
   uint8_t* fb_desc;             // [n_pairs, k_stride, 128] their descriptors (rows of the fallback sweep)
   double ratio;
+  double inv_ratio_sq;          // 1 / ratio^2 (0 when the ratio test is off)
+  int32_t chunk_cols;           // 32 or 64: columns per chunk of the sweep that produced rowres_s
 };
 
 constexpr int kRefineThreads = 256;
@@ -80,9 +82,11 @@ refine_kernel(const RefineParams p) {
       } else if (v.z < kPadScore) {                     // a second chunk with real columns exists
         const int spread = p.spread[ti];
         const int d1lb = max(v.x + na, 0);
-        const int dlow = ratio_radius_sq(dist_from_sq(d1lb), p.ratio);
         const long long ub2 = static_cast<long long>(v.z) + spread + na;
-        if (ub2 < dlow) need = false;                   // a second column lies inside the radius for sure
+        // D*(d1) = d1^2 / ratio^2 up to float rounding (relative 3e-7): a cheap test with a wide margin
+        // settles almost every row, the exact radius is only computed for the rest
+        if (static_cast<double>(ub2) < static_cast<double>(d1lb) * p.inv_ratio_sq * 0.999 - 2.0) need = false;
+        else if (ub2 < ratio_radius_sq(dist_from_sq(d1lb), p.ratio)) need = false;   // a second column lies inside the radius for sure
       }
     }
   }
@@ -95,33 +99,44 @@ refine_kernel(const RefineParams p) {
     todo &= todo - 1;
     const int rr = r_warp0 + src;
     const int g1 = __shfl_sync(0xffffffffu, v.y, src);
-    const int c = g1 * 32 + lane;                        // sorted train column of this lane
-    int s = 0x7fffffff, orig = 0x7fffffff;
-    if (c < kt) {
-      const uint4* colp = reinterpret_cast<const uint4*>(p.sbank + (tbase + c) * 128);
-      const uint4* rowp = reinterpret_cast<const uint4*>(p.bank + (qbase + rr) * 128);
-      uint32_t dot = 0;
+    const uint4* rowp = reinterpret_cast<const uint4*>(p.bank + (qbase + rr) * 128);
+    int bs = 0x7fffffff, bo = 0x7fffffff, s2 = 0x7fffffff;   // best (score, original index), runner-up score
+    for (int sub = 0; sub < p.chunk_cols; sub += 32) {
+      const int c = g1 * p.chunk_cols + sub + lane;          // sorted train column of this lane
+      int s = 0x7fffffff, orig = 0x7fffffff;
+      if (c < kt) {
+        const uint4* colp = reinterpret_cast<const uint4*>(p.sbank + (tbase + c) * 128);
+        uint32_t dot = 0;
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const uint4 a = __ldg(rowp + i), b = __ldg(colp + i);
-        dot = __dp4a(a.x, b.x, dot);
-        dot = __dp4a(a.y, b.y, dot);
-        dot = __dp4a(a.z, b.z, dot);
-        dot = __dp4a(a.w, b.w, dot);
+        for (int i = 0; i < 8; ++i) {
+          const uint4 a = __ldg(rowp + i), b = __ldg(colp + i);
+          dot = __dp4a(a.x, b.x, dot);
+          dot = __dp4a(a.y, b.y, dot);
+          dot = __dp4a(a.z, b.z, dot);
+          dot = __dp4a(a.w, b.w, dot);
+        }
+        s = p.snorm[tbase + c] - 2 * static_cast<int>(dot);
+        orig = p.perm[tbase + c];
       }
-      s = p.snorm[tbase + c] - 2 * static_cast<int>(dot);
-      orig = p.perm[tbase + c];
-    }
-    // best by (score, original index), then the runner-up among the other lanes
-    int bs = s, bo = orig;
+      // best of these 32 columns by (score, original index), then the runner-up among the other lanes
+      int ws = s, wo = orig;
 #pragma unroll
-    for (int off = 16; off >= 1; off >>= 1) {
-      const int os = __shfl_xor_sync(0xffffffffu, bs, off), oo = __shfl_xor_sync(0xffffffffu, bo, off);
-      if (os < bs || (os == bs && oo < bo)) { bs = os; bo = oo; }
-    }
-    int s2 = (orig == bo) ? 0x7fffffff : s;
+      for (int off = 16; off >= 1; off >>= 1) {
+        const int os = __shfl_xor_sync(0xffffffffu, ws, off), oo = __shfl_xor_sync(0xffffffffu, wo, off);
+        if (os < ws || (os == ws && oo < wo)) { ws = os; wo = oo; }
+      }
+      int w2 = (orig == wo) ? 0x7fffffff : s;
 #pragma unroll
-    for (int off = 16; off >= 1; off >>= 1) s2 = min(s2, __shfl_xor_sync(0xffffffffu, s2, off));
+      for (int off = 16; off >= 1; off >>= 1) w2 = min(w2, __shfl_xor_sync(0xffffffffu, w2, off));
+      // merge into the chunk's running (best, runner-up)
+      if (ws < bs || (ws == bs && wo < bo)) {
+        s2 = min(min(s2, w2), bs);
+        bs = ws;
+        bo = wo;
+      } else {
+        s2 = min(min(s2, w2), ws);
+      }
+    }
     if (lane == src) {
       // v = (L1, g1, L2): columns outside chunk g1 score >= L2
       if (!(bs < v.z)) {

@@ -101,10 +101,10 @@ __global__ void sort_gather_kernel(const uint8_t* __restrict__ bank, const int32
   }
 }
 
-// chunk minima (= first norm of the sorted chunk) and the largest chunk spread over real rows per image
+// chunk minima (= first norm of the sorted chunk) and the largest spread of a 32-row / 64-row chunk over real rows per image
 __global__ void sort_chunk_stats_kernel(const int32_t* __restrict__ snorm, const int32_t* __restrict__ k_per_image,
                                         int64_t k_stride, int64_t n_chunks, int32_t* __restrict__ cmin,
-                                        int32_t* __restrict__ spread) {
+                                        int32_t* __restrict__ spread, int32_t* __restrict__ spread64) {
   for (int64_t c = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; c < n_chunks;
        c += static_cast<int64_t>(gridDim.x) * blockDim.x) {
     const int64_t row0 = c * 32;
@@ -116,6 +116,10 @@ __global__ void sort_chunk_stats_kernel(const int32_t* __restrict__ snorm, const
     if (pos0 < k) {
       const int last_pos = min(pos0 + 31, k - 1);
       atomicMax(spread + img, snorm[img * k_stride + last_pos] - first);
+      if ((c & 1) == 0) {          // the 64-row chunk starting here (chunk sweep option "chunk" = 64)
+        const int last64 = min(pos0 + 63, k - 1);
+        atomicMax(spread64 + img, snorm[img * k_stride + last64] - first);
+      }
     }
   }
 }

@@ -157,6 +157,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--n-img", type=int, default=N_IMG, help="development only: fewer images (invalid as a bench number)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--chunk", type=int, default=None, help="development only: columns per chunk of the chunk sweep (32 / 64)")
     ap.add_argument("--kernel", type=int, default=None, help="development only: sweep kernel variant (library option 'kernel')")
     args = ap.parse_args()
     if args.impl == "reference":
@@ -180,6 +181,8 @@ def main():
     dmod = importlib.import_module("3d_reconstruction_b200.distributed")
     if args.kernel is not None:
         pkg.set_option("kernel", args.kernel)
+    if args.chunk is not None:
+        pkg.set_option("chunk", args.chunk)
 
     n_img = args.n_img
     # ------------------------------------------------------------------ inputs

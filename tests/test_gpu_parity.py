@@ -18,10 +18,11 @@ def _bits(x):
 
 DEFAULT_KERNEL = 5
 DEFAULT_PIPELINE = 2
+DEFAULT_CHUNK = 64
 
 
-@pytest.fixture(scope="module", params=[(1, 2, 3), (1, 2, 5), (1, 1, 4), (1, 0, 4), (0, 0, 4), (1, 1, 3), (1, 0, 3), (0, 0, 3)],
-                ids=["chunk_refine", "chunk256_refine", "pair_top1_verify", "pair_top2_reject", "pair_top2_exact", "top1_verify", "top2_reject",
+@pytest.fixture(scope="module", params=[(1, 2, 3), (1, 2, 5, 32), (1, 2, 5, 64), (1, 1, 4), (1, 0, 4), (0, 0, 4), (1, 1, 3), (1, 0, 3), (0, 0, 3)],
+                ids=["chunk_refine", "chunk256x32_refine", "chunk256x64_refine", "pair_top1_verify", "pair_top2_reject", "pair_top2_exact", "top1_verify", "top2_reject",
                      "top2_exact"])
 def epi(pkg, request):
     """(epilogue, pipeline, kernel): the default chunk sweep on the norm-sorted bank + refine + exact
@@ -31,7 +32,9 @@ def epi(pkg, request):
     pkg.set_option("epilogue", request.param[0])
     pkg.set_option("pipeline", request.param[1])
     pkg.set_option("kernel", request.param[2])
+    pkg.set_option("chunk", request.param[3] if len(request.param) > 3 else DEFAULT_CHUNK)
     yield request.param
+    pkg.set_option("chunk", DEFAULT_CHUNK)
     pkg.set_option("epilogue", 1)
     pkg.set_option("pipeline", DEFAULT_PIPELINE)
     pkg.set_option("kernel", DEFAULT_KERNEL)

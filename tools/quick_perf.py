@@ -12,7 +12,7 @@ pkg = importlib.import_module("3d_reconstruction_b200")
 syn = importlib.import_module("3d_reconstruction_b200.synthetic")
 
 
-def run(n_img, k, modes=((1, 2, 3), (1, 2, 5), (2, 2, 3), (2, 2, 5)), reps=3, max_pairs=None, grid=0):
+def run(n_img, k, modes=((1, 2, 5, 64), (1, 2, 5, 32), (2, 2, 5, 32)), reps=3, max_pairs=None, grid=0):
     desc, kpi = syn.make_bank_tensor(n_img, k, seed=1234, device="cuda")
     bank = pkg.DescriptorBank.from_packed(desc, kpi)
     pairs = pkg.blocked_order(pkg.exhaustive_pairs(n_img))
@@ -26,6 +26,7 @@ def run(n_img, k, modes=((1, 2, 3), (1, 2, 5), (2, 2, 3), (2, 2, 5)), reps=3, ma
         pkg.set_option("epilogue", mode[0])
         pkg.set_option("pipeline", mode[1])
         pkg.set_option("kernel", mode[2])
+        pkg.set_option("chunk", mode[3] if len(mode) > 3 else 64)
         pkg.set_option("grid", grid)
         out = pkg.match_pairs(bank, pairs_t, cap=cap, out=out)
         torch.cuda.synchronize()
@@ -47,6 +48,7 @@ def run(n_img, k, modes=((1, 2, 3), (1, 2, 5), (2, 2, 3), (2, 2, 5)), reps=3, ma
     pkg.set_option("pipeline", 2)
     pkg.set_option("kernel", 5)
     pkg.set_option("grid", 0)
+    pkg.set_option("chunk", 64)
 
 
 if __name__ == "__main__":
