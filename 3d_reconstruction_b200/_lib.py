@@ -26,6 +26,8 @@ SYMBOLS = (
     "b200m_match_pairs_u8",
     "b200m_workspace_bytes_bf16",
     "b200m_match_pairs_bf16",
+    "b200m_workspace_bytes_assign",
+    "b200m_assign_pairs_bf16",
     "b200m_vq_f32",
     "b200m_compact_matches",
     "b200m_profile_read",
@@ -77,6 +79,11 @@ def lib() -> C.CDLL:
     L.b200m_match_pairs_u8.argtypes = [vp, vp, vp, vp, vp, i32, i64, vp, i64, dbl, C.c_int, vp, vp, vp, vp, i64, vp, sz, vp]
     L.b200m_workspace_bytes_bf16.restype = sz
     L.b200m_workspace_bytes_bf16.argtypes = [i64, i64]
+    L.b200m_workspace_bytes_assign.restype = sz
+    L.b200m_workspace_bytes_assign.argtypes = [i64, i64]
+    L.b200m_assign_pairs_bf16.restype = C.c_int
+    L.b200m_assign_pairs_bf16.argtypes = [vp, vp, vp, i32, i64, i32, vp, i64, C.c_float, C.c_int, vp, vp, vp, vp, i64,
+                                          vp, sz, vp]
     L.b200m_match_pairs_bf16.restype = C.c_int
     L.b200m_match_pairs_bf16.argtypes = [vp, vp, i32, i64, i32, vp, i64, C.c_float, C.c_int, C.c_int, vp, vp, vp, vp, i64,
                                          vp, sz, vp]

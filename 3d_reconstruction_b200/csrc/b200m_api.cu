@@ -424,18 +424,18 @@ int sweep_rows(const CUtensorMap& tmap_bank, const b200m::SweepParams& sp, bool 
   }
 }
 
-template <int kDim>
+template <int kDim, int kMode = b200m::ip::kIpArgmax>
 int launch_ip_sweep(const CUtensorMap& tmap, const b200m::ip::IpParams& ip, int grid, cudaStream_t st) {
   constexpr size_t smem = sizeof(b200m::ip::IpSmem<kDim>) + 1024;
   static thread_local bool attr_set = false;
   if (!attr_set) {
-    CUDA_TRY(cudaFuncSetAttribute(b200m::ip::ip_sweep_kernel<kDim>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    CUDA_TRY(cudaFuncSetAttribute(b200m::ip::ip_sweep_kernel<kDim, kMode>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   static_cast<int>(smem)));
     attr_set = true;
   }
   {
-    ProfScope ps(&g_prof.first, st);
-    b200m::ip::ip_sweep_kernel<kDim><<<grid, b200m::kThreads, smem, st>>>(tmap, ip);
+    ProfScope ps(kMode == b200m::ip::kIpLse ? &g_prof.verify : &g_prof.first, st);
+    b200m::ip::ip_sweep_kernel<kDim, kMode><<<grid, b200m::kThreads, smem, st>>>(tmap, ip);
   }
   CUDA_TRY(cudaGetLastError());
   return B200M_OK;
@@ -781,6 +781,8 @@ int b200m_match_pairs_bf16(const void* bank_bf16, const int32_t* k_per_image, in
     ip.n_dirs = mutual ? 2 : 1;
     ip.blocks_per_image = static_cast<int32_t>(k_stride / b200m::ip::kRowsF);
     ip.rowbest = rowbest;
+    ip.z = nullptr;
+    ip.nb = nullptr;
     const int grid = sweep_grid(static_cast<int64_t>(ip.n_dirs) * nb * ip.blocks_per_image);
     rc = dim == 256 ? launch_ip_sweep<256>(tmap, ip, grid, st) : launch_ip_sweep<128>(tmap, ip, grid, st);
     if (rc) return rc;
@@ -788,7 +790,67 @@ int b200m_match_pairs_bf16(const void* bank_bf16, const int32_t* k_per_image, in
       ProfScope ps(&g_prof.emit, st);
       b200m::ip::ip_finalize_kernel<1024><<<static_cast<unsigned>(nb), 1024, 0, st>>>(
           rowbest, pairs + 2 * p0, k_per_image, k_stride, static_cast<int32_t>(nb), score_threshold, use_threshold,
-          mutual ? 1 : 0, out_query_idx + p0 * cap, out_train_idx + p0 * cap, out_score + p0 * cap, out_count + p0, cap);
+          mutual ? 1 : 0, 0, out_query_idx + p0 * cap, out_train_idx + p0 * cap, out_score + p0 * cap, out_count + p0, cap);
+    }
+    CUDA_TRY(cudaGetLastError());
+  }
+  return B200M_OK;
+}
+
+size_t b200m_workspace_bytes_assign(int64_t k_stride, int64_t n_pairs) {
+  if (k_stride <= 0 || n_pairs <= 0) return 256;
+  return static_cast<size_t>(2) * batch_pairs(k_stride, n_pairs) * k_stride * (sizeof(float2) + sizeof(float)) + 1024;
+}
+
+int b200m_assign_pairs_bf16(const void* mdesc_bf16, const float* matchability, const int32_t* k_per_image,
+                            int32_t n_img, int64_t k_stride, int32_t dim, const int32_t* pairs, int64_t n_pairs,
+                            float filter_threshold, int use_threshold, int32_t* out_query_idx, int32_t* out_train_idx,
+                            float* out_score, int32_t* out_count, int64_t cap, void* workspace, size_t workspace_bytes,
+                            void* stream) {
+  if (!mdesc_bf16 || !matchability || !k_per_image || n_img <= 0)
+    return fail(B200M_E_BAD_ARG, "null descriptors / matchability / k_per_image or n_img <= 0%s");
+  if (dim != 128 && dim != 256) return fail(B200M_E_BAD_DIM, "the bf16 path handles descriptor lengths 128 and 256%s");
+  if (k_stride <= 0 || (k_stride % B200M_TILE_T) != 0)
+    return fail(B200M_E_BAD_ARG, "k_stride must be a positive multiple of 256%s");
+  if (n_pairs < 0 || (n_pairs > 0 && !pairs)) return fail(B200M_E_BAD_ARG, "bad pairs / n_pairs%s");
+  if (static_cast<int64_t>(n_img) * k_stride >= (int64_t(1) << 31)) return fail(B200M_E_BAD_ARG, "bank has more than 2^31 rows%s");
+  if (device_info().ok != 1) return fail(B200M_E_NO_DEVICE, "no sm_100 CUDA device available (no CPU fallback)%s");
+  if (n_pairs == 0) return B200M_OK;
+  if (!out_query_idx || !out_train_idx || !out_score || !out_count || !workspace || cap <= 0)
+    return fail(B200M_E_BAD_ARG, "null output / workspace or cap <= 0%s");
+  if (workspace_bytes < b200m_workspace_bytes_assign(k_stride, n_pairs)) return fail(B200M_E_WORKSPACE, "workspace too small%s");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  CUtensorMap tmap;
+  int rc = make_row_tmap_bf16(&tmap, mdesc_bf16, static_cast<uint64_t>(n_img) * k_stride, static_cast<uint32_t>(dim));
+  if (rc) return rc;
+  const int64_t B = batch_pairs(k_stride, n_pairs);
+  float2* rowbest = reinterpret_cast<float2*>((reinterpret_cast<uintptr_t>(workspace) + 255) & ~uintptr_t(255));
+  float* nbuf = reinterpret_cast<float*>(rowbest + 2 * B * k_stride);
+  for (int64_t p0 = 0; p0 < n_pairs; p0 += B) {
+    const int64_t nb = (n_pairs - p0 < B) ? (n_pairs - p0) : B;
+    b200m::ip::IpParams ip;
+    ip.k_per_image = k_per_image;
+    ip.pairs = pairs + 2 * p0;
+    ip.k_stride = k_stride;
+    ip.n_pairs = static_cast<int32_t>(nb);
+    ip.n_dirs = 2;
+    ip.blocks_per_image = static_cast<int32_t>(k_stride / b200m::ip::kRowsF);
+    ip.rowbest = rowbest;
+    ip.z = matchability;
+    ip.nb = nbuf;
+    const int grid = sweep_grid(static_cast<int64_t>(2) * nb * ip.blocks_per_image);
+    // pass 1: row and column log-sum-exp (both directions) -> nb; pass 2: arg-max of the log assignment
+    rc = dim == 256 ? launch_ip_sweep<256, b200m::ip::kIpLse>(tmap, ip, grid, st)
+                    : launch_ip_sweep<128, b200m::ip::kIpLse>(tmap, ip, grid, st);
+    if (rc) return rc;
+    rc = dim == 256 ? launch_ip_sweep<256, b200m::ip::kIpBiasArgmax>(tmap, ip, grid, st)
+                    : launch_ip_sweep<128, b200m::ip::kIpBiasArgmax>(tmap, ip, grid, st);
+    if (rc) return rc;
+    {
+      ProfScope ps(&g_prof.emit, st);
+      b200m::ip::ip_finalize_kernel<1024><<<static_cast<unsigned>(nb), 1024, 0, st>>>(
+          rowbest, pairs + 2 * p0, k_per_image, k_stride, static_cast<int32_t>(nb), filter_threshold, use_threshold, 1,
+          1, out_query_idx + p0 * cap, out_train_idx + p0 * cap, out_score + p0 * cap, out_count + p0, cap);
     }
     CUDA_TRY(cudaGetLastError());
   }

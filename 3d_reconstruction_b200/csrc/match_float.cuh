@@ -34,6 +34,14 @@ constexpr int kAStagesF = 2;
 constexpr int kBStagesF = 5;
 constexpr int kAccs = 4;
 constexpr float kNegInf = -3.0e38f;
+constexpr float kLseFloor = -1.0e30f;       // "minus infinity" of the log-sum-exp sweep (its products with log2(e) stay finite)
+constexpr float kLog2e = 1.4426950408889634f;
+constexpr float kLn2 = 0.6931471805599453f;
+
+// epilogue of ip_sweep_kernel
+constexpr int kIpArgmax = 0;      // row arg-max of the raw similarity
+constexpr int kIpLse = 1;         // row log-sum-exp of the similarity -> nb = logsigmoid(z_row) - lse
+constexpr int kIpBiasArgmax = 2;  // row arg-max of 2*sim + nb_other[column], + nb_own[row] at the end
 
 template <int kDim>
 struct IpSmem {
@@ -55,6 +63,9 @@ struct IpParams {
   int32_t blocks_per_image;     // k_stride / 128
   // out: [n_dirs][n_pairs][k_stride] (best similarity, best column); direction 0: rows = query image
   float2* rowbest;
+  // dual-softmax head only (kIpLse writes, kIpBiasArgmax reads):
+  const float* z;               // [n_img, k_stride] matchability logits (lightglue.py:224-225)
+  float* nb;                    // [2][n_pairs][k_stride] logsigmoid(z_row) - log-sum-exp of the row
 };
 
 // kind::f16 instruction descriptor: bf16 A and B (K-major), fp32 accumulator
@@ -101,7 +112,43 @@ __device__ __forceinline__ void ip_process16(int (&v)[16], int c0, int n_cols, f
   }
 }
 
-template <int kDim>
+// sixteen columns of one row: online log-sum-exp, (m, s) with sum_j exp(v_j) = s * exp(m)
+__device__ __forceinline__ void lse_process16(int (&v)[16], int c0, int n_cols, float& m, float& s) {
+  if (c0 + 16 > n_cols) {
+#pragma unroll
+    for (int j = 0; j < 16; ++j)
+      if (c0 + j >= n_cols) v[j] = __float_as_int(kLseFloor);
+  }
+  const float nm = fmaxf(m, fmax16(v));
+  s *= exp2f((m - nm) * kLog2e);
+  m = nm;
+  const float mb = nm * kLog2e;
+  float acc0 = 0.f, acc1 = 0.f;
+#pragma unroll
+  for (int j = 0; j < 16; j += 2) {
+    acc0 += exp2f(fmaf(__int_as_float(v[j]), kLog2e, -mb));
+    acc1 += exp2f(fmaf(__int_as_float(v[j + 1]), kLog2e, -mb));
+  }
+  s += acc0 + acc1;
+}
+
+// sixteen columns: v <- 2 v + bias[column] (bias is the same for every row: one broadcast load per four columns)
+__device__ __forceinline__ void bias16(int (&v)[16], const float* __restrict__ bias) {
+#pragma unroll
+  for (int j = 0; j < 16; j += 4) {
+    const float4 b = __ldg(reinterpret_cast<const float4*>(bias + j));
+    v[j] = __float_as_int(fmaf(2.f, __int_as_float(v[j]), b.x));
+    v[j + 1] = __float_as_int(fmaf(2.f, __int_as_float(v[j + 1]), b.y));
+    v[j + 2] = __float_as_int(fmaf(2.f, __int_as_float(v[j + 2]), b.z));
+    v[j + 3] = __float_as_int(fmaf(2.f, __int_as_float(v[j + 3]), b.w));
+  }
+}
+
+__device__ __forceinline__ float log_sigmoid(float z) {   // F.logsigmoid
+  return fminf(z, 0.f) - log1pf(expf(-fabsf(z)));
+}
+
+template <int kDim, int kMode>
 __global__ void __launch_bounds__(kThreads, 1)
 ip_sweep_kernel(const __grid_constant__ CUtensorMap tmap, const IpParams p) {
   constexpr int kNKB = kDim / kKB;          // K-blocks per descriptor
@@ -215,8 +262,20 @@ ip_sweep_kernel(const __grid_constant__ CUtensorMap tmap, const IpParams p) {
       const uint32_t par = item_it & 1;
       ++item_it;
       const int ntiles = (n_cols + kColsF - 1) / kColsF;
-      float best = kNegInf;
-      int bidx = -1;
+      float best = kMode == kIpLse ? kLseFloor : kNegInf;   // kIpLse: running maximum
+      int bidx = -1;                                          // kIpLse: unused
+      float lsum = 0.f;                                       // kIpLse: running sum of exp(v - best)
+      const float* bias = nullptr;                            // kIpBiasArgmax: nb of the opposite direction (= per column)
+      if constexpr (kMode == kIpBiasArgmax)
+        bias = p.nb + (static_cast<int64_t>(1 - dir) * p.n_pairs + pair) * p.k_stride;
+      auto process = [&](int (&v)[16], int c0) {
+        if constexpr (kMode == kIpLse) {
+          lse_process16(v, c0, n_cols, best, lsum);
+        } else {
+          if constexpr (kMode == kIpBiasArgmax) bias16(v, bias + c0);
+          ip_process16(v, c0, n_cols, best, bidx);
+        }
+      };
       // this warp owns the tiles whose global sequence number is e modulo 4
       int t = static_cast<int>((e + kAccs - (t_seen % kAccs)) % kAccs);
       for (; t < ntiles; t += kAccs) {
@@ -230,7 +289,7 @@ ip_sweep_kernel(const __grid_constant__ CUtensorMap tmap, const IpParams p) {
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
           tmem_ld_32x16(taddr + c * 32 + 16, vb);
-          ip_process16(va, col0 + c * 32, n_cols, best, bidx);
+          process(va, col0 + c * 32);
           tmem_ld_fence16(vb);
           if (c < 3) {
             tmem_ld_32x16(taddr + (c + 1) * 32, va);
@@ -239,23 +298,38 @@ ip_sweep_kernel(const __grid_constant__ CUtensorMap tmap, const IpParams p) {
             __syncwarp();
             if (lane == 0) mbar_arrive(&sm.t_empty[e]);
           }
-          ip_process16(vb, col0 + c * 32 + 16, n_cols, best, bidx);
+          process(vb, col0 + c * 32 + 16);
           if (c < 3) tmem_ld_fence16(va);
         }
       }
       t_seen += ntiles;
       // the four partial results of a row meet here
-      if (e > 0) sm.rowmerge[par][e - 1][rl] = make_float2(best, __int_as_float(bidx));
+      if (e > 0) sm.rowmerge[par][e - 1][rl] = make_float2(best, kMode == kIpLse ? lsum : __int_as_float(bidx));
       named_bar_sync(kEpiBarrier, kEpiWarps * 32);
       if (e == 0 && rl < n_rows) {
-#pragma unroll
-        for (int o = 0; o < kAccs - 1; ++o) {
-          const float2 q = sm.rowmerge[par][o][rl];
-          const int qi = __float_as_int(q.y);
-          if (qi >= 0 && (q.x > best || (q.x == best && qi < bidx) || bidx < 0)) { best = q.x; bidx = qi; }
-        }
         const int64_t o = (static_cast<int64_t>(dir) * p.n_pairs + pair) * p.k_stride + blk * kRowsF + rl;
-        p.rowbest[o] = make_float2(best, __int_as_float(bidx));
+        if constexpr (kMode == kIpLse) {
+          float mm = best;
+#pragma unroll
+          for (int oo = 0; oo < kAccs - 1; ++oo) mm = fmaxf(mm, sm.rowmerge[par][oo][rl].x);
+          float ss = lsum * exp2f((best - mm) * kLog2e);
+#pragma unroll
+          for (int oo = 0; oo < kAccs - 1; ++oo) {
+            const float2 q = sm.rowmerge[par][oo][rl];
+            ss += q.y * exp2f((q.x - mm) * kLog2e);
+          }
+          const float lse = mm + logf(ss);
+          p.nb[o] = log_sigmoid(__ldg(p.z + static_cast<int64_t>(row_img) * p.k_stride + blk * kRowsF + rl)) - lse;
+        } else {
+#pragma unroll
+          for (int oo = 0; oo < kAccs - 1; ++oo) {
+            const float2 q = sm.rowmerge[par][oo][rl];
+            const int qi = __float_as_int(q.y);
+            if (qi >= 0 && (q.x > best || (q.x == best && qi < bidx) || bidx < 0)) { best = q.x; bidx = qi; }
+          }
+          if constexpr (kMode == kIpBiasArgmax) best += p.nb[o];   // the row's own term: the full log assignment score
+          p.rowbest[o] = make_float2(best, __int_as_float(bidx));
+        }
       }
     }
   }
@@ -269,11 +343,12 @@ ip_sweep_kernel(const __grid_constant__ CUtensorMap tmap, const IpParams p) {
 }
 
 // Mutual check + threshold + ascending-query packing (lightglue.py:239-250, 417-426), one CTA per pair.
+// exp_scores: rowbest holds log assignment scores (dual-softmax head); the threshold applies to exp(score).
 template <int kBlock>
 __global__ void __launch_bounds__(kBlock)
 ip_finalize_kernel(const float2* __restrict__ rowbest, const int32_t* __restrict__ pairs,
                    const int32_t* __restrict__ k_per_image, int64_t k_stride, int32_t n_pairs, float threshold,
-                   int use_threshold, int mutual, int32_t* __restrict__ out_q, int32_t* __restrict__ out_t,
+                   int use_threshold, int mutual, int exp_scores, int32_t* __restrict__ out_q, int32_t* __restrict__ out_t,
                    float* __restrict__ out_s, int32_t* __restrict__ out_count, int64_t cap) {
   __shared__ int warp_sums[kBlock / 32];
   __shared__ int running;
@@ -294,6 +369,7 @@ ip_finalize_kernel(const float2* __restrict__ rowbest, const int32_t* __restrict
       s = v.x;
       j = __float_as_int(v.y);
       keep = j >= 0 && j < kt;
+      if (exp_scores) s = expf(s);      // log assignment -> matching score (lightglue.py:243)
       if (keep && use_threshold) keep = s > threshold;
       if (keep && mutual) keep = __float_as_int(bwd[j].y) == r;
     }

@@ -135,6 +135,28 @@ int b200m_match_pairs_bf16(const void* bank_bf16, const int32_t* k_per_image, in
                            int32_t* out_count, int64_t cap,
                            void* workspace, size_t workspace_bytes, void* stream);
 
+/* The reference matcher's assignment head without the M x N matrices: log double-softmax of the
+ * similarity plus matchability (sigmoid_log_double_softmax, lightglue/lightglue.py:196-208, on
+ * sim = mdesc0 . mdesc1 of MatchAssignment.forward :218-227) followed by filter_matches (:235-254)
+ * and the match list (:417-426).
+ *   mdesc_bf16    bf16 [n_img, k_stride, dim]: final_proj(desc) / dim^0.25 (:220-222), dim 128 or 256
+ *   matchability  float32 [n_img, k_stride]: the logits z = matchability(desc) (:224-225)
+ * Per pair and direction the kernel sweeps the similarity twice: pass 1 row log-sum-exp (both
+ * directions = row and column soft-max normalisers), pass 2 the arg-max of
+ *   score[i,j] = 2 sim[i,j] - lse_row[i] - lse_col[j] + logsigmoid(z0[i]) + logsigmoid(z1[j]).
+ * A row i matches j when j = arg-max_j score[i,:], i = arg-max_i score[:,j] and (use_threshold != 0)
+ * exp(score) > filter_threshold. out_score = exp(score) (= matching_scores0 of the reference);
+ * other outputs as b200m_match_pairs_u8. With use_threshold == 0 the list holds every mutual pair,
+ * from which matches0/1 and matching_scores0/1 of the reference follow exactly (host side). */
+size_t b200m_workspace_bytes_assign(int64_t k_stride, int64_t n_pairs);
+int b200m_assign_pairs_bf16(const void* mdesc_bf16, const float* matchability, const int32_t* k_per_image,
+                            int32_t n_img, int64_t k_stride, int32_t dim,
+                            const int32_t* pairs, int64_t n_pairs,
+                            float filter_threshold, int use_threshold,
+                            int32_t* out_query_idx, int32_t* out_train_idx, float* out_score,
+                            int32_t* out_count, int64_t cap,
+                            void* workspace, size_t workspace_bytes, void* stream);
+
 /* Visual-word assignment of the BoW pair scheduler, `vq(descriptors, codebook)` at matching.py:26-28:
  * out_code[i] = arg-min over codebook rows of the L2 distance to obs[i] (first minimum on ties),
  * out_dist[i] = that distance (may be NULL). fp64 arithmetic in scipy's form (|x|^2 + |c|^2 - 2 x.c).

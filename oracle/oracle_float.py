@@ -67,3 +67,47 @@ def agreement(sim: np.ndarray, got_q, got_t, exp_q, exp_t):
                 if r in lst:
                     gap = max(gap, float(sim[r].max() - sim[r, lst[r]]))
     return same / max(len(rows), 1), gap
+
+
+# ---------------------------------------------------------------------- the reference's assignment head
+def log_sigmoid(z):
+    z = np.asarray(z, np.float64)
+    return np.minimum(z, 0) - np.log1p(np.exp(-np.abs(z)))
+
+
+def log_softmax(x, axis):
+    x = np.asarray(x, np.float64)
+    m = x.max(axis=axis, keepdims=True)
+    return x - (m + np.log(np.exp(x - m).sum(axis=axis, keepdims=True)))
+
+
+def log_double_softmax(sim, z0, z1):
+    """sigmoid_log_double_softmax, lightglue.py:196-208 -> the [M, N] core of the log assignment matrix
+    (the extra dust-bin row / column at :206-207 is cut off again by filter_matches at :237). fp64."""
+    sim = np.asarray(sim, np.float64)
+    cert = log_sigmoid(np.asarray(z0).reshape(-1, 1)) + log_sigmoid(np.asarray(z1).reshape(1, -1))     # :200
+    return log_softmax(sim, 1) + log_softmax(sim, 0) + cert                                              # :201-205
+
+
+def filter_log_matches(scores, th=None):
+    """filter_matches on a log assignment core, lightglue.py:235-254 -> (m0, m1, mscores0, mscores1)."""
+    m, n = scores.shape
+    if m == 0 or n == 0:
+        return np.full(m, -1, np.int64), np.full(n, -1, np.int64), np.zeros(m, np.float32), np.zeros(n, np.float32)
+    a0, a1 = scores.argmax(1), scores.argmax(0)                                  # :237-238
+    mutual0 = np.arange(m) == a1[a0]                                             # :241
+    mutual1 = np.arange(n) == a0[a1]
+    max0_exp = np.exp(scores[np.arange(m), a0])                                  # :243
+    ms0 = np.where(mutual0, max0_exp, 0)                                         # :245
+    ms1 = np.where(mutual1, ms0[a1], 0)                                          # :246
+    valid0 = mutual0 & (ms0 > th) if th is not None else mutual0                 # :247-250
+    valid1 = mutual1 & valid0[a1]                                                # :251
+    return (np.where(valid0, a0, -1), np.where(valid1, a1, -1), ms0.astype(np.float32), ms1.astype(np.float32))
+
+
+def assign(mdesc0, mdesc1, z0, z1, th=None):
+    """MatchAssignment.forward after the projections (:223-226) + filter_matches + match list (:417-426)."""
+    scores = log_double_softmax(similarity(mdesc0, mdesc1), z0, z1)
+    m0, m1, ms0, ms1 = filter_log_matches(scores, th)
+    q, t = match_list(m0)
+    return q.astype(np.int32), t.astype(np.int32), ms0[q], (m0, m1, ms0, ms1), scores

@@ -38,3 +38,21 @@ def test_oracle_float_small_cases():
     assert q.size == 0
     q, t, s = oracle_float.match(np.zeros((0, 128), np.float32), d1)
     assert q.size == 0
+
+
+@pytest.mark.parametrize("dim", [128, 256])
+def test_oracle_assignment_head_matches_reference_fixture(golden_dir, dim):
+    """numpy restatement of sigmoid_log_double_softmax + filter_matches (lightglue.py:196-254) against the
+    outputs of the reference's own functions (tests/golden/make_golden_assign.py)."""
+    g = np.load(os.path.join(golden_dir, f"assign_{dim}.npz"))
+    d0, d1 = bf16_bits_to_f32(g["d0_bf16"]), bf16_bits_to_f32(g["d1_bf16"])
+    scores = oracle_float.log_double_softmax(oracle_float.similarity(d0, d1), g["z0"], g["z1"])
+    assert np.allclose(scores[7], g["scores_row7"], atol=2e-4)
+    for name, th in (("none", None), ("thr", float(g["threshold"]))):
+        m0, m1, ms0, ms1 = oracle_float.filter_log_matches(scores, th)
+        # fp32 (reference) vs fp64 (restatement) may flip near-ties and rows sitting on the threshold
+        assert np.mean(m0 == g[f"m0_{name}"]) >= 0.995 and np.mean(m1 == g[f"m1_{name}"]) >= 0.995
+        same = m0 == g[f"m0_{name}"]
+        assert np.allclose(ms0[same], g[f"ms0_{name}"][same], atol=1e-4)
+        assert np.allclose(ms1, g[f"ms1_{name}"], atol=1e-4) or np.mean(np.isclose(ms1, g[f"ms1_{name}"], atol=1e-4)) >= 0.995
+    assert (g["m0_thr"] > -1).sum() > 100 and (g["m0_none"] > -1).sum() > (g["m0_thr"] > -1).sum()
