@@ -263,7 +263,8 @@ def main():
     roofline = {
         "bound": "tensor", "achieved": achieved, "peak": int8_peak, "unit": "TFLOP/s", "frac": achieved / int8_peak,
         "traffic": None,
-        "kernel": "b200m::chunk_sweep_kernel",
+        "kernel": ("b200m::chunk_sweep256_kernel<0,%d>" % pkg.get_option("chunk")) if pkg.get_option("kernel") == 5
+                  else "b200m::chunk_sweep_kernel",
         "peak_source": f"2 x bf16_tflops_sustained of MEASURED_PEAKS.json ({peak_kind}): int8 tcgen05 rate is twice the bf16 rate; "
                        "nominal dense int8 is 4500",
         "frac_of_nominal_4500": achieved / 4500.0,
