@@ -6,6 +6,7 @@
 #include <stdio.h>
 #include <string.h>
 
+#include <algorithm>
 #include <vector>
 
 #include "../../include/b200m.h"
@@ -13,6 +14,7 @@
 #include "match_sweep.cuh"
 #include "match_sweep2.cuh"
 #include "match_chunk.cuh"
+#include "match_chunk2.cuh"
 #include "match_refine.cuh"
 #include "match_sort.cuh"
 #include "match_float.cuh"
@@ -197,6 +199,7 @@ int launch_sweep(const CUtensorMap& tmap_a, const CUtensorMap& tmap_a2, const CU
 constexpr size_t kChunkSmemBytes = sizeof(b200m::ChunkSmem) + 1024;
 
 constexpr size_t kChunk256SmemBytes = sizeof(b200m::Chunk256Smem) + 1024;
+constexpr size_t kChunkPairSmemBytes = sizeof(b200m::pair::ChunkPairSmem) + 1024;
 
 int launch_chunk_sweep(const CUtensorMap& tmap, const b200m::ChunkParams& cp, int grid, cudaStream_t st) {
   static thread_local bool attr_set = false;
@@ -209,11 +212,24 @@ int launch_chunk_sweep(const CUtensorMap& tmap, const b200m::ChunkParams& cp, in
                                   static_cast<int>(kChunk256SmemBytes)));
     CUDA_TRY(cudaFuncSetAttribute(b200m::chunk_sweep256_kernel<true, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   static_cast<int>(kChunk256SmemBytes)));
+
+    CUDA_TRY(cudaFuncSetAttribute(b200m::pair::chunk_sweep_pair_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  static_cast<int>(kChunkPairSmemBytes)));
+    CUDA_TRY(cudaFuncSetAttribute(b200m::pair::chunk_sweep_pair_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  static_cast<int>(kChunkPairSmemBytes)));
     attr_set = true;
   }
   {
     ProfScope ps(&g_prof.first, st);
-    if (g_opt.kernel == 5 && cp.peak)
+    if (g_opt.kernel == 6) {
+      // whole CTA pairs (the kernel carries __cluster_dims__(2, 1, 1)); work items are blocks of 512 rows
+      const int64_t items = static_cast<int64_t>(cp.n_pairs) * ((cp.k_stride + 511) / 512);
+      const int pgrid = 2 * static_cast<int>(std::min<int64_t>(std::max<int64_t>(items, 1), std::max(grid / 2, 1)));
+      if (cp.peak)
+        b200m::pair::chunk_sweep_pair_kernel<true><<<pgrid, b200m::kThreads, kChunkPairSmemBytes, st>>>(tmap, cp);
+      else
+        b200m::pair::chunk_sweep_pair_kernel<false><<<pgrid, b200m::kThreads, kChunkPairSmemBytes, st>>>(tmap, cp);
+    } else if (g_opt.kernel == 5 && cp.peak)
       b200m::chunk_sweep256_kernel<true, 32><<<grid, b200m::kThreads256, kChunk256SmemBytes, st>>>(tmap, cp);
     else if (g_opt.kernel == 5 && cp.chunk_cols == 64)
       b200m::chunk_sweep256_kernel<false, 64><<<grid, b200m::kThreads256, kChunk256SmemBytes, st>>>(tmap, cp);
@@ -644,8 +660,8 @@ int b200m_match_pairs_u8(const uint8_t* bank, const int32_t* norm_table, const u
       cp.blocks_per_pair = static_cast<int32_t>(k_stride / b200m::kRows);
       cp.rowres = w.rowres;
       cp.peak = g_opt.epilogue == 2 ? 1 : 0;
-      cp.chunk_cols = (g_opt.kernel == 5 && g_opt.chunk == 64 && !cp.peak) ? 64 : 32;
-      rc = launch_chunk_sweep(tmap_sbank, cp, sweep_grid(nb * cp.blocks_per_pair), st);
+      cp.chunk_cols = g_opt.kernel == 6 ? 64 : (g_opt.kernel == 5 && g_opt.chunk == 64 && !cp.peak) ? 64 : 32;
+      rc = launch_chunk_sweep(tmap_sbank, cp, g_opt.kernel == 6 ? sweep_grid(1 << 20) : sweep_grid(nb * cp.blocks_per_pair), st);
       if (rc) return rc;
       CUDA_TRY(cudaMemsetAsync(w.fb_count, 0, sizeof(int32_t) * (B + 64), st));   // per-pair counts, the batch total at [B], the verify work-list length at [B + 1]
       b200m::RefineParams rp;

@@ -171,7 +171,8 @@ int b200m_vq_f32(const float* obs, int64_t n_obs, int32_t dim, const double* cod
  *   "pipeline"  2 = chunk sweep on the norm-sorted bank + exact refine / fallback / verify (default),
  *               1 = top-1 sweep + lazy ratio / mutual verify sweeps over the candidates,
  *               0 = exact top-2 sweep + lazy mutual verify sweep
- *   "kernel"    5 = chunk sweep with N256 MMAs / two accumulators (default), 3 = N128 / four accumulators;
+ *   "kernel"    5 = chunk sweep with N256 MMAs / two accumulators (default), 3 = N128 / four accumulators,
+ *               6 = CTA-pair chunk sweep (cta_group::2, four N128 accumulators; slower, kept for comparison);
  *               exact sweeps: 4 = CTA-pair kernel (cta_group::2), otherwise single-CTA
  *   "chunk"     columns per chunk of the chunk sweep: 64 (default, kernel 5 only) or 32
  *   "grid"      number of persistent CTAs, 0 = one per SM (default)

@@ -21,8 +21,8 @@ DEFAULT_PIPELINE = 2
 DEFAULT_CHUNK = 64
 
 
-@pytest.fixture(scope="module", params=[(1, 2, 3), (1, 2, 5, 32), (1, 2, 5, 64), (1, 1, 4), (1, 0, 4), (0, 0, 4), (1, 1, 3), (1, 0, 3), (0, 0, 3)],
-                ids=["chunk_refine", "chunk256x32_refine", "chunk256x64_refine", "pair_top1_verify", "pair_top2_reject", "pair_top2_exact", "top1_verify", "top2_reject",
+@pytest.fixture(scope="module", params=[(1, 2, 3), (1, 2, 5, 32), (1, 2, 5, 64), (1, 2, 6), (1, 1, 4), (1, 0, 4), (0, 0, 4), (1, 1, 3), (1, 0, 3), (0, 0, 3)],
+                ids=["chunk_refine", "chunk256x32_refine", "chunk256x64_refine", "chunkpair_refine", "pair_top1_verify", "pair_top2_reject", "pair_top2_exact", "top1_verify", "top2_reject",
                      "top2_exact"])
 def epi(pkg, request):
     """(epilogue, pipeline, kernel): the default chunk sweep on the norm-sorted bank + refine + exact
