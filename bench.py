@@ -260,9 +260,16 @@ def main():
     pairs_per_launch = P * args.steps / max(prof["first_sweeps"], 1)
     achieved = ops_per_pair * pairs_per_launch / (sweep_ms_per_launch / 1e3) / 1e12
     int8_peak = 2.0 * float(peaks.get("bf16_tflops_sustained", peaks.get("bf16_tflops")))
+    traffic, traffic_src = None, None
+    tpath = os.path.join(ROOT, "profiles", "r01e_traffic.json")
+    if os.path.exists(tpath) and pkg.get_option("kernel") == 5 and pkg.get_option("chunk") == 64 and K == 16384:
+        with open(tpath) as f:
+            tj = json.load(f)
+        traffic = tj["dram_bytes_read_per_launch"] + tj["dram_bytes_write_per_launch"]
+        traffic_src = tj["source"]
     roofline = {
         "bound": "tensor", "achieved": achieved, "peak": int8_peak, "unit": "TFLOP/s", "frac": achieved / int8_peak,
-        "traffic": None,
+        "traffic": traffic, "traffic_unit": "bytes of DRAM read + written per launch (ncu)", "traffic_source": traffic_src,
         "kernel": ("b200m::chunk_sweep256_kernel<0,%d>" % pkg.get_option("chunk")) if pkg.get_option("kernel") == 5
                   else "b200m::chunk_sweep_kernel",
         "peak_source": f"2 x bf16_tflops_sustained of MEASURED_PEAKS.json ({peak_kind}): int8 tcgen05 rate is twice the bf16 rate; "
