@@ -83,7 +83,14 @@ class DescriptorBank:
 
     @classmethod
     def from_arrays(cls, arrays: Sequence, device="cuda", k_stride: int | None = None) -> "DescriptorBank":
-        """arrays: one [K_i,128] array per image (u8, or integer-valued float as cv2.SIFT emits)."""
+        """arrays: one [K_i,128] array per image (u8, or integer-valued float as cv2.SIFT emits).
+        CUDA tensors already on `device` are verified and packed there (no host round trip)."""
+        dev = torch.device(device)
+        if dev.type != "cuda":
+            raise RuntimeError("the descriptor bank must live on a CUDA device (there is no CPU path)")
+        if len(arrays) and all(isinstance(a, torch.Tensor) and a.is_cuda and
+                               (dev.index is None or a.device == dev) for a in arrays):
+            return cls._from_device_tensors(list(arrays), k_stride)
         u8 = [to_u8_descriptors(a) for a in arrays]
         if not u8:
             raise ValueError("empty descriptor list")
@@ -98,10 +105,33 @@ class DescriptorBank:
         for i, a in enumerate(u8):
             hv[i, :a.shape[0]] = a
         kpi = torch.tensor([a.shape[0] for a in u8], dtype=torch.int32)
-        dev = torch.device(device)
-        if dev.type != "cuda":
-            raise RuntimeError("the descriptor bank must live on a CUDA device (there is no CPU path)")
         return cls.from_packed(host.to(dev, non_blocking=True), kpi.to(dev))
+
+    @classmethod
+    def _from_device_tensors(cls, ts, k_stride: int | None) -> "DescriptorBank":
+        for t in ts:
+            if t.dim() != 2 or t.shape[1] != DESC_DIM:
+                raise ValueError(f"descriptors must be [K,{DESC_DIM}], got {tuple(t.shape)}")
+        kmax = max(int(t.shape[0]) for t in ts)
+        ks = round_up(max(kmax, 1), TILE_T) if k_stride is None else int(k_stride)
+        if ks % TILE_T or ks < kmax:
+            raise ValueError("k_stride must be a multiple of 256 and >= the largest image")
+        dev = ts[0].device
+        desc = torch.zeros((len(ts), ks, DESC_DIM), dtype=torch.uint8, device=dev)
+        bad = []
+        for i, t in enumerate(ts):
+            t = t.detach()
+            if t.dtype != torch.uint8:
+                r = t.round()
+                if t.numel():
+                    bad.append(((r != t) | (r < 0) | (r > 255)).any())
+                t = r.to(torch.uint8)
+            desc[i, :t.shape[0]] = t
+        if bad and bool(torch.stack(bad).any().item()):
+            raise ValueError("the exact u8 path needs integer-valued descriptors in [0,255] (OpenCV SIFT); "
+                             "float descriptors (DISK/SuperPoint) are not handled by this path")
+        kpi = torch.tensor([int(t.shape[0]) for t in ts], dtype=torch.int32)
+        return cls.from_packed(desc, kpi)
 
     # ------------------------------------------------------------------ accessors
     @property

@@ -257,8 +257,9 @@ class B200Matcher:
             assert d0.shape[-1] == 128 and d1.shape[-1] == 128        # lightglue.py:365-366
             bank = DescriptorBank.from_arrays([d0[0], d1[0]], device=self.device)
             res = match_pairs(bank, [[0, 1]], ratio=self.conf.ratio, mutual=self.conf.mutual)
-        res.check_overflow()
-        s = int(res.count[0].item())
+        s = int(res.count[0].item())      # the call's one host sync
+        if s > res.cap:
+            raise OverflowError(f"the pair produced {s} matches but cap is {res.cap}")
         q = res.query_idx[0, :s].long()
         t = res.train_idx[0, :s].long()
         dist = res.dist[0, :s]

@@ -255,3 +255,23 @@ def test_lightglue_shaped_adapter(pkg, golden_dir):
     assert np.array_equal(idx0, g["m_q"]) and np.array_equal(idx1, g["m_t"])
     m0 = out["matches0"][0].cpu().numpy()
     assert (m0[idx0] == idx1).all() and (m0 >= 0).sum() == len(idx0)
+
+
+def test_lightglue_shaped_adapter_cuda_inputs(pkg, golden_dir):
+    """matching.py:107-120 builds the feature tensors on the device: descriptors that already live on the GPU
+    are verified and packed there (no host round trip) and give the same lists; non-integer values are refused."""
+    g = np.load(os.path.join(golden_dir, "sift_pair.npz"))
+    m = pkg.B200Matcher().eval().to("cuda")
+    d0 = torch.from_numpy(g["q"].astype(np.float32))[None].cuda()
+    d1 = torch.from_numpy(g["t"].astype(np.float32))[None].cuda()
+    out = m({"image0": {"descriptors": d0}, "image1": {"descriptors": d1}})
+    matches = out["matches"][0]
+    assert np.array_equal(matches[..., 0].cpu().numpy(), g["m_q"]) and np.array_equal(matches[..., 1].cpu().numpy(), g["m_t"])
+    # u8 tensors on the device take the same path
+    bank = pkg.DescriptorBank.from_arrays([d0[0].to(torch.uint8), d1[0].to(torch.uint8)], device="cuda")
+    q, t, _ = pkg.match_pairs(bank, [[0, 1]]).to_lists()[0]
+    assert np.array_equal(q, g["m_q"]) and np.array_equal(t, g["m_t"])
+    with pytest.raises(ValueError):
+        m({"image0": {"descriptors": d0 + 0.25}, "image1": {"descriptors": d1}})
+    with pytest.raises(ValueError):
+        m({"image0": {"descriptors": d0 - 300.0}, "image1": {"descriptors": d1}})
