@@ -9,5 +9,6 @@ from .bank import DescriptorBank, FloatBank, to_u8_descriptors  # noqa: F401
 from .matcher import (B200Matcher, FlatMatches, MatchConfig, PairMatches, knn2_pairs, knn_match,  # noqa: F401
                       match, match_float, match_pairs, match_pairs_float, match_pairs_host)
 from .assignment import AssignmentHead, assign_pairs  # noqa: F401
+from .geometry import PoseBatch, essential_ransac  # noqa: F401
 from .driver import Gates, bow_view_graph, match_view_graph, run_matching_stage, save_matches, vq_words  # noqa: F401
 from .scheduler import blocked_order, exhaustive_pairs, partition, window_pairs, window_shard  # noqa: F401

@@ -27,6 +27,9 @@ SYMBOLS = (
     "b200m_workspace_bytes_bf16",
     "b200m_match_pairs_bf16",
     "b200m_workspace_bytes_assign",
+    "b200m_workspace_bytes_ransac",
+    "b200m_essential_ransac_f32",
+    "b200m_five_point_f64",
     "b200m_assign_pairs_bf16",
     "b200m_vq_f32",
     "b200m_compact_matches",
@@ -84,6 +87,13 @@ def lib() -> C.CDLL:
     L.b200m_assign_pairs_bf16.restype = C.c_int
     L.b200m_assign_pairs_bf16.argtypes = [vp, vp, vp, i32, i64, i32, vp, i64, C.c_float, C.c_int, vp, vp, vp, vp, i64,
                                           vp, sz, vp]
+    L.b200m_workspace_bytes_ransac.restype = sz
+    L.b200m_workspace_bytes_ransac.argtypes = [i64, i32]
+    L.b200m_essential_ransac_f32.restype = C.c_int
+    L.b200m_essential_ransac_f32.argtypes = [vp, vp, i64, i32, C.c_float, C.c_uint64, C.c_float, vp, vp, vp, vp, vp, vp, vp,
+                                             vp, sz, vp]
+    L.b200m_five_point_f64.restype = C.c_int
+    L.b200m_five_point_f64.argtypes = [vp, vp, vp, vp, vp]
     L.b200m_match_pairs_bf16.restype = C.c_int
     L.b200m_match_pairs_bf16.argtypes = [vp, vp, i32, i64, i32, vp, i64, C.c_float, C.c_int, C.c_int, vp, vp, vp, vp, i64,
                                          vp, sz, vp]

@@ -19,6 +19,7 @@
 #include "match_sort.cuh"
 #include "match_float.cuh"
 #include "match_vq.cuh"
+#include "match_ransac.cuh"
 
 namespace {
 
@@ -870,6 +871,75 @@ int b200m_assign_pairs_bf16(const void* mdesc_bf16, const float* matchability, c
     }
     CUDA_TRY(cudaGetLastError());
   }
+  return B200M_OK;
+}
+
+size_t b200m_workspace_bytes_ransac(int64_t n_pairs, int32_t iters) {
+  if (n_pairs <= 0 || iters <= 0) return 256;
+  const int64_t bpp = (iters + b200m::geo::kRansacThreads - 1) / b200m::geo::kRansacThreads;
+  return static_cast<size_t>(n_pairs * bpp) * (sizeof(int32_t) + 9 * sizeof(double)) + 512;
+}
+
+int b200m_essential_ransac_f32(const float* matches_xyxy, const int64_t* offsets, int64_t n_pairs, int32_t iters,
+                               float threshold_norm, uint64_t seed, float max_depth, double* out_E, uint8_t* out_mask,
+                               int32_t* out_inliers, double* out_R, double* out_t, uint8_t* out_pose_mask,
+                               int32_t* out_pose_inliers, void* workspace, size_t workspace_bytes, void* stream) {
+  if (n_pairs == 0) return B200M_OK;
+  if (!matches_xyxy || !offsets || n_pairs < 0 || iters <= 0 || !(threshold_norm > 0.f))
+    return fail(B200M_E_BAD_ARG, "null matches / offsets, or bad n_pairs / iters / threshold%s");
+  if (!out_E || !out_mask || !out_inliers || !out_R || !out_t || !out_pose_mask || !out_pose_inliers || !workspace)
+    return fail(B200M_E_BAD_ARG, "null output / workspace%s");
+  if (n_pairs > 65535) return fail(B200M_E_BAD_ARG, "at most 65535 pairs per call%s");
+  if ((reinterpret_cast<uintptr_t>(matches_xyxy) & 15) != 0) return fail(B200M_E_BAD_ARG, "matches must be 16-byte aligned%s");
+  if (workspace_bytes < b200m_workspace_bytes_ransac(n_pairs, iters)) return fail(B200M_E_WORKSPACE, "workspace too small%s");
+  if (device_info().ok != 1) return fail(B200M_E_NO_DEVICE, "no sm_100 CUDA device available (no CPU fallback)%s");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int bpp = (iters + b200m::geo::kRansacThreads - 1) / b200m::geo::kRansacThreads;
+  double* blk_E = reinterpret_cast<double*>((reinterpret_cast<uintptr_t>(workspace) + 255) & ~uintptr_t(255));
+  int32_t* blk_count = reinterpret_cast<int32_t*>(blk_E + static_cast<size_t>(n_pairs) * bpp * 9);
+  b200m::geo::RansacParams rp;
+  rp.matches = reinterpret_cast<const float4*>(matches_xyxy);
+  rp.offsets = offsets;
+  rp.n_pairs = static_cast<int32_t>(n_pairs);
+  rp.blocks_per_pair = bpp;
+  rp.thr2 = threshold_norm * threshold_norm;
+  rp.seed = seed;
+  rp.blk_count = blk_count;
+  rp.blk_E = blk_E;
+  {
+    ProfScope ps(&g_prof.first, st);
+    b200m::geo::ransac_kernel<<<dim3(bpp, static_cast<unsigned>(n_pairs)), b200m::geo::kRansacThreads, 0, st>>>(rp);
+  }
+  CUDA_TRY(cudaGetLastError());
+  b200m::geo::PoseParams pp;
+  pp.matches = rp.matches;
+  pp.offsets = offsets;
+  pp.n_pairs = rp.n_pairs;
+  pp.blocks_per_pair = bpp;
+  pp.thr2 = rp.thr2;
+  pp.max_depth = max_depth > 0.f ? max_depth : 50.f;
+  pp.blk_count = blk_count;
+  pp.blk_E = blk_E;
+  pp.out_E = out_E;
+  pp.out_mask = out_mask;
+  pp.out_inliers = out_inliers;
+  pp.out_R = out_R;
+  pp.out_t = out_t;
+  pp.out_pose_mask = out_pose_mask;
+  pp.out_pose_inliers = out_pose_inliers;
+  {
+    ProfScope ps(&g_prof.emit, st);
+    b200m::geo::pose_kernel<<<static_cast<unsigned>(n_pairs), b200m::geo::kPoseThreads, 0, st>>>(pp);
+  }
+  CUDA_TRY(cudaGetLastError());
+  return B200M_OK;
+}
+
+int b200m_five_point_f64(const double* x0, const double* x1, double* out_E, int32_t* out_n, void* stream) {
+  if (!x0 || !x1 || !out_E || !out_n) return fail(B200M_E_BAD_ARG, "null argument%s");
+  if (device_info().ok != 1) return fail(B200M_E_NO_DEVICE, "no sm_100 CUDA device available (no CPU fallback)%s");
+  b200m::geo::five_point_debug_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(x0, x1, out_E, out_n);
+  CUDA_TRY(cudaGetLastError());
   return B200M_OK;
 }
 

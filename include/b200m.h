@@ -165,6 +165,29 @@ int b200m_assign_pairs_bf16(const void* mdesc_bf16, const float* matchability, c
 int b200m_vq_f32(const float* obs, int64_t n_obs, int32_t dim, const double* codebook, int32_t n_codes,
                  int32_t* out_code, double* out_dist, double* code_sqr_scratch, void* stream);
 
+/* Batched geometric verification of match lists, the step after the matcher in the reference
+ * (matching.py:133-142): cv2.findEssentialMat(k0, k1, K, method=RANSAC, prob=0.999, threshold=1)
+ * followed by cv2.recoverPose(E, k0[mask], k1[mask], K).
+ *   matches_xyxy  float32 [total, 4] (16-byte aligned): (x0, y0, x1, y1) of every match of every pair in
+ *                 NORMALISED image coordinates (pixel / focal for the reference's K = diag(f, f, 1))
+ *   offsets       int64 [n_pairs + 1]: matches of pair p are rows [offsets[p], offsets[p+1])
+ *   iters         RANSAC hypotheses per pair (rounded up to a multiple of 128; cv2's maxIters is 1000)
+ *   threshold_norm  Sampson threshold in normalised units (threshold_px / focal); max_depth: recoverPose's
+ *                 distanceThresh (<= 0 -> 50)
+ * Per pair: out_E [9] (row-major, unit Frobenius norm; zeros when the pair has < 5 matches or no model),
+ * out_mask [total] / out_inliers: Sampson inliers of the best model; out_R [9], out_t [3] (unit), out_pose_mask /
+ * out_pose_inliers: the (R, t) candidate with the most inliers in front of both cameras and those inliers.
+ * Five-point minimal solver (Nister) per hypothesis; deterministic for a given seed; parity with cv2 is
+ * statistical (RANSAC draws differ), see tests/test_gpu_geometry.py. */
+size_t b200m_workspace_bytes_ransac(int64_t n_pairs, int32_t iters);
+int b200m_essential_ransac_f32(const float* matches_xyxy, const int64_t* offsets, int64_t n_pairs, int32_t iters,
+                               float threshold_norm, uint64_t seed, float max_depth,
+                               double* out_E, uint8_t* out_mask, int32_t* out_inliers,
+                               double* out_R, double* out_t, uint8_t* out_pose_mask, int32_t* out_pose_inliers,
+                               void* workspace, size_t workspace_bytes, void* stream);
+/* One minimal solve (test hook): x0, x1 float64 [5, 2] device -> out_E float64 [10, 9], *out_n solutions. */
+int b200m_five_point_f64(const double* x0, const double* x1, double* out_E, int32_t* out_n, void* stream);
+
 /* Tuning / introspection knobs (process-global, read at launch time).
  *   "epilogue"  0 = exact insertion of every element (debug), 1 = threshold-reject (default),
  *               2 = MMA-only ceiling measurement (results invalid)
