@@ -132,13 +132,33 @@ def directed_edges(connection) -> np.ndarray:
 
 
 # ---------------------------------------------------------------------- the walk
+def verify_edges_gpu(all_points, pair_matches, gates: "Gates", focal: float = FOCAL_LENGTH, device="cuda",
+                     iters: int = 1024, seed: int = 0) -> dict:
+    """Pose-inlier count of every cached edge in ONE batched call (geometry.essential_ransac): what the
+    reference computes per visited edge with cv2.findEssentialMat + cv2.recoverPose (matching.py:133-142).
+    Edges the reference skips before the geometry (`len(kpts0) <= 8`, matching.py:130) are left out."""
+    from .geometry import essential_ransac
+    keys = [k for k, (q, _) in pair_matches.items() if len(q) > gates.min_matches_for_pose]
+    if not keys:
+        return {}
+    p0 = [np.asarray(all_points[a])[np.asarray(pair_matches[(a, b)][0], dtype=np.int64)] for a, b in keys]
+    p1 = [np.asarray(all_points[b])[np.asarray(pair_matches[(a, b)][1], dtype=np.int64)] for a, b in keys]
+    res = essential_ransac(p0, p1, focal, threshold=1.0, iters=iters, seed=seed, device=device)
+    return {k: int(c) for k, c in zip(keys, res.pose_inliers)}
+
+
 def match_view_graph(all_descriptors, all_points, connection, start: int, conf: MatchConfig | None = None,
-                     gates: Gates | None = None, focal: float = FOCAL_LENGTH, device="cuda", pair_matches=None):
+                     gates: Gates | None = None, focal: float = FOCAL_LENGTH, device="cuda", pair_matches=None,
+                     geometry: str = "cv2"):
     """-> (img_pairs [(reference_id, id), ...], all_matches [[idx0, idx1, point3d_ids], ...]).
 
     pair_matches: optional {(a, b): (idx0, idx1)} to replay the walk on precomputed matches
-    (tests inject an oracle here); by default all directed edges are matched on the GPU in one call."""
+    (tests inject an oracle here); by default all directed edges are matched on the GPU in one call.
+    geometry: "cv2" = the reference's own calls per visited edge (matching.py:133-142); "gpu" = every edge
+    verified up front in one batched launch (verify_edges_gpu), the walk reads the cached inlier counts."""
     import cv2
+    if geometry not in ("cv2", "gpu"):
+        raise ValueError("geometry must be 'cv2' or 'gpu'")
     conf = conf or MatchConfig()
     gates = gates or Gates()
     n = len(all_descriptors)
@@ -152,6 +172,7 @@ def match_view_graph(all_descriptors, all_points, connection, start: int, conf: 
                 pair_matches[(a, b)] = (q, t)
 
     K = np.array([[focal, 0, 0], [0, focal, 0], [0, 0, 1]])
+    pose_inliers = verify_edges_gpu(all_points, pair_matches, gates, focal, device) if geometry == "gpu" else None
     next_id = 0
     tracks = [None] * n                 # per image: 3-D point id of every keypoint, -1 = none
     all_matches = []
@@ -186,15 +207,19 @@ def match_view_graph(all_descriptors, all_points, connection, start: int, conf: 
             idx1 = np.asarray(idx1, dtype=np.int64)
             if len(idx0) <= gates.min_matches_for_pose:
                 continue
-            k0 = np.asarray(all_points[ref])[idx0].astype(np.float32)
-            k1 = np.asarray(all_points[nb])[idx1].astype(np.float32)
-            E, mask = cv2.findEssentialMat(k0, k1, K, method=cv2.RANSAC, prob=0.999, threshold=1)
-            if mask is None:
-                continue
-            keep = mask.ravel() > 0
-            _, _, _, inl = cv2.recoverPose(E, k0[keep], k1[keep], K)
-            if int((inl.ravel() > 0).sum()) <= gates.min_pose_inliers:
-                continue
+            if pose_inliers is not None:
+                if pose_inliers.get((ref, nb), 0) <= gates.min_pose_inliers:
+                    continue
+            else:
+                k0 = np.asarray(all_points[ref])[idx0].astype(np.float32)
+                k1 = np.asarray(all_points[nb])[idx1].astype(np.float32)
+                E, mask = cv2.findEssentialMat(k0, k1, K, method=cv2.RANSAC, prob=0.999, threshold=1)
+                if mask is None:
+                    continue
+                keep = mask.ravel() > 0
+                _, _, _, inl = cv2.recoverPose(E, k0[keep], k1[keep], K)
+                if int((inl.ravel() > 0).sum()) <= gates.min_pose_inliers:
+                    continue
             if not tracks[ref]:
                 tracks[ref] = [-1] * np.asarray(all_points[ref]).shape[0]
             if not tracks[nb]:
@@ -231,11 +256,12 @@ def match_view_graph(all_descriptors, all_points, connection, start: int, conf: 
 
 
 def run_matching_stage(output_dir: str = "output", conf: MatchConfig | None = None, gates: Gates | None = None,
-                       device="cuda"):
+                       device="cuda", geometry: str = "cv2"):
     """The whole stage: stage files in -> img_pairs.npy / all_matches.npy out (matching.py as a function)."""
     all_descriptors, all_points, _ = load_features(output_dir)
     k, codebook = load_codebook(output_dir)
     connection, start = bow_view_graph(all_descriptors, k, codebook, device=device)
-    pairs, matches = match_view_graph(all_descriptors, all_points, connection, start, conf, gates, device=device)
+    pairs, matches = match_view_graph(all_descriptors, all_points, connection, start, conf, gates, device=device,
+                                      geometry=geometry)
     save_matches(pairs, matches, output_dir)
     return pairs, matches

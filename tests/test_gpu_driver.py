@@ -35,6 +35,9 @@ def test_driver_equals_reference_loop(pkg, tmp_path):
     # 2. the product matcher as the callable of the reference's own loop (matching.py:122 unchanged)
     via_callable = oracle_driver.reference_loop(desc, pts, size, connection, start, pkg.B200Matcher(), min_matches=60)
     _same(ref, via_callable)
+    # 2b. geometric verification batched on the GPU instead of cv2 per edge: same accepted edges, same rows
+    got_gpu = drv.match_view_graph(desc, pts, connection, start, gates=drv.Gates(min_matches=60), geometry="gpu")
+    _same(ref, got_gpu)
     # 3. stage files for sfm.py
     drv.save_matches(*got, output_dir=str(tmp_path))
     all_matches = np.load(os.path.join(str(tmp_path), "all_matches.npy"), allow_pickle=True)
