@@ -318,6 +318,16 @@ __device__ __forceinline__ float sampson2(const float* e, const float4 m) {
   const float num = fmaf(m.z, a, fmaf(m.w, b, c));
   return num * num / (a * a + b * b + at * at + bt * bt);
 }
+// the same test without the division: sampson2 < thr2
+__device__ __forceinline__ bool sampson_inlier(const float* e, const float4 m, float thr2) {
+  const float a = fmaf(e[0], m.x, fmaf(e[1], m.y, e[2]));
+  const float b = fmaf(e[3], m.x, fmaf(e[4], m.y, e[5]));
+  const float c = fmaf(e[6], m.x, fmaf(e[7], m.y, e[8]));
+  const float at = fmaf(e[0], m.z, fmaf(e[3], m.w, e[6]));
+  const float bt = fmaf(e[1], m.z, fmaf(e[4], m.w, e[7]));
+  const float num = fmaf(m.z, a, fmaf(m.w, b, c));
+  return num * num < thr2 * (a * a + b * b + at * at + bt * bt);
+}
 
 __global__ void __launch_bounds__(kRansacThreads)
 ransac_kernel(const RansacParams p) {
@@ -329,6 +339,11 @@ ransac_kernel(const RansacParams p) {
   int best = -1;
   double bestE[9];
   for (int e = 0; e < 9; ++e) bestE[e] = 0.0;
+  // best count any thread of this CTA has reached so far: a candidate that can no longer reach it stops
+  // being scored (it could not win; candidates that can still TIE go on, so the winner does not depend on timing)
+  __shared__ int s_blk_best;
+  if (threadIdx.x == 0) s_blk_best = 0;
+  __syncthreads();
   if (S >= 5) {
     uint64_t rng = p.seed ^ (static_cast<uint64_t>(pair) << 32) ^ static_cast<uint64_t>(hyp) * 0xD1342543DE82EF95ull;
     int idx[5];
@@ -351,10 +366,15 @@ ransac_kernel(const RansacParams p) {
       float e[9];
       for (int k = 0; k < 9; ++k) e[k] = static_cast<float>(Es[c][k]);
       int cnt = 0;
-      for (int i = 0; i < S; ++i) cnt += sampson2(e, __ldg(m + i)) < p.thr2 ? 1 : 0;
+      for (int i0 = 0; i0 < S; i0 += 64) {
+        const int lim = min(S, i0 + 64);
+        for (int i = i0; i < lim; ++i) cnt += sampson_inlier(e, __ldg(m + i), p.thr2) ? 1 : 0;
+        if (cnt + (S - lim) < max(best, *reinterpret_cast<volatile int*>(&s_blk_best))) { cnt = -1; break; }
+      }
       if (cnt > best) {
         best = cnt;
         for (int k = 0; k < 9; ++k) bestE[k] = Es[c][k];
+        atomicMax(&s_blk_best, cnt);
       }
     }
   }
