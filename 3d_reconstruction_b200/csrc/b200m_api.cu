@@ -889,7 +889,6 @@ int b200m_essential_ransac_f32(const float* matches_xyxy, const int64_t* offsets
     return fail(B200M_E_BAD_ARG, "null matches / offsets, or bad n_pairs / iters / threshold%s");
   if (!out_E || !out_mask || !out_inliers || !out_R || !out_t || !out_pose_mask || !out_pose_inliers || !workspace)
     return fail(B200M_E_BAD_ARG, "null output / workspace%s");
-  if (n_pairs > 65535) return fail(B200M_E_BAD_ARG, "at most 65535 pairs per call%s");
   if ((reinterpret_cast<uintptr_t>(matches_xyxy) & 15) != 0) return fail(B200M_E_BAD_ARG, "matches must be 16-byte aligned%s");
   if (workspace_bytes < b200m_workspace_bytes_ransac(n_pairs, iters)) return fail(B200M_E_WORKSPACE, "workspace too small%s");
   if (device_info().ok != 1) return fail(B200M_E_NO_DEVICE, "no sm_100 CUDA device available (no CPU fallback)%s");
@@ -906,9 +905,12 @@ int b200m_essential_ransac_f32(const float* matches_xyxy, const int64_t* offsets
   rp.seed = seed;
   rp.blk_count = blk_count;
   rp.blk_E = blk_E;
-  {
+  rp.pair0 = 0;
+  for (int64_t p0 = 0; p0 < n_pairs; p0 += 65535) {      // gridDim.y limit
+    const int64_t np = std::min<int64_t>(65535, n_pairs - p0);
+    rp.pair0 = static_cast<int32_t>(p0);
     ProfScope ps(&g_prof.first, st);
-    b200m::geo::ransac_kernel<<<dim3(bpp, static_cast<unsigned>(n_pairs)), b200m::geo::kRansacThreads, 0, st>>>(rp);
+    b200m::geo::ransac_kernel<<<dim3(bpp, static_cast<unsigned>(np)), b200m::geo::kRansacThreads, 0, st>>>(rp);
   }
   CUDA_TRY(cudaGetLastError());
   b200m::geo::PoseParams pp;

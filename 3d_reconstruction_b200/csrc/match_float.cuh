@@ -94,8 +94,12 @@ __device__ __forceinline__ float fmax16(const int (&v)[16]) {
   return fmaxf(fmaxf(m[0], m[1]), fmaxf(m[2], m[3]));
 }
 
-// sixteen columns of one row starting at column c0; n_cols = valid columns of the sweep
-__device__ __forceinline__ void ip_process16(int (&v)[16], int c0, int n_cols, float& best, int& bidx) {
+// sixteen columns of one row starting at column c0; n_cols = valid columns of the sweep.
+// A new row maximum only records the group (c0) and keeps a copy of its sixteen values; the column inside
+// the group is looked up once per work item (ip_locate). With 32 independent rows per warp nearly every
+// group holds a new maximum for SOME lane, so the per-group cost of that path is what matters: sixteen
+// predicated moves instead of a sixteen-step compare / select chain.
+__device__ __forceinline__ void ip_process16(int (&v)[16], int c0, int n_cols, float& best, int& bidx, int (&keep)[16]) {
   if (c0 + 16 > n_cols) {   // ragged end (and padding columns: zero vectors must not compete)
 #pragma unroll
     for (int j = 0; j < 16; ++j)
@@ -104,12 +108,19 @@ __device__ __forceinline__ void ip_process16(int (&v)[16], int c0, int n_cols, f
   const float m = fmax16(v);
   if (m > best) {           // strict: an equal value further right never replaces the lowest column
     best = m;
-    int j = 15;
+    bidx = c0;
 #pragma unroll
-    for (int jj = 14; jj >= 0; --jj)
-      if (__int_as_float(v[jj]) == m) j = jj;
-    bidx = c0 + j;
+    for (int j = 0; j < 16; ++j) keep[j] = v[j];
   }
+}
+// column of the maximum: lowest index inside the recorded group
+__device__ __forceinline__ int ip_locate(const int (&keep)[16], float best, int bidx) {
+  if (bidx < 0) return bidx;
+  int j = 15;
+#pragma unroll
+  for (int jj = 14; jj >= 0; --jj)
+    if (__int_as_float(keep[jj]) == best) j = jj;
+  return bidx + j;
 }
 
 // sixteen columns of one row: online log-sum-exp, (m, s) with sum_j exp(v_j) = s * exp(m)
@@ -265,6 +276,9 @@ ip_sweep_kernel(const __grid_constant__ CUtensorMap tmap, const IpParams p) {
       float best = kMode == kIpLse ? kLseFloor : kNegInf;   // kIpLse: running maximum
       int bidx = -1;                                          // kIpLse: unused
       float lsum = 0.f;                                       // kIpLse: running sum of exp(v - best)
+      int keep[16];                                           // arg-max modes: the sixteen values of the best group
+#pragma unroll
+      for (int j = 0; j < 16; ++j) keep[j] = 0;
       const float* bias = nullptr;                            // kIpBiasArgmax: nb of the opposite direction (= per column)
       if constexpr (kMode == kIpBiasArgmax)
         bias = p.nb + (static_cast<int64_t>(1 - dir) * p.n_pairs + pair) * p.k_stride;
@@ -273,7 +287,7 @@ ip_sweep_kernel(const __grid_constant__ CUtensorMap tmap, const IpParams p) {
           lse_process16(v, c0, n_cols, best, lsum);
         } else {
           if constexpr (kMode == kIpBiasArgmax) bias16(v, bias + c0);
-          ip_process16(v, c0, n_cols, best, bidx);
+          ip_process16(v, c0, n_cols, best, bidx, keep);
         }
       };
       // this warp owns the tiles whose global sequence number is e modulo 4
@@ -303,6 +317,7 @@ ip_sweep_kernel(const __grid_constant__ CUtensorMap tmap, const IpParams p) {
         }
       }
       t_seen += ntiles;
+      if constexpr (kMode != kIpLse) bidx = ip_locate(keep, best, bidx);
       // the four partial results of a row meet here
       if (e > 0) sm.rowmerge[par][e - 1][rl] = make_float2(best, kMode == kIpLse ? lsum : __int_as_float(bidx));
       named_bar_sync(kEpiBarrier, kEpiWarps * 32);

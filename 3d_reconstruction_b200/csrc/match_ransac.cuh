@@ -294,6 +294,7 @@ struct RansacParams {
   const float4* matches;     // [total] (x0, y0, x1, y1): normalised image coordinates of every match of every pair
   const int64_t* offsets;    // [n_pairs + 1] extent of each pair's matches
   int32_t n_pairs;
+  int32_t pair0;             // first pair of this launch (gridDim.y covers at most 65535 pairs)
   int32_t blocks_per_pair;   // hypotheses per pair = blocks_per_pair * kRansacThreads
   float thr2;                // squared Sampson threshold in normalised units: (threshold_px / focal)^2
   uint64_t seed;
@@ -331,7 +332,7 @@ __device__ __forceinline__ bool sampson_inlier(const float* e, const float4 m, f
 
 __global__ void __launch_bounds__(kRansacThreads)
 ransac_kernel(const RansacParams p) {
-  const int pair = blockIdx.y;
+  const int pair = p.pair0 + blockIdx.y;
   const int64_t o0 = p.offsets[pair];
   const int S = static_cast<int>(p.offsets[pair + 1] - o0);
   const float4* m = p.matches + o0;
