@@ -29,7 +29,8 @@ struct Options {
   int64_t epilogue = 1;
   int64_t grid = 0;
   int64_t batch = 0;
-  // chunk sweep (pipeline 2): 5 = N256 MMAs / two accumulators (default), otherwise N128 MMAs / four accumulators;
+  // chunk sweep (pipeline 2): 5 = N256 MMAs / two accumulators (default), 6 = CTA-pair kernel (slower, kept for
+  // comparison), otherwise N128 MMAs / four accumulators;
   // exact sweeps (pipelines 0 / 1, fallback, verify): 4 = CTA-pair kernel (cta_group::2), otherwise single-CTA
   int64_t kernel = 5;
   // 2 = chunk sweep on the norm-sorted bank + refine + exact fallback (default, needs the sorted bank),
