@@ -275,3 +275,15 @@ def test_lightglue_shaped_adapter_cuda_inputs(pkg, golden_dir):
         m({"image0": {"descriptors": d0 + 0.25}, "image1": {"descriptors": d1}})
     with pytest.raises(ValueError):
         m({"image0": {"descriptors": d0 - 300.0}, "image1": {"descriptors": d1}})
+
+
+def test_randomised_campaign(pkg):
+    """tools/stress_parity.py, a slice of it: ragged banks from four generators (uniform bytes, SIFT-like with
+    re-observed rows, tiny alphabets, constant rows), every ordered pair, random ratio / mutual settings; lists and
+    float32 distance bits equal the integer oracle's."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location(
+        "stress_parity", os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools", "stress_parity.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    mod.main(rounds=14, seed=123)
