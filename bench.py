@@ -162,6 +162,7 @@ def main():
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
+    args.warmup = max(args.warmup, 3)       # timing rule: at least three untimed warm-up steps (reported as run)
 
     import torch
     import torch.distributed as dist
