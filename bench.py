@@ -47,6 +47,46 @@ def measured_peaks():
     return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}, "fallback"
 
 
+def int8_peak_probe(pkg, bank, pairs_dev, out, workspace, ops_per_pair):
+    """MEASURED_PEAKS.json has no int8 entry: two live int8 dense rates on this box for context, outside every
+    timed region. (1) cuBLASLt IGEMM through torch._int_mm, 8192^3, a short burst and ~1.5 s sustained;
+    (2) this library's own sweep with the epilogue reduced to one tcgen05.ld per accumulator (option
+    epilogue = 2: TMA + MMA + hand-over only, results invalid) over one batch of 256 pairs."""
+    import torch
+    res = {}
+    n = min(256, int(pairs_dev.shape[0]))
+    pkg.set_option("epilogue", 2)
+    try:
+        pkg.match_pairs(bank, pairs_dev[:n], ratio=RATIO, mutual=True, cap=CAP, out=out, workspace=workspace)
+        pkg.set_option("profile", 1)
+        pkg.profile_read()
+        for _ in range(3):
+            pkg.match_pairs(bank, pairs_dev[:n], ratio=RATIO, mutual=True, cap=CAP, out=out, workspace=workspace)
+        torch.cuda.synchronize()
+        pr = pkg.profile_read()
+        res["mma_only_sweep_tops"] = ops_per_pair * n * 3 / (pr["first_sweep_ms"] / 1e3) / 1e12
+    finally:
+        pkg.set_option("profile", 0)
+        pkg.set_option("epilogue", 1)
+    try:
+        a = torch.randint(-128, 127, (8192, 8192), dtype=torch.int8, device=bank.device)
+        b = torch.randint(-128, 127, (8192, 8192), dtype=torch.int8, device=bank.device)
+        for _ in range(3):
+            torch._int_mm(a, b)
+        for name, iters in (("cublaslt_int_mm_8192_burst_tops", 20), ("cublaslt_int_mm_8192_sustained_tops", 1500)):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(iters):
+                torch._int_mm(a, b)
+            e1.record()
+            torch.cuda.synchronize()
+            res[name] = 2.0 * 8192 ** 3 * iters / (e0.elapsed_time(e1) / 1e3) / 1e12
+        del a, b
+    except Exception as ex:          # a missing cuBLASLt int8 path must not cost the bench line
+        res["cublaslt_int_mm_error"] = str(ex)[:120]
+    return res
+
+
 class ClockSampler(threading.Thread):
     """nvidia-smi clocks and throttle reasons during the timed region (B200_PROFILING.md recipe)."""
 
@@ -283,6 +323,8 @@ def main():
                                       ("verify_sweep_ms", "fallback_sweep_ms", "refine_ms", "select_ms", "emit_ms")},
     }
     gpu_launches = prof["launches"]
+    if world == 1:
+        roofline["int8_peak_probe"] = int8_peak_probe(pkg, bank, pairs_dev, out, workspace, ops_per_pair)
 
     # ------------------------------------------------------------------ end-to-end leg (host buffers)
     # every step: rank 0 host bank -> device (pinned), NCCL broadcast, local match, flat lists gathered
