@@ -67,3 +67,40 @@ def test_vq_words_equal_scipy(pkg):
     c0, s0 = oracle_driver.view_graph(desc, k, codebook, cos_thr=0.2)
     c1, s1 = drv.bow_view_graph(desc, k, codebook, cos_thr=0.2, device="cuda")
     assert s0 == s1 and [list(map(int, a)) for a in c0] == [list(map(int, a)) for a in c1]
+
+
+def test_driver_on_real_photographs(pkg, golden_dir):
+    """Real SIFT features of six of the reference's own photographs (tests/golden/make_golden_scene.py): the BoW
+    view graph with GPU visual words equals the scipy one, and the batched driver reproduces the restated
+    reference loop (cv2 matcher per visited edge) row for row -- with cv2 geometry per edge and with the batched
+    GPU geometry."""
+    drv = importlib.import_module("3d_reconstruction_b200.driver")
+    g = np.load(os.path.join(golden_dir, "ystad_scene.npz"))
+    n = 6
+    desc = np.array([None] * n, dtype=object)
+    pts = np.array([None] * n, dtype=object)
+    size = np.array([None] * n, dtype=object)
+    for i in range(n):
+        desc[i], pts[i], size[i] = g[f"desc{i}"].astype(np.float32), g[f"pts{i}"], g[f"size{i}"]
+    k, codebook = int(g["k"]), g["codebook"]
+    conn_ref, start_ref = oracle_driver.view_graph(desc, k, codebook, cos_thr=0.0)
+    conn, start = drv.bow_view_graph(desc, k, codebook, cos_thr=0.0, device="cuda")
+    assert start == start_ref and [list(map(int, c)) for c in conn] == [list(map(int, c)) for c in conn_ref]
+    ref = oracle_driver.reference_loop(desc, pts, size, conn, start, oracle_driver.cv2_matcher(), min_matches=60)
+    assert len(ref[0]) >= 3 and min(len(m[0]) for m in ref[1]) >= 60
+    got = drv.match_view_graph(desc, pts, conn, start, gates=drv.Gates(min_matches=60))
+    _same(ref, got)
+    # Batched GPU geometry on the same edges. These photographs include near-pure rotations (DSC_0001/0002: 437
+    # RANSAC inliers, none of which cv2 places in front of both cameras within its depth limit), where the
+    # cheirality count is ill-conditioned in any implementation -- so compare the well-conditioned edges only:
+    # every edge the reference loop accepted has a cv2 pose-inlier count the GPU count matches within 15 %.
+    from oracle import oracle_cv2, oracle_geometry
+    for (a, b), row in zip(ref[0], ref[1]):
+        k0, k1 = pts[a][row[0]], pts[b][row[1]]
+        cv = oracle_geometry.verify_pair(k0, k1, drv.FOCAL_LENGTH)
+        gp = pkg.essential_ransac([k0], [k1], drv.FOCAL_LENGTH, iters=2048, seed=1)
+        assert cv is not None and int(cv[4].sum()) > 10
+        assert abs(int(gp.pose_inliers[0]) - int(cv[4].sum())) <= 0.15 * int(cv[4].sum()) + 5, (a, b, gp.pose_inliers, cv[4].sum())
+        assert int(gp.inliers[0]) >= 0.9 * int(cv[1].sum())
+    got_gpu = drv.match_view_graph(desc, pts, conn, start, gates=drv.Gates(min_matches=60), geometry="gpu")
+    assert len(got_gpu[0]) >= 3 and all(len(r) == 3 and len(r[0]) == len(r[1]) == len(r[2]) for r in got_gpu[1])
