@@ -18,6 +18,11 @@
 //   warps 4-19   epilogue: warp (lane quadrant q, accumulator e) drains every 4th column tile for rows
 //                32q..32q+31: running (best value, lowest column) per row; the four partial results of a
 //                row meet through shared memory at the end of the item.
+// Bound: the shared-memory port (128 B/clk). An N = 128 bf16 MMA reads 8 KiB of operands per 64 clk (128 B/clk)
+// and the column stream is written at 64 B/clk (one 128-row block per column image): 192 B/clk asked of 128,
+// a ceiling of 67 % of the tensor peak -- where the D = 256 sweep sits (1.48 of 2.25 PFLOP/s). N = 256 tiles
+// (96 + 64 B/clk, 80 %) would need the row block single-buffered at D = 256 and expose a TMA round trip per
+// 2,048-column item; two row blocks per column stream do not fit next to a useful column ring.
 #pragma once
 #include <cuda_bf16.h>
 
