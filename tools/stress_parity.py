@@ -60,4 +60,11 @@ def main(rounds=40, seed=0):
 
 
 if __name__ == "__main__":
+    # usage: stress_parity.py [rounds] [seed] [pipeline] [kernel] [chunk]
+    if len(sys.argv) > 3:
+        pkg.set_option("pipeline", int(sys.argv[3]))
+    if len(sys.argv) > 4:
+        pkg.set_option("kernel", int(sys.argv[4]))
+    if len(sys.argv) > 5:
+        pkg.set_option("chunk", int(sys.argv[5]))
     main(rounds=int(sys.argv[1]) if len(sys.argv) > 1 else 40, seed=int(sys.argv[2]) if len(sys.argv) > 2 else 0)
