@@ -8,9 +8,20 @@ import numpy as np
 import pytest
 import torch
 
-from oracle import oracle_int
+from oracle import oracle_cv2, oracle_int
 
 pytestmark = pytest.mark.gpu
+
+
+def _check_sampled_cv2(desc, k, pairs, lists, sample):
+    """GPU == cv2 itself (BFMatcher knnMatch k=2 + ratio + cross-check on this box) on sampled pairs:
+    indices and the float32 distance bits."""
+    for p in sample:
+        a, b = map(int, pairs[p])
+        eq, et, ed = oracle_cv2.match(desc[a, :k].cpu().numpy().astype(np.float32), desc[b, :k].cpu().numpy().astype(np.float32), 0.75, True)
+        q, t, d = lists[p]
+        assert np.array_equal(q, eq) and np.array_equal(t, et), (a, b)
+        assert np.array_equal(np.asarray(d, np.float32).view(np.uint32), np.asarray(ed, np.float32).view(np.uint32)), (a, b)
 
 
 def _check_sampled(desc, k, pairs, lists, sample):
@@ -43,6 +54,32 @@ def test_config2_64_images_8192_exhaustive(pkg):
         assert len(set(t.tolist())) == len(t) and np.all(np.diff(q) > 0)      # one-to-one, ascending
     neighbours = [p for p, (a, b) in enumerate(pairs) if b - a == 1][:2]
     _check_sampled(desc, k, pairs, lists, neighbours + [len(pairs) // 2])
+    sample = np.random.default_rng(2).choice(len(pairs), size=8, replace=False).tolist()
+    _check_sampled_cv2(desc, k, pairs, lists, sample)
+
+
+def test_config3_257_images_16384_exhaustive(pkg):
+    """The bench workload itself (BASELINE.json config 3) once, with its properties and eight random pairs
+    (plus two neighbouring ones, which share planted matches) against cv2 on the box."""
+    syn = importlib.import_module("3d_reconstruction_b200.synthetic")
+    n_img, k = 257, 16384
+    desc, kpi = syn.make_bank_tensor(n_img, k, seed=1234, device="cuda")
+    bank = pkg.DescriptorBank.from_packed(desc, kpi)
+    pairs = pkg.blocked_order(pkg.exhaustive_pairs(n_img))
+    assert len(pairs) == 32896
+    out = pkg.match_pairs(bank, pairs, cap=4096)
+    out.check_overflow()
+    cnt = out.count.cpu().numpy()
+    assert cnt.sum() == 1126467                      # what bench.py reports as matches_rank0 for this seed
+    sample = np.random.default_rng(3).choice(len(pairs), size=8, replace=False).tolist()
+    sample += [p for p, (a, b) in enumerate(pairs) if b - a == 1][:2]
+    q_all, t_all, d_all = out.query_idx, out.train_idx, out.dist
+    lists = {p: (q_all[p, :cnt[p]].cpu().numpy().astype(np.int64), t_all[p, :cnt[p]].cpu().numpy().astype(np.int64),
+                 d_all[p, :cnt[p]].cpu().numpy()) for p in sample}
+    for p in sample:
+        q, t, _ = lists[p]
+        assert len(set(t.tolist())) == len(t) and np.all(np.diff(q) > 0)
+    _check_sampled_cv2(desc, k, pairs, lists, sample)
 
 
 def test_config4_window_schedule_and_halo_shards(pkg):
@@ -84,8 +121,10 @@ def test_config4_window_schedule_and_halo_shards(pkg):
             assert np.array_equal(sq[i, :c], q_all[p0 + i, :c]) and np.array_equal(st_[i, :c], t_all[p0 + i, :c])
             assert np.array_equal(sd[i, :c].view(np.uint32), d_all[p0 + i, :c].view(np.uint32))
         del sbank, so
-    lists = {p: (q_all[p, :cnt[p]].astype(np.int64), t_all[p, :cnt[p]].astype(np.int64), d_all[p, :cnt[p]]) for p in (0, 31337)}
+    sample = [0, 31337] + np.random.default_rng(4).choice(len(pairs), size=6, replace=False).tolist()
+    lists = {p: (q_all[p, :cnt[p]].astype(np.int64), t_all[p, :cnt[p]].astype(np.int64), d_all[p, :cnt[p]]) for p in sample}
     _check_sampled(desc, k, pairs, lists, [0, 31337])
+    _check_sampled_cv2(desc, k, pairs, lists, sample)
 
 
 def test_config1_native_size_ragged(pkg):
