@@ -33,6 +33,7 @@ SYMBOLS = (
     "b200m_assign_pairs_bf16",
     "b200m_vq_f32",
     "b200m_compact_matches",
+    "b200m_match_stats_read",
     "b200m_profile_read",
     "b200m_profile_detail",
     "b200m_set_option",
@@ -103,6 +104,8 @@ def lib() -> C.CDLL:
     L.b200m_compact_matches.argtypes = [vp, vp, vp, vp, vp, i64, i64, vp, vp, vp, vp]
     L.b200m_profile_read.restype = C.c_int
     L.b200m_profile_read.argtypes = [C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(i64), C.POINTER(i64)]
+    L.b200m_match_stats_read.restype = C.c_int
+    L.b200m_match_stats_read.argtypes = [vp, C.POINTER(i64), C.c_int, vp]
     L.b200m_profile_detail.restype = C.c_int
     L.b200m_profile_detail.argtypes = [C.POINTER(C.c_double), C.c_int]
     L.b200m_set_option.restype = C.c_int
@@ -126,6 +129,18 @@ def set_option(name: str, value: int) -> None:
 
 def get_option(name: str) -> int:
     return int(lib().b200m_get_option(name.encode()))
+
+
+STAT_FIELDS = ("rows", "rows_chunk_evaluated", "rows_fallback", "candidates", "rows_ratio_verify", "matches")
+
+
+def match_stats(workspace) -> dict:
+    """Counters of the last match_pairs call that used `workspace` (a torch uint8 CUDA tensor); blocks."""
+    import torch
+    out = (C.c_int64 * 6)()
+    with torch.cuda.device(workspace.device):
+        check(lib().b200m_match_stats_read(workspace.data_ptr(), out, 6, torch.cuda.current_stream().cuda_stream))
+    return dict(zip(STAT_FIELDS, (int(x) for x in out)))
 
 
 def profile_read():

@@ -21,7 +21,7 @@ import torch
 
 from . import _lib
 from .bank import TILE_T, FloatBank, round_up
-from .matcher import PairMatches, _pairs_tensor
+from .matcher import PairMatches, _check_out, _pairs_tensor
 
 
 def assign_pairs(bank: FloatBank, matchability: torch.Tensor, pairs, filter_threshold: float | None = 0.1,
@@ -35,7 +35,7 @@ def assign_pairs(bank: FloatBank, matchability: torch.Tensor, pairs, filter_thre
     z = matchability
     if not z.is_cuda or z.dtype != torch.float32 or tuple(z.shape) != (bank.n_img, bank.k_stride) or not z.is_contiguous():
         raise ValueError("matchability must be a contiguous float32 CUDA tensor [n_img, k_stride]")
-    pairs_t = _pairs_tensor(pairs, dev)
+    pairs_t = _pairs_tensor(pairs, dev, bank.n_img)
     P = int(pairs_t.shape[0])
     if cap is None:
         cap = bank.k_stride
@@ -44,6 +44,8 @@ def assign_pairs(bank: FloatBank, matchability: torch.Tensor, pairs, filter_thre
                           torch.empty((P, cap), dtype=torch.int32, device=dev),
                           torch.empty((P, cap), dtype=torch.float32, device=dev),
                           torch.zeros((P,), dtype=torch.int32, device=dev), int(cap))
+    else:
+        _check_out(out, P)
     if P == 0:
         return out
     L = _lib.lib()

@@ -62,9 +62,12 @@ class DescriptorBank:
             raise ValueError("desc must be contiguous uint8 [n_img, k_stride, 128]")
         if desc.shape[1] % TILE_T != 0:
             raise ValueError("k_stride must be a multiple of 256")
-        k_per_image = k_per_image.to(device=desc.device, dtype=torch.int32).contiguous()
         if k_per_image.numel() != desc.shape[0]:
             raise ValueError("k_per_image must have one entry per image")
+        if not k_per_image.is_cuda and k_per_image.numel() and \
+                (int(k_per_image.min()) < 0 or int(k_per_image.max()) > desc.shape[1]):
+            raise ValueError("k_per_image entries must lie in [0, k_stride]")   # device-side counts are clamped by the kernels
+        k_per_image = k_per_image.to(device=desc.device, dtype=torch.int32).contiguous()
         n_tab = int(_lib.lib().b200m_norm_table_elems(desc.shape[0], desc.shape[1]))
         sqnorm = torch.empty((n_tab,), dtype=torch.int32, device=desc.device)   # norms + per-32-row minima
         with torch.cuda.device(desc.device):
@@ -182,9 +185,12 @@ class FloatBank:
         if desc.shape[1] % TILE_T != 0:
             raise ValueError("k_stride must be a multiple of 256")
         self.desc = desc
-        self.k_per_image = k_per_image.to(device=desc.device, dtype=torch.int32).contiguous()
-        if self.k_per_image.numel() != desc.shape[0]:
+        if k_per_image.numel() != desc.shape[0]:
             raise ValueError("k_per_image must have one entry per image")
+        if not k_per_image.is_cuda and k_per_image.numel() and \
+                (int(k_per_image.min()) < 0 or int(k_per_image.max()) > desc.shape[1]):
+            raise ValueError("k_per_image entries must lie in [0, k_stride]")
+        self.k_per_image = k_per_image.to(device=desc.device, dtype=torch.int32).contiguous()
 
     @classmethod
     def from_arrays(cls, arrays: Sequence, device="cuda", k_stride: int | None = None) -> "FloatBank":

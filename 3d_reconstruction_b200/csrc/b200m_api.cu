@@ -7,14 +7,20 @@
 #include <string.h>
 
 #include <algorithm>
+#include <atomic>
+#include <mutex>
+#include <set>
+#include <utility>
 #include <vector>
 
 #include "../../include/b200m.h"
 #include "match_finalize.cuh"
 #include "match_sweep.cuh"
-#include "match_sweep2.cuh"
 #include "match_chunk.cuh"
-#include "match_chunk2.cuh"
+#ifdef B200M_EXPERIMENTAL   // cta_group::2 variants, measured 19-39 % slower: not in the shipped library
+#include "experimental/match_sweep2.cuh"
+#include "experimental/match_chunk2.cuh"
+#endif
 #include "match_refine.cuh"
 #include "match_sort.cuh"
 #include "match_float.cuh"
@@ -25,35 +31,45 @@ namespace {
 
 thread_local char g_err[512] = "";
 
+// Process-global tuning knobs; every field is an atomic so that a set_option from one host thread and a
+// launch from another never race (each entry point reads a knob once per call).
 struct Options {
-  int64_t epilogue = 1;
-  int64_t grid = 0;
-  int64_t batch = 0;
-  // chunk sweep (pipeline 2): 5 = N256 MMAs / two accumulators (default), 6 = CTA-pair kernel (slower, kept for
-  // comparison), otherwise N128 MMAs / four accumulators;
-  // exact sweeps (pipelines 0 / 1, fallback, verify): 4 = CTA-pair kernel (cta_group::2), otherwise single-CTA
-  int64_t kernel = 5;
+  std::atomic<int64_t> epilogue{1};
+  std::atomic<int64_t> grid{0};
+  std::atomic<int64_t> batch{0};
+  // chunk sweep (pipeline 2): 5 = N256 MMAs / two accumulators (default), otherwise N128 MMAs / four accumulators.
+  // (-DB200M_EXPERIMENTAL builds add the slower cta_group::2 variants: 6 = CTA-pair chunk sweep, 4 = CTA-pair exact sweeps.)
+  std::atomic<int64_t> kernel{5};
   // 2 = chunk sweep on the norm-sorted bank + refine + exact fallback (default, needs the sorted bank),
   // 1 = top-1 sweep + ratio/mutual verify sweeps, 0 = top-2 sweep + mutual verify
-  int64_t pipeline = 2;
-  int64_t chunk = 64;     // columns per chunk of the chunk sweep (64 needs kernel 5, else 32 is used)
+  std::atomic<int64_t> pipeline{2};
+  std::atomic<int64_t> chunk{64};     // columns per chunk of the chunk sweep (64 needs kernel 5, else 32 is used)
 } g_opt;
 
 // Optional per-launch timing of the sweeps with CUDA events on the launching stream ("profile" option).
+// The event pool and the lists are guarded by `mu` (two host threads may launch concurrently); the pool is
+// capped: once kMaxEvents are in flight without a b200m_profile_read, further launches are counted but not timed.
 struct Profile {
-  bool on = false;
-  int64_t launches = 0;                                    // every kernel this library launched
+  std::atomic<bool> on{false};
+  std::atomic<int64_t> launches{0};                        // every kernel this library launched
+  std::mutex mu;
   std::vector<cudaEvent_t> pool;
   std::vector<std::pair<int, int>> first, verify;          // (start, stop) indices into pool
   std::vector<std::pair<int, int>> fallback, refine, select, emit;
   size_t used = 0;
-  int take() {
-    if (used == pool.size()) {
+  int64_t dropped = 0;                                     // launches not timed because the pool was full
+  static constexpr size_t kMaxEvents = size_t(1) << 16;
+  // a (start, stop) pair of events, or false when the pool is exhausted; call with mu held
+  bool take2(int* e0, int* e1) {
+    if (used + 2 > kMaxEvents) { ++dropped; return false; }
+    while (pool.size() < used + 2) {
       cudaEvent_t e;
-      cudaEventCreate(&e);
+      if (cudaEventCreate(&e) != cudaSuccess) { cudaGetLastError(); ++dropped; return false; }
       pool.push_back(e);
     }
-    return static_cast<int>(used++);
+    *e0 = static_cast<int>(used++);
+    *e1 = static_cast<int>(used++);
+    return true;
   }
 } g_prof;
 
@@ -61,22 +77,39 @@ struct Profile {
 struct ProfScope {
   std::vector<std::pair<int, int>>* list;
   cudaStream_t st;
-  int e0 = -1;
+  int e0 = -1, e1 = -1;
   ProfScope(std::vector<std::pair<int, int>>* l, cudaStream_t s) : list(l), st(s) {
-    if (g_prof.on && list) {
-      e0 = g_prof.take();
-      cudaEventRecord(g_prof.pool[e0], st);
+    if (g_prof.on.load(std::memory_order_relaxed) && list) {
+      std::lock_guard<std::mutex> lk(g_prof.mu);
+      if (g_prof.take2(&e0, &e1)) cudaEventRecord(g_prof.pool[e0], st);
     }
   }
   ~ProfScope() {
-    ++g_prof.launches;
+    g_prof.launches.fetch_add(1, std::memory_order_relaxed);
     if (e0 >= 0) {
-      const int e1 = g_prof.take();
+      std::lock_guard<std::mutex> lk(g_prof.mu);
       cudaEventRecord(g_prof.pool[e1], st);
       list->push_back({e0, e1});
     }
   }
 };
+
+// cudaFuncAttributeMaxDynamicSharedMemorySize is per device (and context): remember which (kernel, device)
+// pairs have been opted in, so that a process driving several GPUs from one thread works on every one of them.
+template <typename F>
+cudaError_t ensure_smem_attr(F* func, size_t bytes) {
+  static std::mutex mu;
+  static std::set<std::pair<const void*, int>> done;
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  const std::pair<const void*, int> key(reinterpret_cast<const void*>(func), dev);
+  std::lock_guard<std::mutex> lk(mu);
+  if (done.count(key)) return cudaSuccess;
+  e = cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(bytes));
+  if (e == cudaSuccess) done.insert(key);
+  return e;
+}
 
 int fail(int code, const char* fmt, const char* detail = "") {
   snprintf(g_err, sizeof(g_err), fmt, detail);
@@ -176,54 +209,32 @@ constexpr size_t kSweepSmemBytes = sizeof(b200m::SweepSmem) + 1024;
 template <int kKind>
 int launch_sweep(const CUtensorMap& tmap_a, const CUtensorMap& tmap_a2, const CUtensorMap& tmap_b,
                  const b200m::SweepParams& sp, int grid, cudaStream_t st) {
-  static thread_local bool attr_set = false;
-  if (!attr_set) {
-    CUDA_TRY(cudaFuncSetAttribute(b200m::sweep_kernel<kKind>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  static_cast<int>(kSweepSmemBytes)));
-    attr_set = true;
+  CUDA_TRY(ensure_smem_attr(b200m::sweep_kernel<kKind>, kSweepSmemBytes));
+  {
+    ProfScope ps(kKind == b200m::kVerify ? &g_prof.verify : kKind == b200m::kTop1G ? &g_prof.fallback : &g_prof.first, st);
+    b200m::sweep_kernel<kKind><<<grid, b200m::kThreads, kSweepSmemBytes, st>>>(tmap_a, tmap_a2, tmap_b, sp);
   }
-  int e0 = -1, e1 = -1;
-  if (g_prof.on) {
-    e0 = g_prof.take();
-    e1 = g_prof.take();
-    cudaEventRecord(g_prof.pool[e0], st);
-  }
-  b200m::sweep_kernel<kKind><<<grid, b200m::kThreads, kSweepSmemBytes, st>>>(tmap_a, tmap_a2, tmap_b, sp);
   CUDA_TRY(cudaGetLastError());
-  ++g_prof.launches;
-  if (g_prof.on) {
-    cudaEventRecord(g_prof.pool[e1], st);
-    (kKind == b200m::kVerify ? g_prof.verify : kKind == b200m::kTop1G ? g_prof.fallback : g_prof.first).push_back({e0, e1});
-  }
   return B200M_OK;
 }
 
 constexpr size_t kChunkSmemBytes = sizeof(b200m::ChunkSmem) + 1024;
-
 constexpr size_t kChunk256SmemBytes = sizeof(b200m::Chunk256Smem) + 1024;
-constexpr size_t kChunkPairSmemBytes = sizeof(b200m::pair::ChunkPairSmem) + 1024;
 
-int launch_chunk_sweep(const CUtensorMap& tmap, const b200m::ChunkParams& cp, int grid, cudaStream_t st) {
-  static thread_local bool attr_set = false;
-  if (!attr_set) {
-    CUDA_TRY(cudaFuncSetAttribute(b200m::chunk_sweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  static_cast<int>(kChunkSmemBytes)));
-    CUDA_TRY(cudaFuncSetAttribute(b200m::chunk_sweep256_kernel<false, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  static_cast<int>(kChunk256SmemBytes)));
-    CUDA_TRY(cudaFuncSetAttribute(b200m::chunk_sweep256_kernel<false, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  static_cast<int>(kChunk256SmemBytes)));
-    CUDA_TRY(cudaFuncSetAttribute(b200m::chunk_sweep256_kernel<true, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  static_cast<int>(kChunk256SmemBytes)));
-
-    CUDA_TRY(cudaFuncSetAttribute(b200m::pair::chunk_sweep_pair_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  static_cast<int>(kChunkPairSmemBytes)));
-    CUDA_TRY(cudaFuncSetAttribute(b200m::pair::chunk_sweep_pair_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  static_cast<int>(kChunkPairSmemBytes)));
-    attr_set = true;
-  }
+int launch_chunk_sweep(const CUtensorMap& tmap, const b200m::ChunkParams& cp, int grid, int64_t kernel, cudaStream_t st) {
+  CUDA_TRY(ensure_smem_attr(b200m::chunk_sweep_kernel, kChunkSmemBytes));
+  CUDA_TRY(ensure_smem_attr(b200m::chunk_sweep256_kernel<false, 32>, kChunk256SmemBytes));
+  CUDA_TRY(ensure_smem_attr(b200m::chunk_sweep256_kernel<false, 64>, kChunk256SmemBytes));
+  CUDA_TRY(ensure_smem_attr(b200m::chunk_sweep256_kernel<true, 32>, kChunk256SmemBytes));
+#ifdef B200M_EXPERIMENTAL
+  constexpr size_t kChunkPairSmemBytes = sizeof(b200m::pair::ChunkPairSmem) + 1024;
+  CUDA_TRY(ensure_smem_attr(b200m::pair::chunk_sweep_pair_kernel<false>, kChunkPairSmemBytes));
+  CUDA_TRY(ensure_smem_attr(b200m::pair::chunk_sweep_pair_kernel<true>, kChunkPairSmemBytes));
+#endif
   {
     ProfScope ps(&g_prof.first, st);
-    if (g_opt.kernel == 6) {
+#ifdef B200M_EXPERIMENTAL
+    if (kernel == 6) {
       // whole CTA pairs (the kernel carries __cluster_dims__(2, 1, 1)); work items are blocks of 512 rows
       const int64_t items = static_cast<int64_t>(cp.n_pairs) * ((cp.k_stride + 511) / 512);
       const int pgrid = 2 * static_cast<int>(std::min<int64_t>(std::max<int64_t>(items, 1), std::max(grid / 2, 1)));
@@ -231,11 +242,13 @@ int launch_chunk_sweep(const CUtensorMap& tmap, const b200m::ChunkParams& cp, in
         b200m::pair::chunk_sweep_pair_kernel<true><<<pgrid, b200m::kThreads, kChunkPairSmemBytes, st>>>(tmap, cp);
       else
         b200m::pair::chunk_sweep_pair_kernel<false><<<pgrid, b200m::kThreads, kChunkPairSmemBytes, st>>>(tmap, cp);
-    } else if (g_opt.kernel == 5 && cp.peak)
+    } else
+#endif
+    if (kernel == 5 && cp.peak)
       b200m::chunk_sweep256_kernel<true, 32><<<grid, b200m::kThreads256, kChunk256SmemBytes, st>>>(tmap, cp);
-    else if (g_opt.kernel == 5 && cp.chunk_cols == 64)
+    else if (kernel == 5 && cp.chunk_cols == 64)
       b200m::chunk_sweep256_kernel<false, 64><<<grid, b200m::kThreads256, kChunk256SmemBytes, st>>>(tmap, cp);
-    else if (g_opt.kernel == 5)
+    else if (kernel == 5)
       b200m::chunk_sweep256_kernel<false, 32><<<grid, b200m::kThreads256, kChunk256SmemBytes, st>>>(tmap, cp);
     else
       b200m::chunk_sweep_kernel<<<grid, b200m::kThreads, kChunkSmemBytes, st>>>(tmap, cp);
@@ -244,46 +257,38 @@ int launch_chunk_sweep(const CUtensorMap& tmap, const b200m::ChunkParams& cp, in
   return B200M_OK;
 }
 
+#ifdef B200M_EXPERIMENTAL
 constexpr size_t kPairSmemBytes = sizeof(b200m::pair::PairSmem) + 1024;
 
 template <int kKind>
 int launch_sweep_pair(const CUtensorMap& tmap_a, const CUtensorMap& tmap_a2, const CUtensorMap& tmap_b,
                       const b200m::SweepParams& sp, int grid, cudaStream_t st) {
-  static thread_local bool attr_set = false;
-  if (!attr_set) {
-    CUDA_TRY(cudaFuncSetAttribute(b200m::pair::sweep_pair_kernel<kKind>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  static_cast<int>(kPairSmemBytes)));
-    attr_set = true;
-  }
+  CUDA_TRY(ensure_smem_attr(b200m::pair::sweep_pair_kernel<kKind>, kPairSmemBytes));
   grid = (grid + 1) & ~1;   // whole CTA pairs (the kernel carries __cluster_dims__(2, 1, 1))
-  int e0 = -1, e1 = -1;
-  if (g_prof.on) {
-    e0 = g_prof.take();
-    e1 = g_prof.take();
-    cudaEventRecord(g_prof.pool[e0], st);
+  {
+    ProfScope ps(kKind == b200m::kVerify ? &g_prof.verify : &g_prof.first, st);
+    b200m::pair::sweep_pair_kernel<kKind><<<grid, b200m::pair::kThreads2, kPairSmemBytes, st>>>(tmap_a, tmap_a2, tmap_b, sp);
   }
-  b200m::pair::sweep_pair_kernel<kKind><<<grid, b200m::pair::kThreads2, kPairSmemBytes, st>>>(tmap_a, tmap_a2, tmap_b, sp);
   CUDA_TRY(cudaGetLastError());
-  ++g_prof.launches;
-  if (g_prof.on) {
-    cudaEventRecord(g_prof.pool[e1], st);
-    (kKind == b200m::kVerify ? g_prof.verify : g_prof.first).push_back({e0, e1});
-  }
   return B200M_OK;
 }
+#endif
 
-// dispatch on the "kernel" option
+// dispatch on the "kernel" option (the CTA-pair variant exists in -DB200M_EXPERIMENTAL builds only)
 template <int kKind>
 int launch_any(const CUtensorMap& tmap_a, const CUtensorMap& tmap_a2, const CUtensorMap& tmap_b,
                const b200m::SweepParams& sp, int grid, cudaStream_t st) {
-  return g_opt.kernel == 4 ? launch_sweep_pair<kKind>(tmap_a, tmap_a2, tmap_b, sp, grid, st)
-                           : launch_sweep<kKind>(tmap_a, tmap_a2, tmap_b, sp, grid, st);
+#ifdef B200M_EXPERIMENTAL
+  if (g_opt.kernel == 4) return launch_sweep_pair<kKind>(tmap_a, tmap_a2, tmap_b, sp, grid, st);
+#endif
+  return launch_sweep<kKind>(tmap_a, tmap_a2, tmap_b, sp, grid, st);
 }
 
 constexpr int64_t kDefaultBatchRows = int64_t(1) << 22;   // pairs * k_stride per internal batch
 
 int64_t batch_pairs(int64_t k_stride, int64_t n_pairs) {
-  int64_t b = g_opt.batch > 0 ? g_opt.batch : (kDefaultBatchRows / (k_stride > 0 ? k_stride : 1));
+  const int64_t opt_batch = g_opt.batch;
+  int64_t b = opt_batch > 0 ? opt_batch : (kDefaultBatchRows / (k_stride > 0 ? k_stride : 1));
   if (b < 1) b = 1;
   if (b > n_pairs) b = n_pairs;
   if (b < 1) b = 1;
@@ -292,6 +297,7 @@ int64_t batch_pairs(int64_t k_stride, int64_t n_pairs) {
 
 // Workspace carved per batch of B pairs (R = B * k_stride rows):
 struct Workspace {
+  unsigned long long* stats;  // kStatSlots x kStatFields counters of the call (first block of the workspace)
   int4* rowres;             // R
   int32_t* cand_q;          // R
   int32_t* cand_t;          // R
@@ -318,6 +324,7 @@ size_t carve(Workspace* w, void* base, int64_t B, int64_t k_stride) {
   uintptr_t p0 = (reinterpret_cast<uintptr_t>(base) + 255) & ~uintptr_t(255);
   uintptr_t p = p0;
   auto take = [&](size_t bytes) { uintptr_t r = p; p += (bytes + 255) & ~size_t(255); return r; };
+  uintptr_t s0 = take(sizeof(unsigned long long) * b200m::kStatSlots * b200m::kStatFields);
   uintptr_t a = take(sizeof(int4) * R);
   uintptr_t b = take(4 * R), c = take(4 * R), d = take(4 * R), e = take(4 * R), f = take(4 * R);
   uintptr_t f2 = take(4 * R), f3 = take(4 * R);
@@ -329,6 +336,7 @@ size_t carve(Workspace* w, void* base, int64_t B, int64_t k_stride) {
   uintptr_t i5 = take(4 * (B + 64)), i6 = take(4 * (B + 64));
   uintptr_t i7 = take(sizeof(int32_t) * 2 * (2 * R / 256 + 64));
   if (w) {
+    w->stats = reinterpret_cast<unsigned long long*>(s0);
     w->vitems = reinterpret_cast<int32_t*>(i7);
     w->rowres_o = reinterpret_cast<int4*>(i1);
     w->fb_q = reinterpret_cast<int32_t*>(i2);
@@ -393,7 +401,8 @@ int grid_for(int64_t work, int block) {
 }
 
 int sweep_grid(int64_t items) {
-  int grid = g_opt.grid > 0 ? static_cast<int>(g_opt.grid) : device_info().sms;
+  const int64_t opt_grid = g_opt.grid;
+  int grid = opt_grid > 0 ? static_cast<int>(opt_grid) : device_info().sms;
   if (grid > items) grid = static_cast<int>(items);
   return grid < 1 ? 1 : grid;
 }
@@ -408,6 +417,7 @@ b200m::SweepParams base_params(const int32_t* norm_table, int32_t n_img, const i
   sp.k_stride = k_stride;
   sp.n_pairs = static_cast<int32_t>(nb);
   sp.blocks_per_pair = static_cast<int32_t>(k_stride / b200m::kRows);
+  sp.n_img = n_img;
   sp.rowres = w.rowres;
   sp.cand_count = w.cand_count;
   sp.cand_count_r = w.cand_count;
@@ -442,15 +452,18 @@ int sweep_rows(const CUtensorMap& tmap_bank, const b200m::SweepParams& sp, bool 
   }
 }
 
+// out_count[p] = -1 for pair-list entries that name an image outside the bank (the kernels treat them as empty)
+int mark_invalid_pairs(const int32_t* pairs, int64_t n_pairs, int32_t n_img, int32_t* out_count, cudaStream_t st) {
+  b200m::mark_invalid_pairs_kernel<<<static_cast<unsigned>((n_pairs + 255) / 256), 256, 0, st>>>(pairs, n_pairs, n_img, out_count);
+  CUDA_TRY(cudaGetLastError());
+  g_prof.launches.fetch_add(1);
+  return B200M_OK;
+}
+
 template <int kDim, int kMode = b200m::ip::kIpArgmax>
 int launch_ip_sweep(const CUtensorMap& tmap, const b200m::ip::IpParams& ip, int grid, cudaStream_t st) {
   constexpr size_t smem = sizeof(b200m::ip::IpSmem<kDim>) + 1024;
-  static thread_local bool attr_set = false;
-  if (!attr_set) {
-    CUDA_TRY(cudaFuncSetAttribute(b200m::ip::ip_sweep_kernel<kDim, kMode>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  static_cast<int>(smem)));
-    attr_set = true;
-  }
+  CUDA_TRY((ensure_smem_attr(b200m::ip::ip_sweep_kernel<kDim, kMode>, smem)));
   {
     ProfScope ps(kMode == b200m::ip::kIpLse ? &g_prof.verify : &g_prof.first, st);
     b200m::ip::ip_sweep_kernel<kDim, kMode><<<grid, b200m::kThreads, smem, st>>>(tmap, ip);
@@ -482,7 +495,14 @@ int b200m_set_option(const char* name, int64_t value) {
   if (!strcmp(name, "grid")) { g_opt.grid = value; return B200M_OK; }
   if (!strcmp(name, "batch")) { g_opt.batch = value; return B200M_OK; }
   if (!strcmp(name, "pipeline")) { g_opt.pipeline = value; return B200M_OK; }
-  if (!strcmp(name, "kernel")) { g_opt.kernel = value; return B200M_OK; }
+  if (!strcmp(name, "kernel")) {
+#ifndef B200M_EXPERIMENTAL
+    if (value == 4 || value == 6)
+      return fail(B200M_E_BAD_ARG, "kernel variants 4 / 6 (cta_group::2) exist in -DB200M_EXPERIMENTAL builds only%s");
+#endif
+    g_opt.kernel = value;
+    return B200M_OK;
+  }
   if (!strcmp(name, "chunk")) {
     if (value != 32 && value != 64) return fail(B200M_E_BAD_ARG, "chunk must be 32 or 64%s");
     g_opt.chunk = value;
@@ -525,7 +545,7 @@ int b200m_bank_prepare_u8(uint8_t* bank, int32_t n_img, int64_t k_stride, const 
   b200m::bank_prepare_kernel<<<static_cast<int>(blocks), block, 0, st>>>(bank, n_rows, k_stride, k_per_image,
                                                                          norm_table, B200M_PAD_NORM);
   CUDA_TRY(cudaGetLastError());
-  g_prof.launches += 2;
+  g_prof.launches.fetch_add(2);
   int64_t blocks2 = (n_rows + block - 1) / block;
   if (blocks2 > max_blocks) blocks2 = max_blocks;
   b200m::norm_chunk_min_kernel<<<static_cast<int>(blocks2), block, 0, st>>>(norm_table, n_rows, norm_table + n_rows);
@@ -559,16 +579,16 @@ int b200m_bank_sort_u8(const uint8_t* bank, const int32_t* norm_table, const int
   const unsigned smem_blocks = static_cast<unsigned>(total / b200m::kSortChunk);
   b200m::sort_smem_kernel<true><<<smem_blocks, b200m::kSortThreads, 0, st>>>(keys, n2, key_stride, 0);
   CUDA_TRY(cudaGetLastError());
-  g_prof.launches += 2;
+  g_prof.launches.fetch_add(2);
   for (int64_t size = 2 * b200m::kSortChunk; size <= n2; size <<= 1) {
     for (int64_t stride = size / 2; stride >= b200m::kSortChunk; stride >>= 1) {
       b200m::sort_global_kernel<<<grid_for(total / 2, 256), 256, 0, st>>>(keys, n2, key_stride, n_img, size, stride);
       CUDA_TRY(cudaGetLastError());
-      ++g_prof.launches;
+      g_prof.launches.fetch_add(1);
     }
     b200m::sort_smem_kernel<false><<<smem_blocks, b200m::kSortThreads, 0, st>>>(keys, n2, key_stride, size);
     CUDA_TRY(cudaGetLastError());
-    ++g_prof.launches;
+    g_prof.launches.fetch_add(1);
   }
   b200m::sort_extract_kernel<<<grid_for(R, 256), 256, 0, st>>>(keys, key_stride, k_stride, R, const_cast<int32_t*>(tv.perm),
                                                               const_cast<int32_t*>(tv.inv), const_cast<int32_t*>(tv.snorm));
@@ -580,7 +600,7 @@ int b200m_bank_sort_u8(const uint8_t* bank, const int32_t* norm_table, const int
                                                                       const_cast<int32_t*>(tv.cmin), const_cast<int32_t*>(tv.spread),
                                                                       const_cast<int32_t*>(tv.spread64));
   CUDA_TRY(cudaGetLastError());
-  g_prof.launches += 3;
+  g_prof.launches.fetch_add(3);
   return B200M_OK;
 }
 
@@ -610,10 +630,10 @@ int b200m_knn2_u8(const uint8_t* bank, const int32_t* norm_table, const int32_t*
     rc = sweep_rows(tmap, sp, true, st);
     if (rc) return rc;
     dim3 grid(static_cast<unsigned>((k_stride + 255) / 256), static_cast<unsigned>(nb));
-    b200m::knn2_finalize_kernel<<<grid, 256, 0, st>>>(w.rowres, pairs + 2 * p0, k_per_image, k_stride,
+    b200m::knn2_finalize_kernel<<<grid, 256, 0, st>>>(w.rowres, pairs + 2 * p0, k_per_image, n_img, k_stride,
                                                       out_train_idx + 2 * p0 * k_stride, out_dist + 2 * p0 * k_stride);
     CUDA_TRY(cudaGetLastError());
-    ++g_prof.launches;
+    g_prof.launches.fetch_add(1);
   }
   return B200M_OK;
 }
@@ -643,6 +663,7 @@ int b200m_match_pairs_u8(const uint8_t* bank, const int32_t* norm_table, const u
   rc = make_row_tmap(&tmap_gt, w.gath_t, static_cast<uint64_t>(B) * k_stride);
   if (rc) return rc;
   const int do_mutual = mutual ? 1 : 0;
+  CUDA_TRY(cudaMemsetAsync(w.stats, 0, sizeof(unsigned long long) * b200m::kStatSlots * b200m::kStatFields, st));
 
   // ---------------------------------------------------------------- pipeline 2: chunk sweep on the sorted bank
   if (g_opt.pipeline == 2 && sorted_bank && g_opt.epilogue != 0) {
@@ -650,6 +671,7 @@ int b200m_match_pairs_u8(const uint8_t* bank, const int32_t* norm_table, const u
     if (rc) return rc;
     const SortTable tv = sort_table_view(sort_table, n_img, k_stride);
     const int do_ratio = ratio > 0.0 ? 1 : 0;
+    const int64_t opt_kernel = g_opt.kernel;
     for (int64_t p0 = 0; p0 < n_pairs; p0 += B) {
       const int64_t nb = (n_pairs - p0 < B) ? (n_pairs - p0) : B;
       const int32_t* pb = pairs + 2 * p0;
@@ -660,10 +682,12 @@ int b200m_match_pairs_u8(const uint8_t* bank, const int32_t* norm_table, const u
       cp.k_stride = k_stride;
       cp.n_pairs = static_cast<int32_t>(nb);
       cp.blocks_per_pair = static_cast<int32_t>(k_stride / b200m::kRows);
+      cp.n_img = n_img;
       cp.rowres = w.rowres;
       cp.peak = g_opt.epilogue == 2 ? 1 : 0;
-      cp.chunk_cols = g_opt.kernel == 6 ? 64 : (g_opt.kernel == 5 && g_opt.chunk == 64 && !cp.peak) ? 64 : 32;
-      rc = launch_chunk_sweep(tmap_sbank, cp, g_opt.kernel == 6 ? sweep_grid(1 << 20) : sweep_grid(nb * cp.blocks_per_pair), st);
+      cp.chunk_cols = opt_kernel == 6 ? 64 : (opt_kernel == 5 && g_opt.chunk == 64 && !cp.peak) ? 64 : 32;
+      rc = launch_chunk_sweep(tmap_sbank, cp, opt_kernel == 6 ? sweep_grid(1 << 20) : sweep_grid(nb * cp.blocks_per_pair),
+                              opt_kernel, st);
       if (rc) return rc;
       CUDA_TRY(cudaMemsetAsync(w.fb_count, 0, sizeof(int32_t) * (B + 64), st));   // per-pair counts, the batch total at [B], the verify work-list length at [B + 1]
       b200m::RefineParams rp;
@@ -678,6 +702,7 @@ int b200m_match_pairs_u8(const uint8_t* bank, const int32_t* norm_table, const u
       rp.k_per_image = k_per_image;
       rp.pairs = pb;
       rp.k_stride = k_stride;
+      rp.n_img = n_img;
       rp.rowres_s = w.rowres;
       rp.rowres_o = w.rowres_o;
       rp.fb_count = w.fb_count;
@@ -686,6 +711,7 @@ int b200m_match_pairs_u8(const uint8_t* bank, const int32_t* norm_table, const u
       rp.fb_desc = w.gath_q;
       rp.ratio = ratio;
       rp.inv_ratio_sq = ratio > 0.0 ? 1.0 / (ratio * ratio) : 0.0;
+      rp.stats = w.stats;
       {
         ProfScope ps(&g_prof.refine, st);
         dim3 grid(static_cast<unsigned>((k_stride + b200m::kRefineThreads - 1) / b200m::kRefineThreads), static_cast<unsigned>(nb));
@@ -700,9 +726,9 @@ int b200m_match_pairs_u8(const uint8_t* bank, const int32_t* norm_table, const u
       {
         ProfScope ps(&g_prof.select, st);
         b200m::select2_kernel<1024><<<static_cast<unsigned>(nb), 1024, 0, st>>>(
-            w.rowres_o, pb, k_per_image, k_stride, ratio, bank, norm_table, do_ratio, do_mutual, w.cand_q, w.cand_t,
+            w.rowres_o, pb, k_per_image, n_img, k_stride, ratio, bank, norm_table, do_ratio, do_mutual, w.cand_q, w.cand_t,
             w.cand_d, w.cand_thr_mut, w.cand_rslot, w.cand_count, w.cand_thr_ratio, w.cand_excl, w.cand_count_a,
-            w.gath_q, w.gath_t, w.vitems, w.fb_count + B + 1);
+            w.gath_q, w.gath_t, w.vitems, w.fb_count + B + 1, w.stats);
       }
       CUDA_TRY(cudaGetLastError());
       if (do_ratio || do_mutual) {
@@ -719,11 +745,12 @@ int b200m_match_pairs_u8(const uint8_t* bank, const int32_t* norm_table, const u
         ProfScope ps(&g_prof.emit, st);
         b200m::emit_kernel<1024><<<static_cast<unsigned>(nb), 1024, 0, st>>>(
             w.cand_q, w.cand_t, w.cand_d, w.viol_ratio, w.viol_mut, w.cand_count, w.cand_rslot, k_stride, do_ratio,
-            do_mutual, out_query_idx + p0 * cap, out_train_idx + p0 * cap, out_dist + p0 * cap, out_count + p0, cap);
+            do_mutual, out_query_idx + p0 * cap, out_train_idx + p0 * cap, out_dist + p0 * cap, out_count + p0, cap,
+            w.stats);
       }
       CUDA_TRY(cudaGetLastError());
     }
-    return B200M_OK;
+    return mark_invalid_pairs(pairs, n_pairs, n_img, out_count, st);
   }
 
   // ---------------------------------------------------------------- pipelines 0 / 1 (original bank only)
@@ -740,7 +767,7 @@ int b200m_match_pairs_u8(const uint8_t* bank, const int32_t* norm_table, const u
     {
       ProfScope ps(&g_prof.select, st);
       b200m::select_kernel<1024><<<static_cast<unsigned>(nb), 1024, 0, st>>>(
-          w.rowres, pb, k_per_image, k_stride, ratio, exact2 ? 1 : 0, bank, norm_table, do_ratio, do_mutual, w.cand_q,
+          w.rowres, pb, k_per_image, n_img, k_stride, ratio, exact2 ? 1 : 0, bank, norm_table, do_ratio, do_mutual, w.cand_q,
           w.cand_t, w.cand_d, w.cand_thr_ratio, w.cand_thr_mut, w.cand_count, w.gath_q, w.gath_t);
     }
     CUDA_TRY(cudaGetLastError());
@@ -755,11 +782,11 @@ int b200m_match_pairs_u8(const uint8_t* bank, const int32_t* norm_table, const u
       ProfScope ps(&g_prof.emit, st);
       b200m::emit_kernel<1024><<<static_cast<unsigned>(nb), 1024, 0, st>>>(
           w.cand_q, w.cand_t, w.cand_d, w.viol_ratio, w.viol_mut, w.cand_count, nullptr, k_stride, do_ratio, do_mutual,
-          out_query_idx + p0 * cap, out_train_idx + p0 * cap, out_dist + p0 * cap, out_count + p0, cap);
+          out_query_idx + p0 * cap, out_train_idx + p0 * cap, out_dist + p0 * cap, out_count + p0, cap, w.stats);
     }
     CUDA_TRY(cudaGetLastError());
   }
-  return B200M_OK;
+  return mark_invalid_pairs(pairs, n_pairs, n_img, out_count, st);
 }
 
 size_t b200m_workspace_bytes_bf16(int64_t k_stride, int64_t n_pairs) {
@@ -798,6 +825,7 @@ int b200m_match_pairs_bf16(const void* bank_bf16, const int32_t* k_per_image, in
     ip.n_pairs = static_cast<int32_t>(nb);
     ip.n_dirs = mutual ? 2 : 1;
     ip.blocks_per_image = static_cast<int32_t>(k_stride / b200m::ip::kRowsF);
+    ip.n_img = n_img;
     ip.rowbest = rowbest;
     ip.z = nullptr;
     ip.nb = nullptr;
@@ -807,12 +835,12 @@ int b200m_match_pairs_bf16(const void* bank_bf16, const int32_t* k_per_image, in
     {
       ProfScope ps(&g_prof.emit, st);
       b200m::ip::ip_finalize_kernel<1024><<<static_cast<unsigned>(nb), 1024, 0, st>>>(
-          rowbest, pairs + 2 * p0, k_per_image, k_stride, static_cast<int32_t>(nb), score_threshold, use_threshold,
+          rowbest, pairs + 2 * p0, k_per_image, n_img, k_stride, static_cast<int32_t>(nb), score_threshold, use_threshold,
           mutual ? 1 : 0, 0, out_query_idx + p0 * cap, out_train_idx + p0 * cap, out_score + p0 * cap, out_count + p0, cap);
     }
     CUDA_TRY(cudaGetLastError());
   }
-  return B200M_OK;
+  return mark_invalid_pairs(pairs, n_pairs, n_img, out_count, st);
 }
 
 size_t b200m_workspace_bytes_assign(int64_t k_stride, int64_t n_pairs) {
@@ -853,6 +881,7 @@ int b200m_assign_pairs_bf16(const void* mdesc_bf16, const float* matchability, c
     ip.n_pairs = static_cast<int32_t>(nb);
     ip.n_dirs = 2;
     ip.blocks_per_image = static_cast<int32_t>(k_stride / b200m::ip::kRowsF);
+    ip.n_img = n_img;
     ip.rowbest = rowbest;
     ip.z = matchability;
     ip.nb = nbuf;
@@ -867,12 +896,12 @@ int b200m_assign_pairs_bf16(const void* mdesc_bf16, const float* matchability, c
     {
       ProfScope ps(&g_prof.emit, st);
       b200m::ip::ip_finalize_kernel<1024><<<static_cast<unsigned>(nb), 1024, 0, st>>>(
-          rowbest, pairs + 2 * p0, k_per_image, k_stride, static_cast<int32_t>(nb), filter_threshold, use_threshold, 1,
+          rowbest, pairs + 2 * p0, k_per_image, n_img, k_stride, static_cast<int32_t>(nb), filter_threshold, use_threshold, 1,
           1, out_query_idx + p0 * cap, out_train_idx + p0 * cap, out_score + p0 * cap, out_count + p0, cap);
     }
     CUDA_TRY(cudaGetLastError());
   }
-  return B200M_OK;
+  return mark_invalid_pairs(pairs, n_pairs, n_img, out_count, st);
 }
 
 size_t b200m_workspace_bytes_ransac(int64_t n_pairs, int32_t iters) {
@@ -957,16 +986,12 @@ int b200m_vq_f32(const float* obs, int64_t n_obs, int32_t dim, const double* cod
   b200m::vq_code_sqr_kernel<<<(n_codes + 127) / 128, 128, 0, st>>>(codebook, dim, n_codes, code_sqr_scratch);
   CUDA_TRY(cudaGetLastError());
   const size_t smem = sizeof(double) * b200m::kVqObsPerBlock * dim;
-  static thread_local bool attr_set = false;
-  if (!attr_set) {
-    CUDA_TRY(cudaFuncSetAttribute(b200m::vq_argmin_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536));
-    attr_set = true;
-  }
+  CUDA_TRY(ensure_smem_attr(b200m::vq_argmin_kernel, 65536));
   const int64_t blocks = (n_obs + b200m::kVqObsPerBlock - 1) / b200m::kVqObsPerBlock;
   b200m::vq_argmin_kernel<<<static_cast<unsigned>(blocks), b200m::kVqThreads, smem, st>>>(
       obs, n_obs, dim, codebook, code_sqr_scratch, n_codes, out_code, out_dist);
   CUDA_TRY(cudaGetLastError());
-  g_prof.launches += 2;
+  g_prof.launches.fetch_add(2);
   return B200M_OK;
 }
 
@@ -981,11 +1006,12 @@ int b200m_compact_matches(const int32_t* query_idx, const int32_t* train_idx, co
   b200m::compact_kernel<<<static_cast<unsigned>(n_pairs), 256, 0, static_cast<cudaStream_t>(stream)>>>(
       query_idx, train_idx, dist, count, offsets, cap, flat_query_idx, flat_train_idx, flat_dist);
   CUDA_TRY(cudaGetLastError());
-  ++g_prof.launches;
+  g_prof.launches.fetch_add(1);
   return B200M_OK;
 }
 
 int b200m_profile_read(double* first_sweep_ms, double* verify_sweep_ms, int64_t* first_sweeps, int64_t* launches) {
+  std::lock_guard<std::mutex> lk(g_prof.mu);
   double a = 0.0, b = 0.0;
   for (auto& pr : g_prof.first) {
     float ms = 0.f;
@@ -1002,7 +1028,7 @@ int b200m_profile_read(double* first_sweep_ms, double* verify_sweep_ms, int64_t*
   if (first_sweep_ms) *first_sweep_ms = a;
   if (verify_sweep_ms) *verify_sweep_ms = b;
   if (first_sweeps) *first_sweeps = static_cast<int64_t>(g_prof.first.size());
-  if (launches) *launches = g_prof.launches;
+  if (launches) *launches = g_prof.launches.load();
   g_prof.first.clear();
   g_prof.verify.clear();
   g_prof.fallback.clear();
@@ -1010,12 +1036,30 @@ int b200m_profile_read(double* first_sweep_ms, double* verify_sweep_ms, int64_t*
   g_prof.select.clear();
   g_prof.emit.clear();
   g_prof.used = 0;
+  g_prof.dropped = 0;
   g_prof.launches = 0;
+  return B200M_OK;
+}
+
+int b200m_match_stats_read(const void* workspace, int64_t* out_host, int n, void* stream) {
+  if (!workspace || !out_host || n < 6) return fail(B200M_E_BAD_ARG, "null workspace / out_host must hold 6 int64%s");
+  Workspace w;
+  carve(&w, const_cast<void*>(workspace), 1, B200M_TILE_T);
+  unsigned long long host[b200m::kStatSlots * b200m::kStatFields];
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  CUDA_TRY(cudaMemcpyAsync(host, w.stats, sizeof(host), cudaMemcpyDeviceToHost, st));
+  CUDA_TRY(cudaStreamSynchronize(st));
+  for (int f = 0; f < 6; ++f) {
+    unsigned long long s = 0;
+    for (int i = 0; i < b200m::kStatSlots; ++i) s += host[i * b200m::kStatFields + f];
+    out_host[f] = static_cast<int64_t>(s);
+  }
   return B200M_OK;
 }
 
 int b200m_profile_detail(double* out_ms, int n) {
   if (!out_ms || n < 6) return fail(B200M_E_BAD_ARG, "out_ms must hold 6 doubles%s");
+  std::lock_guard<std::mutex> lk(g_prof.mu);
   std::vector<std::pair<int, int>>* lists[6] = {&g_prof.first, &g_prof.verify, &g_prof.fallback,
                                                 &g_prof.refine, &g_prof.select, &g_prof.emit};
   for (int i = 0; i < 6; ++i) {

@@ -23,7 +23,7 @@
 //   warps 4-19   epilogue: warp (lane quadrant q, slot s = 2 u + j) drains slot s of every tile for
 //                rows 32 q .. 32 q + 31 of M-half u: two chunks per tile, branch-free (match_chunk.cuh)
 #pragma once
-#include "match_chunk.cuh"
+#include "../match_chunk.cuh"
 
 namespace b200m {
 namespace pair {

@@ -15,7 +15,7 @@
 //                64c..64c+63 of every tile; the four quarters of a row share their running bound
 //                through shared memory and meet once per item.
 #pragma once
-#include "match_sweep.cuh"
+#include "../match_sweep.cuh"
 
 namespace b200m {
 namespace pair {

@@ -41,6 +41,7 @@ struct ChunkParams {
   int64_t k_stride;
   int32_t n_pairs;
   int32_t blocks_per_pair;      // k_stride / 256
+  int32_t n_img;                // pair-list entries outside [0, n_img) are skipped (load_pair)
   // out, per (pair, SORTED query row): (L1, g1, L2, 0) -- the smallest chunk bound, its chunk,
   // the second smallest chunk bound (kBig when the train image has a single chunk)
   int4* rowres;
@@ -101,10 +102,8 @@ chunk_sweep_kernel(const __grid_constant__ CUtensorMap tmap, const ChunkParams p
   auto decode = [&](int item, int& pair, int& blk, int& row0, int& col_img, int& n_rows, int& ntiles, int& nm) {
     pair = item / p.blocks_per_pair;
     blk = item - pair * p.blocks_per_pair;
-    const int qi = __ldg(p.pairs + 2 * pair);
-    const int ti = __ldg(p.pairs + 2 * pair + 1);
-    const int kq = __ldg(p.k_per_image + qi);
-    const int kt = __ldg(p.k_per_image + ti);
+    const PairInfo pi = load_pair(p.pairs, p.k_per_image, pair, p.n_img, p.k_stride);
+    const int qi = pi.qi, ti = pi.ti, kq = pi.kq, kt = pi.kt;
     n_rows = min(kq - blk * kRows, kRows);
     col_img = ti;
     row0 = static_cast<int>(qi * p.k_stride + blk * kRows);
@@ -347,10 +346,8 @@ chunk_sweep256_kernel(const __grid_constant__ CUtensorMap tmap, const ChunkParam
   auto decode = [&](int item, int& pair, int& blk, int& row0, int& col_img, int& n_rows, int& ntiles, int& nm) {
     pair = item / p.blocks_per_pair;
     blk = item - pair * p.blocks_per_pair;
-    const int qi = __ldg(p.pairs + 2 * pair);
-    const int ti = __ldg(p.pairs + 2 * pair + 1);
-    const int kq = __ldg(p.k_per_image + qi);
-    const int kt = __ldg(p.k_per_image + ti);
+    const PairInfo pi = load_pair(p.pairs, p.k_per_image, pair, p.n_img, p.k_stride);
+    const int qi = pi.qi, ti = pi.ti, kq = pi.kq, kt = pi.kt;
     n_rows = min(kq - blk * kRows, kRows);
     col_img = ti;
     row0 = static_cast<int>(qi * p.k_stride + blk * kRows);

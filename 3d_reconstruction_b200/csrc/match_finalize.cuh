@@ -4,6 +4,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include "match_common.cuh"
+
 namespace b200m {
 
 // One warp per descriptor row: lane l owns bytes [4l, 4l+4). Padding rows are zeroed and get the
@@ -55,11 +57,11 @@ __device__ __forceinline__ float dist_from_sq(int d2) {
 
 // knnMatch(k=2) layout: out_train_idx / out_dist are [n_pairs_total, k_stride, 2]
 __global__ void knn2_finalize_kernel(const int4* __restrict__ rowres, const int32_t* __restrict__ pairs,
-                                     const int32_t* __restrict__ k_per_image, int64_t k_stride,
+                                     const int32_t* __restrict__ k_per_image, int n_img, int64_t k_stride,
                                      int32_t* __restrict__ out_idx, float* __restrict__ out_dist) {
   const int pair = blockIdx.y;
-  const int kq = k_per_image[pairs[2 * pair]];
-  const int kt = k_per_image[pairs[2 * pair + 1]];
+  const PairInfo pi = load_pair(pairs, k_per_image, pair, n_img, k_stride);
+  const int kq = pi.kq, kt = pi.kt;
   const float inf = __int_as_float(0x7f800000);
   for (int r = blockIdx.x * blockDim.x + threadIdx.x; r < kq; r += gridDim.x * blockDim.x) {
     const int64_t o = static_cast<int64_t>(pair) * k_stride + r;
@@ -121,7 +123,7 @@ __device__ __forceinline__ int ratio_radius_sq(float d1f, double ratio) {
 template <int kBlock>
 __global__ void __launch_bounds__(kBlock)
 select_kernel(const int4* __restrict__ rowres, const int32_t* __restrict__ pairs,
-              const int32_t* __restrict__ k_per_image, int64_t k_stride, double ratio, int exact2,
+              const int32_t* __restrict__ k_per_image, int n_img, int64_t k_stride, double ratio, int exact2,
               const uint8_t* __restrict__ bank, const int32_t* __restrict__ sqnorm, int gather_q, int gather_t,
               int32_t* __restrict__ cand_q, int32_t* __restrict__ cand_t, float* __restrict__ cand_d,
               int32_t* __restrict__ cand_thr_ratio, int32_t* __restrict__ cand_thr_mut,
@@ -129,9 +131,8 @@ select_kernel(const int4* __restrict__ rowres, const int32_t* __restrict__ pairs
   __shared__ int warp_sums[kBlock / 32];
   __shared__ int running;
   const int pair = blockIdx.x;
-  const int qi = pairs[2 * pair], ti = pairs[2 * pair + 1];
-  const int kq = k_per_image[qi];
-  const int kt = k_per_image[ti];
+  const PairInfo pi = load_pair(pairs, k_per_image, pair, n_img, k_stride);
+  const int qi = pi.qi, ti = pi.ti, kq = pi.kq, kt = pi.kt;
   if (threadIdx.x == 0) running = 0;
   __syncthreads();
   const int64_t base = static_cast<int64_t>(pair) * k_stride;
@@ -189,7 +190,8 @@ emit_kernel(const int32_t* __restrict__ cand_q, const int32_t* __restrict__ cand
             const float* __restrict__ cand_d, const int32_t* __restrict__ viol_ratio,
             const int32_t* __restrict__ viol_mut, const int32_t* __restrict__ cand_count,
             const int32_t* __restrict__ cand_rslot, int64_t k_stride, int use_ratio, int use_mutual, int32_t* __restrict__ out_q, int32_t* __restrict__ out_t,
-            float* __restrict__ out_d, int32_t* __restrict__ out_count, int64_t cap) {
+            float* __restrict__ out_d, int32_t* __restrict__ out_count, int64_t cap,
+            unsigned long long* __restrict__ stats = nullptr) {
   __shared__ int warp_sums[kBlock / 32];
   __shared__ int running;
   const int pair = blockIdx.x;
@@ -215,7 +217,10 @@ emit_kernel(const int32_t* __restrict__ cand_q, const int32_t* __restrict__ cand
     }
   }
   __syncthreads();
-  if (threadIdx.x == 0) out_count[pair] = running;
+  if (threadIdx.x == 0) {
+    out_count[pair] = running;
+    stat_add(stats, 5, running);
+  }
 }
 
 // [n_pairs, cap] slots + counts -> flat lists at offsets[pair] (exclusive scan of min(count, cap)).

@@ -66,6 +66,7 @@ struct IpParams {
   int32_t n_pairs;
   int32_t n_dirs;               // 2: both directions (mutual check), 1: rows = query image only
   int32_t blocks_per_image;     // k_stride / 128
+  int32_t n_img;                // pair-list entries outside [0, n_img) are skipped (load_pair)
   // out: [n_dirs][n_pairs][k_stride] (best similarity, best column); direction 0: rows = query image
   float2* rowbest;
   // dual-softmax head only (kIpLse writes, kIpBiasArgmax reads):
@@ -194,11 +195,11 @@ ip_sweep_kernel(const __grid_constant__ CUtensorMap tmap, const IpParams p) {
     blk = item - pd * p.blocks_per_image;
     pair = pd / p.n_dirs;
     dir = pd - pair * p.n_dirs;
-    const int qi = __ldg(p.pairs + 2 * pair), ti = __ldg(p.pairs + 2 * pair + 1);
-    row_img = dir ? ti : qi;
-    col_img = dir ? qi : ti;
-    n_rows = min(__ldg(p.k_per_image + row_img) - blk * kRowsF, kRowsF);
-    n_cols = __ldg(p.k_per_image + col_img);
+    const PairInfo pi = load_pair(p.pairs, p.k_per_image, pair, p.n_img, p.k_stride);
+    row_img = dir ? pi.ti : pi.qi;
+    col_img = dir ? pi.qi : pi.ti;
+    n_rows = min((dir ? pi.kt : pi.kq) - blk * kRowsF, kRowsF);
+    n_cols = dir ? pi.kq : pi.kt;
     return n_rows > 0 && n_cols > 0;
   };
 
@@ -367,13 +368,14 @@ ip_sweep_kernel(const __grid_constant__ CUtensorMap tmap, const IpParams p) {
 template <int kBlock>
 __global__ void __launch_bounds__(kBlock)
 ip_finalize_kernel(const float2* __restrict__ rowbest, const int32_t* __restrict__ pairs,
-                   const int32_t* __restrict__ k_per_image, int64_t k_stride, int32_t n_pairs, float threshold,
+                   const int32_t* __restrict__ k_per_image, int n_img, int64_t k_stride, int32_t n_pairs, float threshold,
                    int use_threshold, int mutual, int exp_scores, int32_t* __restrict__ out_q, int32_t* __restrict__ out_t,
                    float* __restrict__ out_s, int32_t* __restrict__ out_count, int64_t cap) {
   __shared__ int warp_sums[kBlock / 32];
   __shared__ int running;
   const int pair = blockIdx.x;
-  const int kq = k_per_image[pairs[2 * pair]], kt = k_per_image[pairs[2 * pair + 1]];
+  const PairInfo pi = load_pair(pairs, k_per_image, pair, n_img, k_stride);
+  const int kq = pi.kq, kt = pi.kt;
   if (threadIdx.x == 0) running = 0;
   __syncthreads();
   const float2* fwd = rowbest + static_cast<int64_t>(pair) * k_stride;

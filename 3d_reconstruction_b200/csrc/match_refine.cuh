@@ -40,6 +40,7 @@ struct RefineParams {
   const int32_t* k_per_image;
   const int32_t* pairs;
   int64_t k_stride;
+  int32_t n_img;                // pair-list entries outside [0, n_img) are skipped (load_pair)
   const int4* rowres_s;         // chunk sweep output (sorted query rows)
   int4* rowres_o;               // out (original query rows)
   int32_t* fb_count;            // [n_pairs] rows sent to the fallback sweep (zeroed by the caller)
@@ -49,6 +50,7 @@ struct RefineParams {
   double ratio;
   double inv_ratio_sq;          // 1 / ratio^2 (0 when the ratio test is off)
   int32_t chunk_cols;           // 32 or 64: columns per chunk of the sweep that produced rowres_s
+  unsigned long long* stats;    // counters of the call (match_common.cuh), may be NULL
 };
 
 constexpr int kRefineThreads = 256;
@@ -58,8 +60,8 @@ constexpr int kPadScore = 1 << 23;   // bound of an all-padding chunk (B200M_PAD
 __global__ void __launch_bounds__(kRefineThreads)
 refine_kernel(const RefineParams p) {
   const int pair = blockIdx.y;
-  const int qi = p.pairs[2 * pair], ti = p.pairs[2 * pair + 1];
-  const int kq = p.k_per_image[qi], kt = p.k_per_image[ti];
+  const PairInfo pi = load_pair(p.pairs, p.k_per_image, pair, p.n_img, p.k_stride);
+  const int qi = pi.qi, ti = pi.ti, kq = pi.kq, kt = pi.kt;
   const int lane = threadIdx.x & 31;
   const int r_warp0 = (blockIdx.x * kRefineThreads + threadIdx.x) & ~31;
   if (r_warp0 >= kq) return;
@@ -94,6 +96,10 @@ refine_kernel(const RefineParams p) {
   bool fallback = false;
 
   unsigned todo = __ballot_sync(0xffffffffu, need);
+  if (lane == 0) {
+    stat_add(p.stats, 0, static_cast<unsigned>(min(kq - r_warp0, 32)));
+    stat_add(p.stats, 1, __popc(todo));
+  }
   while (todo) {
     const int src = __ffs(todo) - 1;
     todo &= todo - 1;
@@ -155,6 +161,8 @@ refine_kernel(const RefineParams p) {
       }
     }
   }
+  const unsigned fbm = __ballot_sync(0xffffffffu, fallback);
+  if (lane == 0) stat_add(p.stats, 2, __popc(fbm));
   if (r < kq) {
     if (fallback) {
       const int slot = atomicAdd(p.fb_count + pair, 1);
@@ -233,18 +241,17 @@ __device__ __forceinline__ void block_scan2(int x, int y, int& off_x, int& off_y
 template <int kBlock>
 __global__ void __launch_bounds__(kBlock)
 select2_kernel(const int4* __restrict__ rowres_o, const int32_t* __restrict__ pairs,
-               const int32_t* __restrict__ k_per_image, int64_t k_stride, double ratio,
+               const int32_t* __restrict__ k_per_image, int n_img, int64_t k_stride, double ratio,
                const uint8_t* __restrict__ bank, const int32_t* __restrict__ sqnorm, int do_ratio, int gather_t,
                int32_t* __restrict__ cand_q, int32_t* __restrict__ cand_t, float* __restrict__ cand_d,
                int32_t* __restrict__ cand_thr_mut, int32_t* __restrict__ cand_rslot, int32_t* __restrict__ cand_count,
                int32_t* __restrict__ a_thr_ratio, int32_t* __restrict__ a_excl, int32_t* __restrict__ a_count,
                uint8_t* __restrict__ gath_q, uint8_t* __restrict__ gath_t, int32_t* __restrict__ vitems,
-               int32_t* __restrict__ vitem_count) {
+               int32_t* __restrict__ vitem_count, unsigned long long* __restrict__ stats) {
   __shared__ int2 warp_tot[kBlock / 32];
   const int pair = blockIdx.x;
-  const int qi = pairs[2 * pair], ti = pairs[2 * pair + 1];
-  const int kq = k_per_image[qi];
-  const int kt = k_per_image[ti];
+  const PairInfo pi = load_pair(pairs, k_per_image, pair, n_img, k_stride);
+  const int qi = pi.qi, ti = pi.ti, kq = pi.kq, kt = pi.kt;
   const int64_t base = static_cast<int64_t>(pair) * k_stride;
   const int64_t qbase = static_cast<int64_t>(qi) * k_stride;
   const int64_t tbase = static_cast<int64_t>(ti) * k_stride;
@@ -310,6 +317,8 @@ select2_kernel(const int4* __restrict__ rowres_o, const int32_t* __restrict__ pa
   if (threadIdx.x == 0) {
     cand_count[pair] = tot_b;
     a_count[pair] = tot_a;
+    stat_add(stats, 3, tot_b);
+    stat_add(stats, 4, tot_a);
     // verify work list: 256-row blocks of list A (check 0, ratio) and list B (check 1, mutual)
     const int na = do_ratio ? (tot_a + 255) / 256 : 0;
     const int nb = gather_t ? (tot_b + 255) / 256 : 0;

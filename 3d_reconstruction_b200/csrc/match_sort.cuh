@@ -110,7 +110,7 @@ __global__ void sort_chunk_stats_kernel(const int32_t* __restrict__ snorm, const
     const int64_t row0 = c * 32;
     const int64_t img = row0 / k_stride;
     const int pos0 = static_cast<int>(row0 - img * k_stride);
-    const int k = k_per_image[img];
+    const int k = min(k_per_image[img], static_cast<int>(k_stride));
     const int first = snorm[row0];
     cmin[c] = first;
     if (pos0 < k) {

@@ -37,6 +37,7 @@
 //            gathered buffer, results go to the rows' original slots in (d1^2, i1, d2^2 bound, state) form.
 //   kTop2Exact / kPeak  debugging (every element through the insertion) and MMA-only ceiling.
 #pragma once
+#include "match_common.cuh"
 #include "ptx_sm100.cuh"
 
 namespace b200m {
@@ -89,6 +90,7 @@ struct SweepParams {
   int64_t k_stride;
   int32_t n_pairs;
   int32_t blocks_per_pair;      // k_stride / 256
+  int32_t n_img;                // pair-list entries outside [0, n_img) are skipped (load_pair)
   // kTop1 / kTop2 output per (pair, query row): (d1^2, i1, d2^2, i2); for kTop1 d2^2 is an upper
   // bound of the second-nearest squared distance and i2 is unused
   int4* rowres;
@@ -141,10 +143,8 @@ __device__ __forceinline__ ItemInfo decode_item(const SweepParams& p, int item) 
     it.pair = item / p.blocks_per_pair;
     it.blk = item - it.pair * p.blocks_per_pair;
   }
-  const int qi = __ldg(p.pairs + 2 * it.pair);
-  const int ti = __ldg(p.pairs + 2 * it.pair + 1);
-  const int kq = __ldg(p.k_per_image + qi);
-  const int kt = __ldg(p.k_per_image + ti);
+  const PairInfo pi = load_pair(p.pairs, p.k_per_image, it.pair, p.n_img, p.k_stride);
+  const int qi = pi.qi, ti = pi.ti, kq = pi.kq, kt = pi.kt;
   if (kKind == kVerify) {
     const bool on = it.check == 0 ? p.do_ratio != 0 : p.do_mutual != 0;
     const int s = on ? __ldg((it.check == 0 ? p.cand_count_r : p.cand_count) + it.pair) : 0;

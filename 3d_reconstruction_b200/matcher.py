@@ -37,7 +37,11 @@ class PairMatches:
     cap: int
 
     def check_overflow(self) -> None:
-        mx = int(self.count.max().item()) if self.count.numel() else 0
+        if not self.count.numel():
+            return
+        mn, mx = (int(x) for x in torch.aminmax(self.count))
+        if mn < 0:
+            raise ValueError("the pair list names an image outside the bank (out_count = -1 for that pair)")
         if mx > self.cap:
             raise OverflowError(f"a pair produced {mx} matches but cap is {self.cap}; matches are never truncated silently")
 
@@ -87,14 +91,32 @@ class FlatMatches:
         return self.query_idx[a:b], self.train_idx[a:b], self.dist[a:b]
 
 
-def _pairs_tensor(pairs, device) -> torch.Tensor:
+def _pairs_tensor(pairs, device, n_img: int | None = None) -> torch.Tensor:
+    """int32 [P,2] on `device`. Host-side lists are range-checked here (free); a pair list that already lives on
+    the device is checked by the kernels themselves: an entry outside [0, n_img) is treated as a pair of empty
+    images and reported through out_count = -1 (PairMatches.check_overflow raises)."""
     if isinstance(pairs, torch.Tensor):
+        if pairs.dim() != 2 or pairs.shape[1] != 2:
+            raise ValueError("pairs must be [P,2]")
+        if not pairs.is_cuda and n_img is not None and pairs.numel() and \
+                (int(pairs.min()) < 0 or int(pairs.max()) >= n_img):
+            raise ValueError(f"pairs must index images in [0, {n_img})")
         t = pairs.to(device=device, dtype=torch.int32)
     else:
-        t = torch.as_tensor(np.asarray(pairs, dtype=np.int32).reshape(-1, 2)).to(device)
-    if t.dim() != 2 or t.shape[1] != 2:
-        raise ValueError("pairs must be [P,2]")
+        a = np.asarray(pairs, dtype=np.int64).reshape(-1, 2)
+        if n_img is not None and a.size and (a.min() < 0 or a.max() >= n_img):
+            raise ValueError(f"pairs must index images in [0, {n_img})")
+        t = torch.as_tensor(a.astype(np.int32)).to(device)
     return t.contiguous()
+
+
+def _check_out(out: "PairMatches", n_pairs: int) -> None:
+    for name in ("query_idx", "train_idx", "dist"):
+        t = getattr(out, name)
+        if tuple(t.shape) != (n_pairs, out.cap) or not t.is_contiguous():
+            raise ValueError(f"out.{name} must be a contiguous [{n_pairs}, {out.cap}] tensor, got {tuple(t.shape)}")
+    if tuple(out.count.shape) != (n_pairs,):
+        raise ValueError(f"out.count must be [{n_pairs}], got {tuple(out.count.shape)}")
 
 
 def _workspace(bank: DescriptorBank, n_pairs: int) -> torch.Tensor:
@@ -105,7 +127,7 @@ def _workspace(bank: DescriptorBank, n_pairs: int) -> torch.Tensor:
 def match_pairs(bank: DescriptorBank, pairs, ratio: float = 0.75, mutual: bool = True, cap: int | None = None,
                 out: PairMatches | None = None, workspace: torch.Tensor | None = None) -> PairMatches:
     """Full rule for every (query_img, train_img) pair; asynchronous on the current stream."""
-    pairs_t = _pairs_tensor(pairs, bank.device)
+    pairs_t = _pairs_tensor(pairs, bank.device, bank.n_img)
     P = int(pairs_t.shape[0])
     if cap is None:
         cap = bank.k_stride
@@ -115,6 +137,8 @@ def match_pairs(bank: DescriptorBank, pairs, ratio: float = 0.75, mutual: bool =
                           torch.empty((P, cap), dtype=torch.int32, device=dev),
                           torch.empty((P, cap), dtype=torch.float32, device=dev),
                           torch.zeros((P,), dtype=torch.int32, device=dev), int(cap))
+    else:
+        _check_out(out, P)
     if P == 0:
         return out
     ws = workspace if workspace is not None else _workspace(bank, P)
@@ -135,7 +159,7 @@ def match_pairs_float(bank: FloatBank, pairs, score_threshold: float | None = No
                       workspace: torch.Tensor | None = None) -> PairMatches:
     """Float path: mutual arg-max of the inner product for every (query_img, train_img) pair
     (lightglue.py:223 + :235-254 in raw-similarity form). `dist` of the result holds the similarity."""
-    pairs_t = _pairs_tensor(pairs, bank.device)
+    pairs_t = _pairs_tensor(pairs, bank.device, bank.n_img)
     P = int(pairs_t.shape[0])
     if cap is None:
         cap = bank.k_stride
@@ -145,6 +169,8 @@ def match_pairs_float(bank: FloatBank, pairs, score_threshold: float | None = No
                           torch.empty((P, cap), dtype=torch.int32, device=dev),
                           torch.empty((P, cap), dtype=torch.float32, device=dev),
                           torch.zeros((P,), dtype=torch.int32, device=dev), int(cap))
+    else:
+        _check_out(out, P)
     if P == 0:
         return out
     L = _lib.lib()
@@ -170,7 +196,7 @@ def match_float(desc_q, desc_t, score_threshold: float | None = None, mutual: bo
 
 def knn2_pairs(bank: DescriptorBank, pairs, workspace: torch.Tensor | None = None):
     """knnMatch(k=2) for every pair -> (train_idx int32 [P,k_stride,2], dist float32 [P,k_stride,2])."""
-    pairs_t = _pairs_tensor(pairs, bank.device)
+    pairs_t = _pairs_tensor(pairs, bank.device, bank.n_img)
     P = int(pairs_t.shape[0])
     idx = torch.full((P, bank.k_stride, 2), -1, dtype=torch.int32, device=bank.device)
     dist = torch.full((P, bank.k_stride, 2), float("inf"), dtype=torch.float32, device=bank.device)

@@ -37,7 +37,7 @@
 extern "C" {
 #endif
 
-#define B200M_VERSION 100          /* 0.1.0 */
+#define B200M_VERSION 110          /* 0.1.1 */
 #define B200M_DESC_DIM 128         /* SIFT / DISK descriptor length handled by the u8 path */
 #define B200M_TILE_Q 128           /* query rows per UMMA M-tile (two per work item) */
 #define B200M_TILE_T 256           /* train rows per tile (UMMA N) */
@@ -107,7 +107,9 @@ int b200m_knn2_u8(const uint8_t* bank, const int32_t* norm_table, const int32_t*
  * neighbour and is dropped by the ratio test (cv2: the `for m, n in knn` unpack needs two).
  *   out_query_idx / out_train_idx / out_dist   [n_pairs, cap], ascending query index
  *   out_count  int32 [n_pairs]: matches FOUND; if > cap only the first cap were stored and the
- *              caller must treat the pair as overflowed (never silently truncated).
+ *              caller must treat the pair as overflowed (never silently truncated). -1: the pair-list
+ *              entry names an image outside [0, n_img) (such entries are skipped, never dereferenced;
+ *              k_per_image entries are clamped to [0, k_stride] by every kernel).
  *   sorted_bank / sort_table: outputs of b200m_bank_sort_u8, or both NULL (then the slower
  *              pipeline 1 runs on the original bank alone). Results are identical either way. */
 int b200m_match_pairs_u8(const uint8_t* bank, const int32_t* norm_table,
@@ -194,9 +196,9 @@ int b200m_five_point_f64(const double* x0, const double* x1, double* out_E, int3
  *   "pipeline"  2 = chunk sweep on the norm-sorted bank + exact refine / fallback / verify (default),
  *               1 = top-1 sweep + lazy ratio / mutual verify sweeps over the candidates,
  *               0 = exact top-2 sweep + lazy mutual verify sweep
- *   "kernel"    5 = chunk sweep with N256 MMAs / two accumulators (default), 3 = N128 / four accumulators,
- *               6 = CTA-pair chunk sweep (cta_group::2, four N128 accumulators; slower, kept for comparison);
- *               exact sweeps: 4 = CTA-pair kernel (cta_group::2), otherwise single-CTA
+ *   "kernel"    5 = chunk sweep with N256 MMAs / two accumulators (default), 3 = N128 / four accumulators
+ *               (4 / 6, the slower cta_group::2 variants of csrc/experimental/, are refused unless the library
+ *               was built with -DB200M_EXPERIMENTAL)
  *   "chunk"     columns per chunk of the chunk sweep: 64 (default, kernel 5 only) or 32
  *   "grid"      number of persistent CTAs, 0 = one per SM (default)
  *   "batch"     pairs per internal batch, 0 = default
@@ -210,6 +212,12 @@ int64_t b200m_get_option(const char* name);
 int b200m_compact_matches(const int32_t* query_idx, const int32_t* train_idx, const float* dist,
                           const int32_t* count, const int64_t* offsets, int64_t n_pairs, int64_t cap,
                           int32_t* flat_query_idx, int32_t* flat_train_idx, float* flat_dist, void* stream);
+
+/* Counters of the last b200m_match_pairs_u8 call that used `workspace` (blocks until `stream` has drained):
+ * out_host[0..5] = query rows seen by the refine step | rows whose winning chunk was evaluated exactly | rows sent
+ * to the exact fallback sweep | candidates surviving the Lowe test | rows whose Lowe test needed the verify sweep |
+ * matches emitted. Throughput of the default pipeline depends on these fractions. */
+int b200m_match_stats_read(const void* workspace, int64_t* out_host, int n, void* stream);
 
 /* With option "profile" = 1 every sweep launch is bracketed by CUDA events on its stream.
  * Reads (and resets) the accumulated device time of the first sweeps and of the verify sweeps,

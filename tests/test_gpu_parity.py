@@ -21,14 +21,14 @@ DEFAULT_PIPELINE = 2
 DEFAULT_CHUNK = 64
 
 
-@pytest.fixture(scope="module", params=[(1, 2, 3), (1, 2, 5, 32), (1, 2, 5, 64), (1, 2, 6), (1, 1, 4), (1, 0, 4), (0, 0, 4), (1, 1, 3), (1, 0, 3), (0, 0, 3)],
-                ids=["chunk_refine", "chunk256x32_refine", "chunk256x64_refine", "chunkpair_refine", "pair_top1_verify", "pair_top2_reject", "pair_top2_exact", "top1_verify", "top2_reject",
-                     "top2_exact"])
+@pytest.fixture(scope="module", params=[(1, 2, 3), (1, 2, 5, 32), (1, 2, 5, 64), (1, 1, 3), (1, 0, 3), (0, 0, 3)],
+                ids=["chunk_refine", "chunk256x32_refine", "chunk256x64_refine", "top1_verify", "top2_reject", "top2_exact"])
 def epi(pkg, request):
-    """(epilogue, pipeline, kernel): the default chunk sweep on the norm-sorted bank + refine + exact
-    fallback; the top-1 sweep + verify sweeps, the top-2 threshold-reject sweep with only the mutual
-    verify, and the debug epilogue that sends every element through the insertion, each on the CTA-pair
-    kernel (cta_group::2) and on the single-CTA kernel."""
+    """(epilogue, pipeline, kernel[, chunk]): the shipped variants -- the default chunk sweep on the norm-sorted
+    bank + refine + exact fallback (N128 and N256 MMAs, 32- and 64-column chunks); the top-1 sweep + verify
+    sweeps; the top-2 threshold-reject sweep with only the mutual verify; and the debug epilogue that sends
+    every element through the insertion. (The cta_group::2 variants live in csrc/experimental/ and are only
+    compiled with -DB200M_EXPERIMENTAL.)"""
     pkg.set_option("epilogue", request.param[0])
     pkg.set_option("pipeline", request.param[1])
     pkg.set_option("kernel", request.param[2])

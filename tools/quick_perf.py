@@ -12,7 +12,7 @@ pkg = importlib.import_module("3d_reconstruction_b200")
 syn = importlib.import_module("3d_reconstruction_b200.synthetic")
 
 
-def run(n_img, k, modes=((1, 2, 5, 64), (1, 2, 6, 64), (2, 2, 5, 32)), reps=3, max_pairs=None, grid=0):
+def run(n_img, k, modes=((1, 2, 5, 64), (1, 2, 5, 32), (2, 2, 5, 32)), reps=3, max_pairs=None, grid=0):
     desc, kpi = syn.make_bank_tensor(n_img, k, seed=1234, device="cuda")
     bank = pkg.DescriptorBank.from_packed(desc, kpi)
     pairs = pkg.blocked_order(pkg.exhaustive_pairs(n_img))
