@@ -6,7 +6,7 @@ The compute path is hand-written sm_100a CUDA behind the C-ABI in include/b200m.
 """
 from ._lib import B200MError, LIB_PATH, SYMBOLS, get_option, match_stats, profile_read, set_option  # noqa: F401
 from .bank import DescriptorBank, FloatBank, to_u8_descriptors  # noqa: F401
-from .matcher import (B200Matcher, FlatMatches, MatchConfig, PairMatches, knn2_pairs, knn_match,  # noqa: F401
+from .matcher import (B200Matcher, FlatMatches, MatchConfig, PairMatches, digest_matches, knn2_pairs, knn_match,  # noqa: F401
                       match, match_float, match_pairs, match_pairs_float, match_pairs_host)
 from .assignment import AssignmentHead, assign_pairs  # noqa: F401
 from .geometry import PoseBatch, essential_ransac  # noqa: F401

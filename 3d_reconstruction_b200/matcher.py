@@ -90,6 +90,50 @@ class FlatMatches:
         a, b = int(self.offsets[p]), int(self.offsets[p + 1])
         return self.query_idx[a:b], self.train_idx[a:b], self.dist[a:b]
 
+    def digest(self, pair_ids=None):
+        """-> (per-pair int64 [P], total as an unsigned 64-bit Python int): an order-independent 64-bit digest of
+        every match record (pair id, query row, train row, float32 distance bits). `pair_ids` are the GLOBAL
+        indices of this list's pairs (default 0..P-1), so the per-pair values of a rank's slice are the values a
+        single process computes for the same pairs and the totals of all ranks simply add (mod 2^64): the
+        N-GPU == 1-GPU check of bench.py and tests/test_gpu_multirank.py (matching.py:174,188-189: one ordered
+        row per pair, whoever computed it)."""
+        return digest_matches(self.query_idx, self.train_idx, self.dist, self.offsets, pair_ids)
+
+
+def _i64(c: int) -> int:
+    return c - (1 << 64) if c >= (1 << 63) else c
+
+
+_DIGEST_K = tuple(_i64(c) for c in (0x9E3779B97F4A7C15, 0xC2B2AE3D27D4EB4F, 0x165667B19E3779F9, 0x27D4EB2F165667C5,
+                                    0xBF58476D1CE4E5B9, 0x94D049BB133111EB))
+
+
+def digest_matches(query_idx: torch.Tensor, train_idx: torch.Tensor, dist: torch.Tensor, offsets: torch.Tensor,
+                   pair_ids=None):
+    """See FlatMatches.digest. Pure integer tensor arithmetic (wrapping int64), identical on CPU and CUDA tensors
+    and restated in numpy by tests/test_digest_cpu.py."""
+    dev = offsets.device
+    P = int(offsets.numel()) - 1
+    counts = offsets[1:] - offsets[:-1]
+    if pair_ids is None:
+        pair_ids = torch.arange(P, dtype=torch.int64, device=dev)
+    else:
+        pair_ids = torch.as_tensor(pair_ids).to(device=dev, dtype=torch.int64)
+        if pair_ids.numel() != P:
+            raise ValueError("pair_ids must name every pair of the list")
+    slot = torch.repeat_interleave(torch.arange(P, dtype=torch.int64, device=dev), counts)
+    k1, k2, k3, k4, k5, k6 = _DIGEST_K
+    x = (pair_ids[slot] * k1 + query_idx.to(torch.int64) * k2 + train_idx.to(torch.int64) * k3 +
+         dist.contiguous().view(torch.int32).to(torch.int64) * k4)
+    x = (x ^ (x >> 30)) * k5            # splitmix64 finaliser with arithmetic shifts (same in numpy / torch)
+    x = (x ^ (x >> 27)) * k6
+    x = x ^ (x >> 31)
+    per_pair = torch.zeros((P,), dtype=torch.int64, device=dev)
+    if x.numel():
+        per_pair.index_add_(0, slot, x)
+    total = int(per_pair.sum().item()) & ((1 << 64) - 1) if P else 0
+    return per_pair, total
+
 
 def _pairs_tensor(pairs, device, n_img: int | None = None) -> torch.Tensor:
     """int32 [P,2] on `device`. Host-side lists are range-checked here (free); a pair list that already lives on

@@ -82,6 +82,37 @@ def test_config3_257_images_16384_exhaustive(pkg):
     _check_sampled_cv2(desc, k, pairs, lists, sample)
 
 
+def test_config3_every_list_default_pipeline_equals_exact_pipeline(pkg):
+    """The WHOLE bench workload (all 32,896 pairs of BASELINE.json config 3) through the default pipeline (chunk
+    bounds on the norm-sorted bank + refine + fallback, whose shortcut proof depends on the data) and through the
+    independent exact pipeline 1 (threshold-reject top-1 sweep + verify sweeps on the original bank): the 64-bit
+    digest of every single pair's list (query rows, train rows, float32 distance bits) must agree."""
+    syn = importlib.import_module("3d_reconstruction_b200.synthetic")
+    n_img, k = 257, 16384
+    desc, kpi = syn.make_bank_tensor(n_img, k, seed=1234, device="cuda")
+    bank = pkg.DescriptorBank.from_packed(desc, kpi)
+    pairs = pkg.blocked_order(pkg.exhaustive_pairs(n_img))
+    per = {}
+    out = None
+    for pl in (2, 1):
+        pkg.set_option("pipeline", pl)
+        try:
+            out = pkg.match_pairs(bank, pairs, cap=4096, out=out)
+            out.check_overflow()
+            flat = out.flatten()
+            per[pl], total = flat.digest()
+            cnt = (flat.offsets[1:] - flat.offsets[:-1]).clone()
+            print(f"pipeline {pl}: {int(flat.offsets[-1])} matches, digest {total:016x}")
+            if pl == 2:
+                cnt2 = cnt
+        finally:
+            pkg.set_option("pipeline", 2)
+    assert int(cnt2.sum()) == 1126467
+    assert torch.equal(cnt, cnt2)
+    bad = torch.nonzero(per[1] != per[2]).flatten()
+    assert bad.numel() == 0, f"{bad.numel()} pairs differ between the pipelines, first: {pairs[bad[:5].cpu().numpy()].tolist()}"
+
+
 def test_config4_window_schedule_and_halo_shards(pkg):
     syn = importlib.import_module("3d_reconstruction_b200.synthetic")
     n_img, k, window = 2000, 8192, 32

@@ -1,0 +1,81 @@
+"""GPU: BASELINE.json config 1 at its REAL size with REAL SIFT descriptors (tests/golden/sift_full.npz: every
+descriptor of the reference's ystad_kloster/DSC_0001.JPG / DSC_0002.JPG, 56,041 x 52,421 rows, and the
+nfeatures=16384 subsets) against cv2 LIVE on this box: the complete knnMatch(k=2) table (indices + float32
+distance bits of every query row) and the ratio / cross-check lists, for every shipped pipeline variant.
+Real SIFT rows carry the norm / near-tie structure the chunk-bound + refine proof of the default pipeline
+leans on (csrc/match_refine.cuh), which synthetic rows only imitate."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import oracle_cv2
+
+pytestmark = pytest.mark.gpu
+
+VARIANTS = {"chunk256x64_refine": (1, 2, 5, 64), "chunk256x32_refine": (1, 2, 5, 32), "chunk_refine": (1, 2, 3, 64),
+            "top1_verify": (1, 1, 3, 64), "top2_reject": (1, 0, 3, 64)}
+
+
+def _bits(x):
+    return np.ascontiguousarray(x, dtype=np.float32).view(np.uint32)
+
+
+@pytest.fixture(scope="module")
+def cases(golden_dir):
+    g = np.load(os.path.join(golden_dir, "sift_full.npz"))
+    q, t = g["q"], g["t"]
+    q16, t16 = q[g["q_idx16k"]], t[g["t_idx16k"]]
+    out = {
+        "16k": (q16, t16),                      # cv2.SIFT_create(nfeatures=16384): 16,385 x 16,384
+        "ragged_8k_16k": (q16[:8192], t16),     # its 8,192 strongest keypoints against all of the other image
+        "full": (q, t),                         # nfeatures=0: 56,041 x 52,421
+    }
+    ref = {}
+    for name, (a, b) in out.items():
+        idx, dist = oracle_cv2.knn2(a, b)
+        ref[name] = {"knn": (idx, dist), "ratio_mutual": oracle_cv2.match(a, b, 0.75, True),
+                     "ratio": oracle_cv2.match(a, b, 0.75, False), "mutual": oracle_cv2.match(a, b, 0.0, True)}
+    # the box's cv2 agrees with the container that made the fixture
+    assert len(ref["full"]["ratio"][0]) == int(g["n_ratio_full"]) and len(ref["full"]["ratio_mutual"][0]) == int(g["n_mutual_full"])
+    assert len(ref["16k"]["ratio"][0]) == int(g["n_ratio_16k"]) and len(ref["16k"]["ratio_mutual"][0]) == int(g["n_mutual_16k"])
+    return out, ref
+
+
+@pytest.mark.parametrize("variant", list(VARIANTS))
+@pytest.mark.parametrize("case", ["16k", "ragged_8k_16k", "full"])
+def test_real_sift_equals_cv2(pkg, cases, case, variant):
+    data, ref = cases
+    q, t = data[case]
+    epi, pipeline, kernel, chunk = VARIANTS[variant]
+    for name, val in (("epilogue", epi), ("pipeline", pipeline), ("kernel", kernel), ("chunk", chunk)):
+        pkg.set_option(name, val)
+    try:
+        bank = pkg.DescriptorBank.from_arrays([q, t])
+        idx, dist = pkg.knn2_pairs(bank, [[0, 1]])
+        idx, dist = idx[0, :len(q)].cpu().numpy(), dist[0, :len(q)].cpu().numpy()
+        eidx, edist = ref[case]["knn"]
+        assert np.array_equal(idx, eidx), f"knn rows differ: {np.nonzero((idx != eidx).any(1))[0][:8]}"
+        assert np.array_equal(_bits(dist), _bits(edist))
+        for key, ratio, mutual in (("ratio_mutual", 0.75, True), ("ratio", 0.75, False), ("mutual", 0.0, True)):
+            gq, gt, gd = pkg.match_pairs(bank, [[0, 1]], ratio=ratio, mutual=mutual).to_lists()[0]
+            eq, et, ed = ref[case][key]
+            assert np.array_equal(gq, eq) and np.array_equal(gt, et), (key, len(gq), len(eq))
+            assert np.array_equal(_bits(gd), _bits(ed)), key
+            assert len(gq) > 1000
+        if variant == "chunk256x64_refine":
+            st = pkg.match_stats(_last_workspace(pkg, bank))
+            print(f"{case}: rows {st['rows']}, chunk-evaluated {st['rows_chunk_evaluated']}, fallback {st['rows_fallback']}, "
+                  f"ratio-verify {st['rows_ratio_verify']}, matches {st['matches']}")
+    finally:
+        for name, val in (("epilogue", 1), ("pipeline", 2), ("kernel", 5), ("chunk", 64)):
+            pkg.set_option(name, val)
+        torch.cuda.synchronize()
+
+
+def _last_workspace(pkg, bank):
+    """Runs the default rule once more with a workspace we keep, so that its counters can be read."""
+    ws = torch.empty(int(pkg._lib.lib().b200m_workspace_bytes(bank.k_stride, 1)), dtype=torch.uint8, device=bank.device)
+    pkg.match_pairs(bank, [[0, 1]], ratio=0.75, mutual=True, workspace=ws)
+    return ws
