@@ -20,8 +20,8 @@ from dataclasses import dataclass
 
 import numpy as np
 
-from .bank import DescriptorBank
-from .matcher import MatchConfig, match_pairs
+from .bank import DescriptorBank, FloatBank
+from .matcher import MatchConfig, match_pairs, match_pairs_float
 
 FOCAL_LENGTH = 2378.98305085      # matching.py:92 / sfm.py:24
 
@@ -131,6 +131,35 @@ def directed_edges(connection) -> np.ndarray:
     return np.asarray(sorted(set(out)), dtype=np.int32).reshape(-1, 2)
 
 
+# ---------------------------------------------------------------------- batched matching of the graph's edges
+def match_edges(all_descriptors, edges: np.ndarray, conf: MatchConfig, device="cuda") -> dict:
+    """{(a, b): (idx0, idx1)} for every directed edge, ONE batched GPU call, dispatched on conf.metric:
+      "l2_u8"   the exact integer rule (2-NN, Lowe ratio conf.ratio, cross-check conf.mutual) on SIFT-valued
+                descriptors -- integer values in [0, 255], verified while packing (bank.to_u8_descriptors);
+      "ip_bf16" mutual arg-max of the inner product with conf.score_threshold on float descriptors: what the
+                reference's own stage file holds (DISK, 128-d float32, feature_extraction.py:10,28,50) and the
+                raw-similarity form of its matcher head (lightglue.py:223,235-254).
+    Anything else raises (no setting is silently ignored)."""
+    if conf.metric not in ("l2_u8", "ip_bf16"):
+        raise NotImplementedError(f"unknown metric {conf.metric!r} (l2_u8 or ip_bf16)")
+    if conf.metric == "l2_u8" and conf.k != 2:
+        raise NotImplementedError("the l2_u8 rule is knnMatch k=2 + ratio + cross-check; other k are not implemented")
+    if conf.metric == "l2_u8" and conf.score_threshold is not None:
+        raise ValueError("score_threshold belongs to metric 'ip_bf16'; the l2_u8 rule filters with `ratio`")
+    out = {}
+    if not len(edges):
+        return out
+    if conf.metric == "ip_bf16":
+        bank = FloatBank.from_arrays([np.asarray(d, dtype=np.float32) for d in all_descriptors], device=device)
+        res = match_pairs_float(bank, edges, conf.score_threshold, conf.mutual)
+    else:
+        bank = DescriptorBank.from_arrays(list(all_descriptors), device=device)
+        res = match_pairs(bank, edges, ratio=conf.ratio, mutual=conf.mutual)
+    for (a, b), (q, t, _) in zip(np.asarray(edges).tolist(), res.to_lists()):
+        out[(a, b)] = (q, t)
+    return out
+
+
 # ---------------------------------------------------------------------- the walk
 def verify_edges_gpu(all_points, pair_matches, gates: "Gates", focal: float = FOCAL_LENGTH, device="cuda",
                      iters: int = 1024, seed: int = 0) -> dict:
@@ -163,13 +192,7 @@ def match_view_graph(all_descriptors, all_points, connection, start: int, conf: 
     gates = gates or Gates()
     n = len(all_descriptors)
     if pair_matches is None:
-        edges = directed_edges(connection)
-        pair_matches = {}
-        if len(edges):
-            bank = DescriptorBank.from_arrays(list(all_descriptors), device=device)
-            res = match_pairs(bank, edges, ratio=conf.ratio, mutual=conf.mutual)
-            for (a, b), (q, t, _) in zip(edges.tolist(), res.to_lists()):
-                pair_matches[(a, b)] = (q, t)
+        pair_matches = match_edges(all_descriptors, directed_edges(connection), conf, device)
 
     K = np.array([[focal, 0, 0], [0, focal, 0], [0, 0, 1]])
     pose_inliers = verify_edges_gpu(all_points, pair_matches, gates, focal, device) if geometry == "gpu" else None

@@ -9,8 +9,11 @@ output/*.npy and downloads LightGlue weights):
                       gate (:160), 3-D point id assignment (:161-172), [idx0, idx1, ids] rows (:174)
 The matcher is a parameter (any callable with the LightGlue dict contract, lightglue.py:326-341,
 442-450), so the same loop runs with the cv2 oracle matcher or with the product's B200Matcher.
-Parity status: the reference has no tests or fixtures for this stage; this restatement is pinned only
-by reading the script ("parity unpinned" by the reference itself).
+Parity status: PINNED to the reference's own script. tests/golden/make_golden_stage.py runs the unmodified
+/root/reference/matching.py under runpy (scratch output/ directory with real SIFT features of twelve of the
+reference's photographs, `lightglue` stubbed by the cv2 matcher) and commits what it wrote
+(tests/golden/stage_ref.npz); tests/test_driver_cpu.py::test_restated_loop_equals_the_reference_script_itself
+checks view_graph() and reference_loop() against those files entry for entry.
 """
 from __future__ import annotations
 

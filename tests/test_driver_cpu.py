@@ -8,6 +8,7 @@ import pytest
 
 from oracle import oracle_cv2, oracle_driver
 from tests.scene import make_scene
+from tests.stage_fixture import assert_same_stage, load_stage_ref
 
 
 @pytest.fixture(scope="module")
@@ -65,3 +66,29 @@ def test_stage_files_roundtrip(pkg, scene, tmp_path):
     idx0, idx1, ids = all_matches[0]                                                      # sfm.py:102-103
     assert np.array_equal(idx1, np.arange(5) + 1) and np.array_equal(ids, np.arange(5) + 7)
     assert np.array_equal(pts[0][idx0], pts[0][:5])                                       # fancy indexing as sfm.py:110
+
+
+def test_restated_loop_equals_the_reference_script_itself(pkg):
+    """tests/golden/stage_ref.npz holds what the UNMODIFIED /root/reference/matching.py wrote (img_pairs.npy,
+    all_matches.npy) when run under runpy on real SIFT features of twelve of its own photographs with its
+    hard-coded gates (cos > 0.75, > 8, > 10, >= 500, >= 30 %) and the cv2 matcher behind its LightGlue import.
+    oracle_driver (view graph + loop) and the product's host walk must reproduce those files entry for entry."""
+    drv = importlib.import_module("3d_reconstruction_b200.driver")
+    s = load_stage_ref()
+    assert len(s["img_pairs"]) >= 5
+    conn, start = oracle_driver.view_graph(s["desc"], s["k"], s["codebook"])
+    assert start == s["start"] and [list(map(int, c)) if c else [] for c in conn] == s["connection"]
+    conn2, start2 = drv.bow_view_graph(s["desc"], s["k"], s["codebook"])
+    assert start2 == s["start"] and [list(map(int, c)) if c else [] for c in conn2] == s["connection"]
+    pairs, matches = oracle_driver.reference_loop(s["desc"], s["pts"], s["size"], conn, start, oracle_driver.cv2_matcher())
+    assert_same_stage(s["img_pairs"], s["all_matches"], pairs, matches)
+    # the product's walk on injected cv2 matches (its GPU matcher is exercised by tests/test_gpu_driver.py)
+    cache = {}
+    for a, b in drv.directed_edges(conn2).tolist():
+        q, t, _ = oracle_cv2.match(s["desc"][a], s["desc"][b], 0.75, True)
+        cache[(a, b)] = (q, t)
+    pairs1, matches1 = drv.match_view_graph(s["desc"], s["pts"], conn2, start2, pair_matches=cache)
+    assert_same_stage(s["img_pairs"], s["all_matches"], pairs1, matches1)
+    # the gates did something on this scene: some visited edges were refused
+    n_edges = len(drv.directed_edges(conn2)) // 2
+    assert len(pairs) < n_edges

@@ -9,6 +9,7 @@ import pytest
 
 from oracle import oracle_driver
 from tests.scene import make_scene
+from tests.stage_fixture import assert_same_stage, load_stage_ref
 
 pytestmark = pytest.mark.gpu
 
@@ -104,3 +105,77 @@ def test_driver_on_real_photographs(pkg, golden_dir):
         assert int(gp.inliers[0]) >= 0.9 * int(cv[1].sum())
     got_gpu = drv.match_view_graph(desc, pts, conn, start, gates=drv.Gates(min_matches=60), geometry="gpu")
     assert len(got_gpu[0]) >= 3 and all(len(r) == 3 and len(r[0]) == len(r[1]) == len(r[2]) for r in got_gpu[1])
+
+
+def test_driver_equals_the_reference_script_itself(pkg, tmp_path):
+    """The product stage (GPU visual words -> view graph -> every directed edge matched in one batched GPU call ->
+    host walk with the reference's default gates) against the files the UNMODIFIED /root/reference/matching.py
+    wrote for the same inputs (tests/golden/stage_ref.npz, made by tests/golden/make_golden_stage.py); also the
+    product matcher as the script's own `matcher` callable (matching.py:20,122)."""
+    drv = importlib.import_module("3d_reconstruction_b200.driver")
+    s = load_stage_ref()
+    conn, start = drv.bow_view_graph(s["desc"], s["k"], s["codebook"], device="cuda")
+    assert start == s["start"] and [list(map(int, c)) if c else [] for c in conn] == s["connection"]
+    pairs, matches = drv.match_view_graph(s["desc"], s["pts"], conn, start)
+    assert_same_stage(s["img_pairs"], s["all_matches"], pairs, matches)
+    via = oracle_driver.reference_loop(s["desc"], s["pts"], s["size"], conn, start, pkg.B200Matcher())
+    assert_same_stage(s["img_pairs"], s["all_matches"], *via)
+    # stage files in -> stage files out (run_matching_stage), in the reference's on-disk layout
+    import joblib
+    out = str(tmp_path)
+    np.save(os.path.join(out, "all_descriptors.npy"), s["desc"])
+    np.save(os.path.join(out, "all_points.npy"), s["pts"])
+    np.save(os.path.join(out, "img_size.npy"), s["size"])
+    joblib.dump((s["k"], s["codebook"]), os.path.join(out, "bow_codebook.plk"), compress=3)
+    drv.run_matching_stage(out)
+    img_pairs = np.load(os.path.join(out, "img_pairs.npy"), allow_pickle=True)
+    all_matches = np.load(os.path.join(out, "all_matches.npy"), allow_pickle=True)
+    assert_same_stage(s["img_pairs"], s["all_matches"], img_pairs, [list(r) for r in all_matches])
+
+
+def test_driver_float_descriptors_dispatch(pkg):
+    """The reference's own stage file holds FLOAT descriptors (DISK, feature_extraction.py:10,28,50): with
+    MatchConfig(metric="ip_bf16") the driver packs a bf16 bank and runs the mutual arg-max rule with the score
+    threshold; the walk equals the restated reference loop driven by the float oracle matcher (inputs are
+    bf16-representable, so the two agree row for row). Unsupported settings raise instead of being ignored."""
+    import torch
+
+    from oracle import oracle_float
+    drv = importlib.import_module("3d_reconstruction_b200.driver")
+    rng = np.random.default_rng(5)
+    n_img, n_world, k_img = 6, 2600, 1400
+    world = rng.standard_normal((n_world, 128)).astype(np.float32)
+    world /= np.linalg.norm(world, axis=1, keepdims=True)
+    xyz = rng.uniform([-4, -3, 8], [4, 3, 14], size=(n_world, 3))
+    desc = np.array([None] * n_img, dtype=object)
+    pts = np.array([None] * n_img, dtype=object)
+    size = np.array([None] * n_img, dtype=object)
+    for i in range(n_img):
+        ids = rng.permutation(n_world)[:k_img]
+        d = world[ids] + 0.04 * rng.standard_normal((k_img, 128)).astype(np.float32)
+        d /= np.linalg.norm(d, axis=1, keepdims=True)
+        desc[i] = torch.from_numpy(d).to(torch.bfloat16).float().numpy()          # DISK-shaped: float32 [K, 128], unit norm
+        cam = xyz[ids] + np.array([-(i - n_img / 2) * 0.5, 0.0, 0.0])
+        pts[i] = (drv.FOCAL_LENGTH * cam[:, :2] / cam[:, 2:3] + rng.normal(0, 0.3, size=(k_img, 2))).astype(np.float32)
+        size[i] = np.array([1296.0, 1936.0], dtype=np.float32)
+    connection = [[j for j in range(n_img) if j != i] for i in range(n_img)]
+    thr = 0.6
+
+    def float_oracle_matcher(data):
+        q, t, sc = oracle_float.match(data["image0"]["descriptors"][0].numpy(), data["image1"]["descriptors"][0].numpy(), thr, True)
+        return {"matches": [torch.from_numpy(np.stack([q, t], -1).astype(np.int64)).reshape(-1, 2)], "scores": [torch.from_numpy(sc)]}
+
+    ref = oracle_driver.reference_loop(desc, pts, size, connection, 0, float_oracle_matcher, min_matches=200)
+    assert len(ref[0]) >= 3
+    conf = pkg.MatchConfig(metric="ip_bf16", score_threshold=thr, mutual=True)
+    got = drv.match_view_graph(desc, pts, connection, 0, conf=conf, gates=drv.Gates(min_matches=200))
+    _same(ref, got)
+    # the u8 path refuses float descriptors loudly, unknown settings raise
+    with pytest.raises(ValueError):
+        drv.match_view_graph(desc, pts, connection, 0, conf=pkg.MatchConfig())
+    with pytest.raises(NotImplementedError):
+        drv.match_view_graph(desc, pts, connection, 0, conf=pkg.MatchConfig(metric="hamming"))
+    with pytest.raises(NotImplementedError):
+        drv.match_view_graph(desc, pts, connection, 0, conf=pkg.MatchConfig(k=3))
+    with pytest.raises(ValueError):
+        drv.match_view_graph(desc, pts, connection, 0, conf=pkg.MatchConfig(score_threshold=0.5))

@@ -34,9 +34,21 @@ def cases(golden_dir):
     }
     ref = {}
     for name, (a, b) in out.items():
+        # two cv2 calls per case (forward k=2, reverse: its first column is knnMatch k=1); the three lists are
+        # derived from them exactly as oracle_cv2.match does (Python-float compare of the float32 distances)
         idx, dist = oracle_cv2.knn2(a, b)
-        ref[name] = {"knn": (idx, dist), "ratio_mutual": oracle_cv2.match(a, b, 0.75, True),
-                     "ratio": oracle_cv2.match(a, b, 0.75, False), "mutual": oracle_cv2.match(a, b, 0.0, True)}
+        nearest_q = oracle_cv2.knn2(b, a)[0][:, 0]
+        rows = np.arange(len(a))
+        lowe = dist[:, 0].astype(np.float64) < 0.75 * dist[:, 1].astype(np.float64)
+        mut = nearest_q[idx[:, 0]] == rows
+
+        def pick(mask):
+            return rows[mask].astype(np.int32), idx[mask, 0], dist[mask, 0]
+        ref[name] = {"knn": (idx, dist), "ratio_mutual": pick(lowe & mut), "ratio": pick(lowe), "mutual": pick(mut)}
+    # ... and that derivation is oracle_cv2.match itself on the smallest case
+    eq, et, ed = oracle_cv2.match(*out["ragged_8k_16k"], 0.75, True)
+    gq, gt, gd = ref["ragged_8k_16k"]["ratio_mutual"]
+    assert np.array_equal(eq, gq) and np.array_equal(et, gt) and np.array_equal(_bits(ed), _bits(gd))
     # the box's cv2 agrees with the container that made the fixture
     assert len(ref["full"]["ratio"][0]) == int(g["n_ratio_full"]) and len(ref["full"]["ratio_mutual"][0]) == int(g["n_mutual_full"])
     assert len(ref["16k"]["ratio"][0]) == int(g["n_ratio_16k"]) and len(ref["16k"]["ratio_mutual"][0]) == int(g["n_mutual_16k"])
