@@ -21,6 +21,8 @@ SYMBOLS = (
     "b200m_bank_prepare_u8",
     "b200m_sort_table_elems",
     "b200m_bank_sort_u8",
+    "b200m_bank_prepare_range_u8",
+    "b200m_bank_sort_range_u8",
     "b200m_workspace_bytes",
     "b200m_knn2_u8",
     "b200m_match_pairs_u8",
@@ -75,6 +77,10 @@ def lib() -> C.CDLL:
     L.b200m_sort_table_elems.argtypes = [i32, i64]
     L.b200m_bank_sort_u8.restype = C.c_int
     L.b200m_bank_sort_u8.argtypes = [vp, vp, vp, i32, i64, vp, vp, vp]
+    L.b200m_bank_prepare_range_u8.restype = C.c_int
+    L.b200m_bank_prepare_range_u8.argtypes = [vp, i32, i64, vp, vp, i32, i32, vp]
+    L.b200m_bank_sort_range_u8.restype = C.c_int
+    L.b200m_bank_sort_range_u8.argtypes = [vp, vp, vp, i32, i64, vp, vp, i32, i32, vp]
     L.b200m_workspace_bytes.restype = sz
     L.b200m_workspace_bytes.argtypes = [i64, i64]
     L.b200m_knn2_u8.restype = C.c_int

@@ -85,6 +85,58 @@ class DescriptorBank:
         return cls(desc, k_per_image, sqnorm, sorted_desc, sort_table)
 
     @classmethod
+    def allocate(cls, n_img: int, k_stride: int, k_per_image: torch.Tensor, device="cuda") -> "DescriptorBank":
+        """Uninitialised device bank (descriptors, norm table, norm-sorted copy, sort table) for `n_img` images; the
+        caller fills `desc` image range by image range and calls prepare_range for each (matcher.match_pairs_host
+        behind chunked host->device copies, distributed.match_pairs_host on the image slice of every rank)."""
+        dev = torch.device(device)
+        if dev.type != "cuda":
+            raise RuntimeError("the descriptor bank must live on a CUDA device (there is no CPU path)")
+        if k_stride % TILE_T != 0 or k_stride <= 0 or n_img <= 0:
+            raise ValueError("k_stride must be a positive multiple of 256 and n_img positive")
+        k_per_image = torch.as_tensor(k_per_image)
+        if k_per_image.numel() != n_img:
+            raise ValueError("k_per_image must have one entry per image")
+        if not k_per_image.is_cuda and (int(k_per_image.min()) < 0 or int(k_per_image.max()) > k_stride):
+            raise ValueError("k_per_image entries must lie in [0, k_stride]")
+        L = _lib.lib()
+        desc = torch.empty((n_img, k_stride, DESC_DIM), dtype=torch.uint8, device=dev)
+        sqnorm = torch.empty((int(L.b200m_norm_table_elems(n_img, k_stride)),), dtype=torch.int32, device=dev)
+        sorted_desc = torch.empty_like(desc)
+        sort_table = torch.empty((int(L.b200m_sort_table_elems(n_img, k_stride)),), dtype=torch.int32, device=dev)
+        sort_table[3 * n_img * k_stride + n_img * k_stride // 32:].zero_()     # the two per-image spread arrays (+ padding)
+        return cls(desc, k_per_image.to(device=dev, dtype=torch.int32, non_blocking=True).contiguous(), sqnorm,
+                   sorted_desc, sort_table)
+
+    def prepare_range(self, img_lo: int, img_count: int) -> None:
+        """Norms, padding, norm-sorted copy and tables of the images [img_lo, img_lo + img_count) on the current
+        stream (b200m_bank_prepare_range_u8 + b200m_bank_sort_range_u8); ranges are independent."""
+        L = _lib.lib()
+        with torch.cuda.device(self.device):
+            st = torch.cuda.current_stream().cuda_stream
+            _lib.check(L.b200m_bank_prepare_range_u8(self.desc.data_ptr(), self.n_img, self.k_stride,
+                                                     self.k_per_image.data_ptr(), self.sqnorm.data_ptr(),
+                                                     int(img_lo), int(img_count), st))
+            if self.sorted_desc is not None:
+                _lib.check(L.b200m_bank_sort_range_u8(self.desc.data_ptr(), self.sqnorm.data_ptr(),
+                                                      self.k_per_image.data_ptr(), self.n_img, self.k_stride,
+                                                      self.sorted_desc.data_ptr(), self.sort_table.data_ptr(),
+                                                      int(img_lo), int(img_count), st))
+
+    def table_sections(self):
+        """Views of every per-image section of the bank's tensors as (tensor, rows per image) -- what a multi-GPU
+        all-gather of image slices has to move (distributed.allgather_bank)."""
+        R, ks, n = self.n_img * self.k_stride, self.k_stride, self.n_img
+        out = [(self.desc.view(-1), ks * DESC_DIM), (self.sqnorm[:R], ks), (self.sqnorm[R:R + R // 32], ks // 32)]
+        if self.sorted_desc is not None:
+            t = self.sort_table
+            n4 = (n + 3) & ~3
+            b = 3 * R + R // 32
+            out += [(self.sorted_desc.view(-1), ks * DESC_DIM), (t[:R], ks), (t[R:2 * R], ks), (t[2 * R:3 * R], ks),
+                    (t[3 * R:b], ks // 32), (t[b:b + n], 1), (t[b + n4:b + n4 + n], 1)]
+        return out
+
+    @classmethod
     def from_arrays(cls, arrays: Sequence, device="cuda", k_stride: int | None = None) -> "DescriptorBank":
         """arrays: one [K_i,128] array per image (u8, or integer-valued float as cv2.SIFT emits).
         CUDA tensors already on `device` are verified and packed there (no host round trip)."""

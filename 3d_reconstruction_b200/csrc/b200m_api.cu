@@ -292,6 +292,9 @@ int64_t batch_pairs(int64_t k_stride, int64_t n_pairs) {
   if (b < 1) b = 1;
   if (b > n_pairs) b = n_pairs;
   if (b < 1) b = 1;
+  // equal batches: 4,112 pairs run as 17 x 242 instead of 16 x 256 + a launch sequence carrying 16 pairs
+  const int64_t n_batches = (n_pairs + b - 1) / b;
+  if (n_batches > 1) b = (n_pairs + n_batches - 1) / n_batches;
   return b;
 }
 
@@ -530,27 +533,41 @@ int64_t b200m_norm_table_elems(int32_t n_img, int64_t k_stride) {
   return rows + rows / 32;
 }
 
-int b200m_bank_prepare_u8(uint8_t* bank, int32_t n_img, int64_t k_stride, const int32_t* k_per_image,
-                          int32_t* norm_table, void* stream) {
+int b200m_bank_prepare_range_u8(uint8_t* bank, int32_t n_img, int64_t k_stride, const int32_t* k_per_image,
+                                int32_t* norm_table, int32_t img_lo, int32_t img_count, void* stream) {
   if (!bank || !k_per_image || !norm_table || n_img <= 0) return fail(B200M_E_BAD_ARG, "null argument or n_img <= 0%s");
   if (k_stride <= 0 || (k_stride % B200M_TILE_T) != 0)
     return fail(B200M_E_BAD_ARG, "k_stride must be a positive multiple of 256%s");
+  if (img_lo < 0 || img_count < 0 || static_cast<int64_t>(img_lo) + img_count > n_img)
+    return fail(B200M_E_BAD_ARG, "image range outside [0, n_img)%s");
   if (device_info().ok != 1) return fail(B200M_E_NO_DEVICE, "no sm_100 CUDA device available (no CPU fallback)%s");
-  const int64_t n_rows = static_cast<int64_t>(n_img) * k_stride;
+  if (img_count == 0) return B200M_OK;
+  // every kernel below indexes relative to its first row, so a range is the same launch on offset pointers;
+  // only the section offsets of the tables come from the size of the WHOLE bank
+  const int64_t all_rows = static_cast<int64_t>(n_img) * k_stride;
+  const int64_t row_lo = static_cast<int64_t>(img_lo) * k_stride;
+  const int64_t n_rows = static_cast<int64_t>(img_count) * k_stride;
   const int block = 256;
   int64_t blocks = (n_rows * 32 + block - 1) / block;
   const int64_t max_blocks = static_cast<int64_t>(device_info().sms) * 16;
   if (blocks > max_blocks) blocks = max_blocks;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  b200m::bank_prepare_kernel<<<static_cast<int>(blocks), block, 0, st>>>(bank, n_rows, k_stride, k_per_image,
-                                                                         norm_table, B200M_PAD_NORM);
+  b200m::bank_prepare_kernel<<<static_cast<int>(blocks), block, 0, st>>>(bank + row_lo * 128, n_rows, k_stride,
+                                                                         k_per_image + img_lo, norm_table + row_lo,
+                                                                         B200M_PAD_NORM);
   CUDA_TRY(cudaGetLastError());
   g_prof.launches.fetch_add(2);
   int64_t blocks2 = (n_rows + block - 1) / block;
   if (blocks2 > max_blocks) blocks2 = max_blocks;
-  b200m::norm_chunk_min_kernel<<<static_cast<int>(blocks2), block, 0, st>>>(norm_table, n_rows, norm_table + n_rows);
+  b200m::norm_chunk_min_kernel<<<static_cast<int>(blocks2), block, 0, st>>>(norm_table + row_lo, n_rows,
+                                                                            norm_table + all_rows + row_lo / 32);
   CUDA_TRY(cudaGetLastError());
   return B200M_OK;
+}
+
+int b200m_bank_prepare_u8(uint8_t* bank, int32_t n_img, int64_t k_stride, const int32_t* k_per_image,
+                          int32_t* norm_table, void* stream) {
+  return b200m_bank_prepare_range_u8(bank, n_img, k_stride, k_per_image, norm_table, 0, n_img, stream);
 }
 
 int64_t b200m_sort_table_elems(int32_t n_img, int64_t k_stride) {
@@ -558,23 +575,37 @@ int64_t b200m_sort_table_elems(int32_t n_img, int64_t k_stride) {
   return sort_table_elems(n_img, k_stride);
 }
 
-int b200m_bank_sort_u8(const uint8_t* bank, const int32_t* norm_table, const int32_t* k_per_image, int32_t n_img,
-                       int64_t k_stride, uint8_t* sorted_bank, int32_t* sort_table, void* stream) {
+int b200m_bank_sort_range_u8(const uint8_t* bank, const int32_t* norm_table, const int32_t* k_per_image, int32_t n_img,
+                             int64_t k_stride, uint8_t* sorted_bank, int32_t* sort_table, int32_t img_lo,
+                             int32_t img_count, void* stream) {
   if (!bank || !norm_table || !k_per_image || !sorted_bank || !sort_table || n_img <= 0)
     return fail(B200M_E_BAD_ARG, "null argument or n_img <= 0%s");
   if (k_stride <= 0 || (k_stride % B200M_TILE_T) != 0)
     return fail(B200M_E_BAD_ARG, "k_stride must be a positive multiple of 256%s");
+  if (img_lo < 0 || img_count < 0 || static_cast<int64_t>(img_lo) + img_count > n_img)
+    return fail(B200M_E_BAD_ARG, "image range outside [0, n_img)%s");
   if (device_info().ok != 1) return fail(B200M_E_NO_DEVICE, "no sm_100 CUDA device available (no CPU fallback)%s");
+  if (img_count == 0) return B200M_OK;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  const int64_t R = static_cast<int64_t>(n_img) * k_stride;
+  const int64_t row_lo = static_cast<int64_t>(img_lo) * k_stride;
+  const int64_t R = static_cast<int64_t>(img_count) * k_stride;      // rows of the range
   int64_t n2 = b200m::kSortChunk;
   while (n2 < k_stride) n2 <<= 1;
   // the 64-bit sort keys live in the (not yet written) sorted bank: 8 * n2 <= 16 * k_stride bytes of each 128 * k_stride slab
-  unsigned long long* keys = reinterpret_cast<unsigned long long*>(sorted_bank);
+  unsigned long long* keys = reinterpret_cast<unsigned long long*>(sorted_bank + row_lo * 128);
   const int64_t key_stride = k_stride * 16;
+  // sections of the WHOLE bank's table, every pointer moved to the first image of the range (the kernels index
+  // relative to their first row / image)
   const SortTable tv = sort_table_view(sort_table, n_img, k_stride);
-  const int64_t total = static_cast<int64_t>(n_img) * n2;
-  b200m::sort_init_kernel<<<grid_for(total, 256), 256, 0, st>>>(norm_table, k_stride, n2, total, keys, key_stride);
+  int32_t* perm = const_cast<int32_t*>(tv.perm) + row_lo;
+  int32_t* inv = const_cast<int32_t*>(tv.inv) + row_lo;
+  int32_t* snorm = const_cast<int32_t*>(tv.snorm) + row_lo;
+  int32_t* cmin = const_cast<int32_t*>(tv.cmin) + row_lo / 32;
+  int32_t* spread = const_cast<int32_t*>(tv.spread) + img_lo;
+  int32_t* spread64 = const_cast<int32_t*>(tv.spread64) + img_lo;
+  const int32_t* norms = norm_table + row_lo;
+  const int64_t total = static_cast<int64_t>(img_count) * n2;
+  b200m::sort_init_kernel<<<grid_for(total, 256), 256, 0, st>>>(norms, k_stride, n2, total, keys, key_stride);
   CUDA_TRY(cudaGetLastError());
   const unsigned smem_blocks = static_cast<unsigned>(total / b200m::kSortChunk);
   b200m::sort_smem_kernel<true><<<smem_blocks, b200m::kSortThreads, 0, st>>>(keys, n2, key_stride, 0);
@@ -582,7 +613,7 @@ int b200m_bank_sort_u8(const uint8_t* bank, const int32_t* norm_table, const int
   g_prof.launches.fetch_add(2);
   for (int64_t size = 2 * b200m::kSortChunk; size <= n2; size <<= 1) {
     for (int64_t stride = size / 2; stride >= b200m::kSortChunk; stride >>= 1) {
-      b200m::sort_global_kernel<<<grid_for(total / 2, 256), 256, 0, st>>>(keys, n2, key_stride, n_img, size, stride);
+      b200m::sort_global_kernel<<<grid_for(total / 2, 256), 256, 0, st>>>(keys, n2, key_stride, img_count, size, stride);
       CUDA_TRY(cudaGetLastError());
       g_prof.launches.fetch_add(1);
     }
@@ -590,18 +621,26 @@ int b200m_bank_sort_u8(const uint8_t* bank, const int32_t* norm_table, const int
     CUDA_TRY(cudaGetLastError());
     g_prof.launches.fetch_add(1);
   }
-  b200m::sort_extract_kernel<<<grid_for(R, 256), 256, 0, st>>>(keys, key_stride, k_stride, R, const_cast<int32_t*>(tv.perm),
-                                                              const_cast<int32_t*>(tv.inv), const_cast<int32_t*>(tv.snorm));
+  b200m::sort_extract_kernel<<<grid_for(R, 256), 256, 0, st>>>(keys, key_stride, k_stride, R, perm, inv, snorm);
   CUDA_TRY(cudaGetLastError());
-  b200m::sort_gather_kernel<<<grid_for(R * 32, 256), 256, 0, st>>>(bank, tv.perm, k_stride, R, sorted_bank);
+  b200m::sort_gather_kernel<<<grid_for(R * 32, 256), 256, 0, st>>>(bank + row_lo * 128, perm, k_stride, R,
+                                                                   sorted_bank + row_lo * 128);
   CUDA_TRY(cudaGetLastError());
-  CUDA_TRY(cudaMemsetAsync(const_cast<int32_t*>(tv.spread), 0, sizeof(int32_t) * 2 * ((n_img + 3) & ~3), st));
-  b200m::sort_chunk_stats_kernel<<<grid_for(R / 32, 256), 256, 0, st>>>(tv.snorm, k_per_image, k_stride, R / 32,
-                                                                      const_cast<int32_t*>(tv.cmin), const_cast<int32_t*>(tv.spread),
-                                                                      const_cast<int32_t*>(tv.spread64));
+  CUDA_TRY(cudaMemsetAsync(spread, 0, sizeof(int32_t) * img_count, st));
+  CUDA_TRY(cudaMemsetAsync(spread64, 0, sizeof(int32_t) * img_count, st));
+  b200m::sort_chunk_stats_kernel<<<grid_for(R / 32, 256), 256, 0, st>>>(snorm, k_per_image + img_lo, k_stride, R / 32,
+                                                                      cmin, spread, spread64);
   CUDA_TRY(cudaGetLastError());
   g_prof.launches.fetch_add(3);
   return B200M_OK;
+}
+
+int b200m_bank_sort_u8(const uint8_t* bank, const int32_t* norm_table, const int32_t* k_per_image, int32_t n_img,
+                       int64_t k_stride, uint8_t* sorted_bank, int32_t* sort_table, void* stream) {
+  if (sort_table && n_img > 0 && k_stride > 0)      // the padding entries of the two spread arrays (n_img rounded up to 4) stay defined
+    cudaMemsetAsync(sort_table + 3 * static_cast<int64_t>(n_img) * k_stride + static_cast<int64_t>(n_img) * k_stride / 32, 0,
+                    sizeof(int32_t) * 2 * ((n_img + 3) & ~3), static_cast<cudaStream_t>(stream));
+  return b200m_bank_sort_range_u8(bank, norm_table, k_per_image, n_img, k_stride, sorted_bank, sort_table, 0, n_img, stream);
 }
 
 size_t b200m_workspace_bytes(int64_t k_stride, int64_t n_pairs) {

@@ -83,8 +83,18 @@ class FlatMatches:
     dist: torch.Tensor        # float32 [S_total]
     offsets: torch.Tensor     # int64 [P + 1]
 
-    def cpu(self) -> "FlatMatches":
-        return FlatMatches(self.query_idx.cpu(), self.train_idx.cpu(), self.dist.cpu(), self.offsets.cpu())
+    def cpu(self, staging: bool = False) -> "FlatMatches":
+        """Host copy. staging=True copies through cached PINNED buffers with one synchronisation; the returned
+        tensors then alias those buffers and are overwritten by the next staging=True call on this process."""
+        if not staging or not self.offsets.is_cuda:
+            return FlatMatches(self.query_idx.cpu(), self.train_idx.cpu(), self.dist.cpu(), self.offsets.cpu())
+        outs = []
+        for name, t in (("q", self.query_idx), ("t", self.train_idx), ("d", self.dist), ("o", self.offsets)):
+            h = _pinned(name, t.numel(), t.dtype)
+            h.copy_(t, non_blocking=True)
+            outs.append(h)
+        torch.cuda.current_stream(self.offsets.device).synchronize()
+        return FlatMatches(*outs)
 
     def pair(self, p: int):
         a, b = int(self.offsets[p]), int(self.offsets[p + 1])
@@ -98,6 +108,18 @@ class FlatMatches:
         N-GPU == 1-GPU check of bench.py and tests/test_gpu_multirank.py (matching.py:174,188-189: one ordered
         row per pair, whoever computed it)."""
         return digest_matches(self.query_idx, self.train_idx, self.dist, self.offsets, pair_ids)
+
+
+_pinned_cache: dict = {}
+
+
+def _pinned(name: str, numel: int, dtype) -> torch.Tensor:
+    """A pinned host tensor of `numel` elements from a grow-only cache (cudaHostAlloc costs milliseconds)."""
+    buf = _pinned_cache.get((name, dtype))
+    if buf is None or buf.numel() < numel:
+        buf = torch.empty((max(numel, 1) * 5 // 4 + 16,), dtype=dtype).pin_memory()
+        _pinned_cache[(name, dtype)] = buf
+    return buf[:numel]
 
 
 def _i64(c: int) -> int:
@@ -255,17 +277,97 @@ def knn2_pairs(bank: DescriptorBank, pairs, workspace: torch.Tensor | None = Non
     return idx, dist
 
 
+def _new_out(n_pairs: int, cap: int, dev) -> PairMatches:
+    return PairMatches(torch.empty((n_pairs, cap), dtype=torch.int32, device=dev),
+                       torch.empty((n_pairs, cap), dtype=torch.int32, device=dev),
+                       torch.empty((n_pairs, cap), dtype=torch.float32, device=dev),
+                       torch.zeros((n_pairs,), dtype=torch.int32, device=dev), int(cap))
+
+
+def _out_rows(out: PairMatches, lo: int, hi: int) -> PairMatches:
+    return PairMatches(out.query_idx[lo:hi], out.train_idx[lo:hi], out.dist[lo:hi], out.count[lo:hi], out.cap)
+
+
+def upload_segments(pairs: np.ndarray, n_img: int, block: int):
+    """Split a pair list, IN ORDER, into segments that can start as soon as a prefix of the image blocks is
+    resident: -> list of (last image block needed, first pair, end pair). The blocked order of the scheduler
+    (16 x 16 patches of the pair grid) needs the blocks one after the other; any other order still works (its
+    first segment simply waits for more of the bank)."""
+    if len(pairs) == 0:
+        return []
+    need = np.maximum.accumulate(pairs.max(axis=1) // block)
+    cuts = np.nonzero(np.diff(need))[0] + 1
+    starts = np.concatenate([[0], cuts])
+    ends = np.concatenate([cuts, [len(pairs)]])
+    return [(int(need[a]), int(a), int(b)) for a, b in zip(starts, ends)]
+
+
 def match_pairs_host(desc_host: torch.Tensor, k_per_image, pairs, ratio: float = 0.75, mutual: bool = True,
-                     cap: int | None = None, device="cuda") -> FlatMatches:
+                     cap: int | None = None, device="cuda", block: int = 16, out: PairMatches | None = None,
+                     workspace: torch.Tensor | None = None, staging: bool = False) -> FlatMatches:
     """End-to-end call with HOST buffers: descriptors (uint8 [n_img, k_stride, 128], ideally pinned) and
     the pair list go host -> device, the matches come back as flat host arrays. This is the unit the
-    reference performs per pair at matching.py:107-128 (host descriptors in, idx0 / idx1 on the host out)."""
+    reference performs per pair at matching.py:107-128 (host descriptors in, idx0 / idx1 on the host out).
+
+    The bank is uploaded in blocks of `block` images on a copy stream; every block is prepared (norms, padding,
+    norm sort) as it lands, and the pairs whose images are resident are matched while the rest of the bank is
+    still on its way: only the first block's copy is exposed. Results are identical to
+    match_pairs(DescriptorBank.from_packed(...)) -- same kernels, same order inside every pair.
+    staging=True: the result aliases cached pinned buffers (FlatMatches.cpu)."""
     dev = torch.device(device)
-    desc = desc_host.to(dev, non_blocking=True)
-    kpi = torch.as_tensor(np.asarray(k_per_image, dtype=np.int32)).to(dev, non_blocking=True)
-    bank = DescriptorBank.from_packed(desc, kpi)
-    res = match_pairs(bank, pairs, ratio=ratio, mutual=mutual, cap=cap)
-    return res.flatten().cpu()
+    if dev.type != "cuda":
+        raise RuntimeError("match_pairs_host runs on a CUDA device (there is no CPU path)")
+    if desc_host.dtype != torch.uint8 or desc_host.dim() != 3 or desc_host.shape[2] != 128:
+        raise ValueError("desc_host must be uint8 [n_img, k_stride, 128]")
+    n_img, ks = int(desc_host.shape[0]), int(desc_host.shape[1])
+    kpi = torch.as_tensor(np.asarray(k_per_image, dtype=np.int32))
+    pairs_np = np.ascontiguousarray(np.asarray(pairs.cpu() if isinstance(pairs, torch.Tensor) else pairs,
+                                               dtype=np.int64).reshape(-1, 2))
+    if pairs_np.size and (pairs_np.min() < 0 or pairs_np.max() >= n_img):
+        raise ValueError(f"pairs must index images in [0, {n_img})")
+    P = len(pairs_np)
+    cap = ks if cap is None else int(cap)
+    with torch.cuda.device(dev):
+        main = torch.cuda.current_stream()
+        bank = DescriptorBank.allocate(n_img, ks, kpi, dev)
+        pairs_dev = torch.from_numpy(pairs_np.astype(np.int32)).to(dev, non_blocking=True)
+        if out is None:
+            out = _new_out(P, cap, dev)
+        else:
+            _check_out(out, P)
+        ws = workspace if workspace is not None else _workspace(bank, max(P, 1))
+        copy = _copy_stream(dev)
+        copy.wait_stream(main)                       # the bank's memory may have been in use on `main` a moment ago
+        n_blocks = (n_img + block - 1) // block
+        landed = []
+        with torch.cuda.stream(copy):
+            for b in range(n_blocks):
+                lo, hi = b * block, min(n_img, (b + 1) * block)
+                bank.desc[lo:hi].copy_(desc_host[lo:hi], non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(copy)
+                landed.append(ev)
+        segs = upload_segments(pairs_np, n_img, block)
+        si = 0
+        for b in range(n_blocks):
+            main.wait_event(landed[b])
+            bank.prepare_range(b * block, min(n_img, (b + 1) * block) - b * block)
+            while si < len(segs) and segs[si][0] <= b:
+                _, p0, p1 = segs[si]
+                match_pairs(bank, pairs_dev[p0:p1], ratio=ratio, mutual=mutual, cap=cap, out=_out_rows(out, p0, p1),
+                            workspace=ws)
+                si += 1
+        return out.flatten().cpu(staging)
+
+
+_copy_streams: dict = {}
+
+
+def _copy_stream(dev: torch.device) -> "torch.cuda.Stream":
+    key = dev.index if dev.index is not None else torch.cuda.current_device()
+    if key not in _copy_streams:
+        _copy_streams[key] = torch.cuda.Stream(device=dev)
+    return _copy_streams[key]
 
 
 # ---------------------------------------------------------------------- cv2-shaped single pair

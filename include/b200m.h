@@ -37,7 +37,7 @@
 extern "C" {
 #endif
 
-#define B200M_VERSION 110          /* 0.1.1 */
+#define B200M_VERSION 120          /* 0.2.0 */
 #define B200M_DESC_DIM 128         /* SIFT / DISK descriptor length handled by the u8 path */
 #define B200M_TILE_Q 128           /* query rows per UMMA M-tile (two per work item) */
 #define B200M_TILE_T 256           /* train rows per tile (UMMA N) */
@@ -83,6 +83,19 @@ int64_t b200m_sort_table_elems(int32_t n_img, int64_t k_stride);
 int b200m_bank_sort_u8(const uint8_t* bank, const int32_t* norm_table, const int32_t* k_per_image,
                        int32_t n_img, int64_t k_stride,
                        uint8_t* sorted_bank, int32_t* sort_table, void* stream);
+
+/* The same two passes over the images [img_lo, img_lo + img_count) only; table layouts stay those of the WHOLE bank
+ * (n_img images). Lets a caller prepare the bank while it is still arriving -- block by block behind the
+ * host->device copies of one process, or slice by slice on the ranks of a multi-GPU job, each preparing the images
+ * it uploaded before an all-gather distributes bank and tables (the per-pair host->device repacking of
+ * matching.py:107-120, overlapped and sharded). Ranges are independent of each other. */
+int b200m_bank_prepare_range_u8(uint8_t* bank, int32_t n_img, int64_t k_stride,
+                                const int32_t* k_per_image, int32_t* norm_table,
+                                int32_t img_lo, int32_t img_count, void* stream);
+int b200m_bank_sort_range_u8(const uint8_t* bank, const int32_t* norm_table, const int32_t* k_per_image,
+                             int32_t n_img, int64_t k_stride,
+                             uint8_t* sorted_bank, int32_t* sort_table,
+                             int32_t img_lo, int32_t img_count, void* stream);
 
 /* Scratch bytes needed to process `n_pairs` pairs of images with slab stride `k_stride`.
  * Pairs are processed in internal batches, so this saturates at a fixed batch size. */

@@ -111,3 +111,33 @@ def assign(mdesc0, mdesc1, z0, z1, th=None):
     m0, m1, ms0, ms1 = filter_log_matches(scores, th)
     q, t = match_list(m0)
     return q.astype(np.int32), t.astype(np.int32), ms0[q], (m0, m1, ms0, ms1), scores
+
+
+# ---------------------------------------------------------------------- timed CPU baseline of config 5 (bench.py)
+def head_torch_cpu(mdesc0, mdesc1, z0=None, z1=None, th=0.1):
+    """The reference's matcher head as it EXECUTES it -- torch fp32 ops on full M x N matrices -- on the host cores:
+    sim = einsum (lightglue.py:223); with logits: log double soft-max incl. the dust-bin border (:196-208) and
+    filter_matches (:235-254); without: filter_matches' arg-max / mutual / threshold steps on the raw similarity.
+    Restated here (the reference package cannot be imported on the GPU box); bench.py times it beside the GPU
+    float path. Inputs: float32 torch tensors [M, D], [N, D], logits [M], [N]. -> (m0 [M], mscores0 [M])."""
+    import torch
+    import torch.nn.functional as F
+    sim = torch.einsum("md,nd->mn", mdesc0, mdesc1)
+    if z0 is not None:
+        m, n = sim.shape
+        border = sim.new_zeros((m + 1, n + 1))
+        border[:m, :n] = (F.log_softmax(sim, 1) + F.log_softmax(sim.t().contiguous(), 1).t()
+                          + F.logsigmoid(z0)[:, None] + F.logsigmoid(z1)[None, :])
+        border[:m, n] = F.logsigmoid(-z0)
+        border[m, :n] = F.logsigmoid(-z1)
+        core = border[:m, :n]
+        best0, best1 = core.max(1), core.max(0)
+        val0 = best0.values.exp()
+    else:
+        best0, best1 = sim.max(1), sim.max(0)
+        val0 = best0.values
+    a0, a1 = best0.indices, best1.indices
+    mutual0 = torch.arange(a0.numel()) == a1[a0]
+    ms0 = torch.where(mutual0, val0, val0.new_zeros(()))
+    valid0 = mutual0 & (ms0 > th) if th is not None else mutual0
+    return torch.where(valid0, a0, torch.full_like(a0, -1)), ms0

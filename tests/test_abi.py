@@ -23,7 +23,7 @@ def test_library_exports_every_declared_symbol(pkg):
     dll = ctypes.CDLL(pkg.LIB_PATH)
     for s in syms:
         assert hasattr(dll, s), s
-    assert dll.b200m_version() == 110
+    assert dll.b200m_version() == 120
 
 
 def test_options_roundtrip(pkg):

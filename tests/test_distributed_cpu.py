@@ -98,3 +98,94 @@ def test_two_rank_window_shard_with_halo(tmp_path, pkg):
             assert int(w["k"][la]) == int(full["kpi"][ga])
         gps.append(w["gp"].numpy())
     assert np.array_equal(np.concatenate(gps), pkg.window_pairs(9, 3))
+
+
+class _FakeBank:
+    """CPU stand-in with the table layout of DescriptorBank (bank.table_sections): the all-gather of image slices
+    is host logic + collectives and runs under gloo; the kernels that fill a slice need a GPU."""
+
+    def __init__(self, n_img, ks):
+        bank_mod = importlib.import_module("3d_reconstruction_b200.bank")
+        self.n_img, self.k_stride = n_img, ks
+        R = n_img * ks
+        self.desc = torch.zeros((n_img, ks, 128), dtype=torch.uint8)
+        self.sqnorm = torch.zeros((R + R // 32,), dtype=torch.int32)
+        self.sorted_desc = torch.zeros_like(self.desc)
+        self.sort_table = torch.zeros((3 * R + R // 32 + 2 * ((n_img + 3) & ~3),), dtype=torch.int32)
+        self.table_sections = lambda: bank_mod.DescriptorBank.table_sections(self)
+
+
+def _fill(bank, lo, hi, seed):
+    """Deterministic stand-in for prepare_range: every section of the images [lo, hi) gets values that depend on
+    (section, image, offset) only."""
+    for s, (t, per) in enumerate(bank.table_sections()):
+        for img in range(lo, hi):
+            g = torch.Generator().manual_seed(seed * 1000 + s * 100 + img)
+            t[img * per:(img + 1) * per] = torch.randint(0, 200, (per,), generator=g).to(t.dtype)
+
+
+def _worker_sharded(rank, world, port, out_dir):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    dmod = importlib.import_module("3d_reconstruction_b200.distributed")
+    sched = importlib.import_module("3d_reconstruction_b200.scheduler")
+    n_img = 5
+    n_loc, n_pad = dmod.image_slices(n_img, world)
+    bank = _FakeBank(n_pad, 256)
+    _fill(bank, rank * n_loc, (rank + 1) * n_loc, seed=7)
+    dmod.allgather_bank(bank, n_loc)
+    torch.save([t.clone() for t, _ in bank.table_sections()], os.path.join(out_dir, f"bank{rank}.pt"))
+    # packed gather of variable-length lists: rank r's pairs produce (global pair index % 5) + 1 matches each
+    pairs = sched.exhaustive_pairs(n_img)
+    mine, idx = sched.partition(pairs, world, rank)
+    n_pairs_of = [len(sched.partition(pairs, world, r)[1]) for r in range(world)]
+    counts = torch.tensor([(int(i) % 5) + 1 for i in idx], dtype=torch.int32)
+    q = torch.cat([torch.arange(c, dtype=torch.int32) + 100 * int(i) for c, i in zip(counts.tolist(), idx)])
+    d = q.to(torch.float32) * 0.5
+    got = dmod.gather_packed(counts, [q, q + 1, d], n_pairs_of)
+    if rank == 0:
+        off, (gq, gt, gd) = got
+        torch.save({"off": off, "q": gq, "t": gt, "d": gd}, os.path.join(out_dir, "gathered.pt"))
+    else:
+        assert got is None
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_two_rank_bank_allgather_and_packed_gather(tmp_path, pkg):
+    """The sharded host-buffer path (distributed.match_pairs_host) minus the kernels: every rank fills the table
+    sections of ITS image slice, the in-place all-gather leaves the whole bank on every rank; the packed gather
+    returns exactly the single-process flat lists."""
+    mp.spawn(_worker_sharded, args=(2, _free_port(), str(tmp_path)), nprocs=2, join=True)
+    n_img = 5
+    whole = _FakeBank(6, 256)
+    _fill(whole, 0, 6, seed=7)
+    exp = [t for t, _ in whole.table_sections()]
+    for r in range(2):
+        got = torch.load(str(tmp_path / f"bank{r}.pt"))
+        assert len(got) == len(exp) == 10
+        for g, e in zip(got, exp):
+            assert torch.equal(g, e)
+    res = torch.load(str(tmp_path / "gathered.pt"))
+    n_pairs = n_img * (n_img - 1) // 2
+    counts = [(i % 5) + 1 for i in range(n_pairs)]
+    assert res["off"].tolist() == np.concatenate([[0], np.cumsum(counts)]).tolist()
+    eq = torch.cat([torch.arange(c, dtype=torch.int32) + 100 * i for i, c in enumerate(counts)])
+    assert torch.equal(res["q"], eq) and torch.equal(res["t"], eq + 1) and torch.equal(res["d"], eq.float() * 0.5)
+
+
+def test_upload_segments_follow_the_pair_order(pkg):
+    m = importlib.import_module("3d_reconstruction_b200.matcher")
+    pairs = pkg.blocked_order(pkg.exhaustive_pairs(70), 16)
+    segs = m.upload_segments(pairs, 70, 16)
+    assert [s[0] for s in segs] == [0, 1, 2, 3, 4]                       # blocks become necessary one after the other
+    assert segs[0][1] == 0 and segs[-1][2] == len(pairs)
+    for (need, a, b), nxt in zip(segs, segs[1:] + [None]):
+        assert b > a and pairs[a:b].max() // 16 <= need
+        if nxt:
+            assert nxt[1] == b
+    row_major = pkg.exhaustive_pairs(70)                                   # (0, 69) comes early: one big late segment
+    segs = m.upload_segments(row_major, 70, 16)
+    assert segs[-1][0] == 4 and segs[-1][2] == len(row_major) and sum(b - a for _, a, b in segs) == len(row_major)
+    assert m.upload_segments(np.zeros((0, 2), np.int64), 70, 16) == []
