@@ -286,13 +286,20 @@ int launch_any(const CUtensorMap& tmap_a, const CUtensorMap& tmap_a2, const CUte
 
 constexpr int64_t kDefaultBatchRows = int64_t(1) << 22;   // pairs * k_stride per internal batch
 
-int64_t batch_pairs(int64_t k_stride, int64_t n_pairs) {
+// Largest internal batch a call over n_pairs pairs may use: what the workspace is sized and carved for.
+int64_t batch_cap(int64_t k_stride, int64_t n_pairs) {
   const int64_t opt_batch = g_opt.batch;
   int64_t b = opt_batch > 0 ? opt_batch : (kDefaultBatchRows / (k_stride > 0 ? k_stride : 1));
   if (b < 1) b = 1;
   if (b > n_pairs) b = n_pairs;
   if (b < 1) b = 1;
-  // equal batches: 4,112 pairs run as 17 x 242 instead of 16 x 256 + a launch sequence carrying 16 pairs
+  return b;
+}
+
+// Pairs per internal batch: equal batches under the cap, so 4,112 pairs run as 17 x 242 instead of 16 x 256 + a
+// launch sequence carrying 16 pairs. (The workspace of a longer list is large enough for any shorter one.)
+int64_t batch_pairs(int64_t k_stride, int64_t n_pairs) {
+  int64_t b = batch_cap(k_stride, n_pairs);
   const int64_t n_batches = (n_pairs + b - 1) / b;
   if (n_batches > 1) b = (n_pairs + n_batches - 1) / n_batches;
   return b;
@@ -645,7 +652,7 @@ int b200m_bank_sort_u8(const uint8_t* bank, const int32_t* norm_table, const int
 
 size_t b200m_workspace_bytes(int64_t k_stride, int64_t n_pairs) {
   if (k_stride <= 0 || n_pairs <= 0) return 256;
-  return carve(nullptr, nullptr, batch_pairs(k_stride, n_pairs), k_stride);
+  return carve(nullptr, nullptr, batch_cap(k_stride, n_pairs), k_stride);
 }
 
 int b200m_knn2_u8(const uint8_t* bank, const int32_t* norm_table, const int32_t* k_per_image, int32_t n_img,
@@ -830,7 +837,7 @@ int b200m_match_pairs_u8(const uint8_t* bank, const int32_t* norm_table, const u
 
 size_t b200m_workspace_bytes_bf16(int64_t k_stride, int64_t n_pairs) {
   if (k_stride <= 0 || n_pairs <= 0) return 256;
-  return static_cast<size_t>(2) * batch_pairs(k_stride, n_pairs) * k_stride * sizeof(float2) + 512;
+  return static_cast<size_t>(2) * batch_cap(k_stride, n_pairs) * k_stride * sizeof(float2) + 512;
 }
 
 int b200m_match_pairs_bf16(const void* bank_bf16, const int32_t* k_per_image, int32_t n_img, int64_t k_stride,
@@ -884,7 +891,7 @@ int b200m_match_pairs_bf16(const void* bank_bf16, const int32_t* k_per_image, in
 
 size_t b200m_workspace_bytes_assign(int64_t k_stride, int64_t n_pairs) {
   if (k_stride <= 0 || n_pairs <= 0) return 256;
-  return static_cast<size_t>(2) * batch_pairs(k_stride, n_pairs) * k_stride * (sizeof(float2) + sizeof(float)) + 1024;
+  return static_cast<size_t>(2) * batch_cap(k_stride, n_pairs) * k_stride * (sizeof(float2) + sizeof(float)) + 1024;
 }
 
 int b200m_assign_pairs_bf16(const void* mdesc_bf16, const float* matchability, const int32_t* k_per_image,
