@@ -24,6 +24,7 @@
 #include "match_refine.cuh"
 #include "match_sort.cuh"
 #include "match_float.cuh"
+#include "match_float2.cuh"
 #include "match_vq.cuh"
 #include "match_ransac.cuh"
 
@@ -44,6 +45,9 @@ struct Options {
   // 1 = top-1 sweep + ratio/mutual verify sweeps, 0 = top-2 sweep + mutual verify
   std::atomic<int64_t> pipeline{2};
   std::atomic<int64_t> chunk{64};     // columns per chunk of the chunk sweep (64 needs kernel 5, else 32 is used)
+  // float path: 0 = one sweep per pair with the column maximum fused into it (match_float2.cuh, default),
+  // 1 = one sweep per direction (match_float.cuh; resolves exact ties between different rows like the reference)
+  std::atomic<int64_t> float_sweep{0};
 } g_opt;
 
 // Optional per-launch timing of the sweeps with CUDA events on the launching stream ("profile" option).
@@ -482,6 +486,57 @@ int launch_ip_sweep(const CUtensorMap& tmap, const b200m::ip::IpParams& ip, int 
   return B200M_OK;
 }
 
+template <int kDim, int kMode>
+int launch_ip_sweep2(const CUtensorMap& tmap, const b200m::ip::Ip2Params& ip, int grid, cudaStream_t st) {
+  constexpr size_t smem = sizeof(b200m::ip::Ip2Smem<kDim>) + 1024;
+  CUDA_TRY((ensure_smem_attr(b200m::ip::ip_sweep2_kernel<kDim, kMode>, smem)));
+  {
+    ProfScope ps(&g_prof.first, st);
+    b200m::ip::ip_sweep2_kernel<kDim, kMode><<<grid, b200m::kThreads, smem, st>>>(tmap, ip);
+  }
+  CUDA_TRY(cudaGetLastError());
+  return B200M_OK;
+}
+
+// One batch of the single-sweep float path: (row arg-max, column maxima) sweep + mutual / threshold / packing.
+// ws_rows: float2 [nb * k_stride] row results, followed by int32 column keys and int32 claims of the same length.
+int float_single_sweep_batch(const CUtensorMap& tmap, const int32_t* k_per_image, int32_t n_img, int64_t k_stride, int32_t dim,
+                             const int32_t* pairs_batch, int64_t nb, int64_t batch_cap_rows, float2* ws_rows, const float* nbuf,
+                             float threshold, int use_threshold, int mutual, int32_t* out_q, int32_t* out_t, float* out_s,
+                             int32_t* out_count, int64_t cap, cudaStream_t st) {
+  int32_t* colkey = reinterpret_cast<int32_t*>(ws_rows + batch_cap_rows);
+  int32_t* claim = colkey + batch_cap_rows;
+  CUDA_TRY(cudaMemsetAsync(colkey, 0x80, sizeof(int32_t) * nb * k_stride, st));
+  CUDA_TRY(cudaMemsetAsync(claim, 0x7f, sizeof(int32_t) * nb * k_stride, st));
+  b200m::ip::Ip2Params ip;
+  ip.k_per_image = k_per_image;
+  ip.pairs = pairs_batch;
+  ip.k_stride = k_stride;
+  ip.n_pairs = static_cast<int32_t>(nb);
+  ip.blocks_per_image = static_cast<int32_t>(k_stride / b200m::ip::kRows2);
+  ip.n_img = n_img;
+  ip.rowbest = ws_rows;
+  ip.colkey = colkey;
+  ip.nb = nbuf;
+  const int grid = sweep_grid(nb * ip.blocks_per_image);
+  int rc;
+  if (nbuf)
+    rc = dim == 256 ? launch_ip_sweep2<256, b200m::ip::kIpBiasArgmax>(tmap, ip, grid, st)
+                    : launch_ip_sweep2<128, b200m::ip::kIpBiasArgmax>(tmap, ip, grid, st);
+  else
+    rc = dim == 256 ? launch_ip_sweep2<256, b200m::ip::kIpArgmax>(tmap, ip, grid, st)
+                    : launch_ip_sweep2<128, b200m::ip::kIpArgmax>(tmap, ip, grid, st);
+  if (rc) return rc;
+  {
+    ProfScope ps(&g_prof.emit, st);
+    b200m::ip::ip_finalize2_kernel<1024><<<static_cast<unsigned>(nb), 1024, 0, st>>>(
+        ws_rows, colkey, claim, pairs_batch, k_per_image, n_img, k_stride, threshold, use_threshold, mutual, nbuf ? 1 : 0,
+        out_q, out_t, out_s, out_count, cap);
+  }
+  CUDA_TRY(cudaGetLastError());
+  return B200M_OK;
+}
+
 }  // namespace
 
 extern "C" {
@@ -519,6 +574,11 @@ int b200m_set_option(const char* name, int64_t value) {
     return B200M_OK;
   }
   if (!strcmp(name, "profile")) { g_prof.on = value != 0; return B200M_OK; }
+  if (!strcmp(name, "float_sweep")) {
+    if (value != 0 && value != 1) return fail(B200M_E_BAD_ARG, "float_sweep must be 0 (single sweep) or 1 (one sweep per direction)%s");
+    g_opt.float_sweep = value;
+    return B200M_OK;
+  }
   return fail(B200M_E_BAD_ARG, "unknown option %s", name);
 }
 
@@ -531,6 +591,7 @@ int64_t b200m_get_option(const char* name) {
   if (!strcmp(name, "kernel")) return g_opt.kernel;
   if (!strcmp(name, "chunk")) return g_opt.chunk;
   if (!strcmp(name, "profile")) return g_prof.on ? 1 : 0;
+  if (!strcmp(name, "float_sweep")) return g_opt.float_sweep;
   return -1;
 }
 
@@ -864,6 +925,13 @@ int b200m_match_pairs_bf16(const void* bank_bf16, const int32_t* k_per_image, in
   float2* rowbest = reinterpret_cast<float2*>((reinterpret_cast<uintptr_t>(workspace) + 255) & ~uintptr_t(255));
   for (int64_t p0 = 0; p0 < n_pairs; p0 += B) {
     const int64_t nb = (n_pairs - p0 < B) ? (n_pairs - p0) : B;
+    if (g_opt.float_sweep == 0) {
+      rc = float_single_sweep_batch(tmap, k_per_image, n_img, k_stride, dim, pairs + 2 * p0, nb, B * k_stride, rowbest, nullptr,
+                                    score_threshold, use_threshold, mutual ? 1 : 0, out_query_idx + p0 * cap,
+                                    out_train_idx + p0 * cap, out_score + p0 * cap, out_count + p0, cap, st);
+      if (rc) return rc;
+      continue;
+    }
     b200m::ip::IpParams ip;
     ip.k_per_image = k_per_image;
     ip.pairs = pairs + 2 * p0;
@@ -936,6 +1004,13 @@ int b200m_assign_pairs_bf16(const void* mdesc_bf16, const float* matchability, c
     rc = dim == 256 ? launch_ip_sweep<256, b200m::ip::kIpLse>(tmap, ip, grid, st)
                     : launch_ip_sweep<128, b200m::ip::kIpLse>(tmap, ip, grid, st);
     if (rc) return rc;
+    if (g_opt.float_sweep == 0) {      // pass 2 as ONE sweep per pair: row arg-max and column maxima of the full score
+      rc = float_single_sweep_batch(tmap, k_per_image, n_img, k_stride, dim, pairs + 2 * p0, nb, B * k_stride, rowbest, nbuf,
+                                    filter_threshold, use_threshold, 1, out_query_idx + p0 * cap, out_train_idx + p0 * cap,
+                                    out_score + p0 * cap, out_count + p0, cap, st);
+      if (rc) return rc;
+      continue;
+    }
     rc = dim == 256 ? launch_ip_sweep<256, b200m::ip::kIpBiasArgmax>(tmap, ip, grid, st)
                     : launch_ip_sweep<128, b200m::ip::kIpBiasArgmax>(tmap, ip, grid, st);
     if (rc) return rc;

@@ -219,11 +219,11 @@ def _timed(torch, fn, reps):
     return min(ts), float(np.median(ts))
 
 
-def _int8_line(n_pairs, k, best, med, int8_peak):
+def _int8_line(n_pairs, k, best, med, int8_peak, gpus=1):
     ops = 2.0 * k * k * 128 * n_pairs
     return {"pairs": n_pairs, "pairs_per_s": n_pairs / med, "pairs_per_s_best": n_pairs / best, "ms": 1e3 * med,
-            "tops": ops / med / 1e12, "frac_of_peak": ops / med / 1e12 / int8_peak if int8_peak else None,
-            "frac_of_nominal_4500": ops / med / 1e12 / 4500.0}
+            "tops": ops / med / 1e12, "frac_of_peak": ops / med / 1e12 / (int8_peak * gpus) if int8_peak else None,
+            "frac_of_nominal_4500": ops / med / 1e12 / (4500.0 * gpus)}
 
 
 def secondary_c2(pkg, torch, dev, int8_peak):
@@ -308,7 +308,7 @@ def secondary_c4(pkg, dmod, torch, dist, dev, rank, world, int8_peak):
         dist.all_reduce(agg, op=dist.ReduceOp.SUM)
     t = t.tolist()
     n_pairs = int(sum(n_pairs_of))
-    r = _int8_line(n_pairs, k, t[1] / 1e3, t[1] / 1e3, int8_peak * world if int8_peak else None)
+    r = _int8_line(n_pairs, k, t[1] / 1e3, t[1] / 1e3, int8_peak, world)
     r.update({"gpus": world, "match_ms": t[1], "gather_ms": t[2], "scatter_prepare_sort_ms_first_call": t[0],
               "images_on_rank0": int(ld.shape[0]), "matches_total": int(agg[0]),
               "result_digest": f"{int(agg[1]) & ((1 << 64) - 1):016x}",
@@ -587,7 +587,8 @@ def main():
         e2e_same = bool(res.digest()[1] == result_digest and int(res.offsets[-1]) == matches_total)
         assert e2e_same, "the host-buffer path returned different match lists than the resident-bank path"
     if world > 1:                                     # warm per-phase device times of the sharded path (outside the timed steps)
-        for _ in range(2):
+        for _ in range(3):
+            barrier()                                 # no rank-to-rank skew inside the phase times
             e2e_step(True)
         barrier()
     phases = {k: max_over_ranks(float(np.median(v))) for k, v in sorted(phase_ms.items())}

@@ -18,6 +18,14 @@ from oracle import oracle_float
 pytestmark = pytest.mark.gpu
 
 
+@pytest.fixture(autouse=True, params=[0, 1], ids=["single_sweep", "sweep_per_direction"])
+def float_sweep(pkg, request):
+    """Both float kernels: the single sweep with the fused column maximum (default) and one sweep per direction."""
+    pkg.set_option("float_sweep", request.param)
+    yield request.param
+    pkg.set_option("float_sweep", 0)
+
+
 def bf16_bits_to_f32(x):
     return (x.astype(np.uint16).astype(np.uint32) << 16).view(np.float32)
 

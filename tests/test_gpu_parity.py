@@ -287,3 +287,49 @@ def test_randomised_campaign(pkg):
     mod = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(mod)
     mod.main(rounds=14, seed=123)
+
+
+def test_rowmerge_handoff_stress_one_tile_items(pkg):
+    """100,000 work items of a single column tile each (K = 256 per image): the 16 epilogue warps hand their row
+    states over through the double-buffered `rowmerge` shared-memory slots (parity flips every item) as fast as
+    the kernels can go -- a race there would show as a wrong or missing row. compute-sanitizer is closed on the
+    GPU pool, so: every pipeline (chunk sweep, exact top-1, exact top-2) must produce the same per-pair digests
+    twice in a row, and 400 sampled pairs must equal the integer oracle."""
+    syn = importlib.import_module("3d_reconstruction_b200.synthetic")
+    n_img, k = 448, 256
+    ks = np.full(n_img, k)
+    ks[::7] = 255
+    ks[3::11] = 129
+    ks[5::13] = 128
+    desc, kpi = syn.make_bank_tensor(n_img, k, seed=17, device="cuda", k_per_image=ks.tolist(), p_shared=0.5)
+    bank = pkg.DescriptorBank.from_packed(desc, kpi)
+    rng = np.random.default_rng(0)
+    a = rng.integers(0, n_img, size=100000)
+    pairs = np.stack([a, (a + rng.integers(1, 4, size=a.size)) % n_img], 1).astype(np.int32)   # neighbours share rows
+    pairs_dev = torch.from_numpy(pairs).cuda()
+    digests = {}
+    out = None
+    try:
+        for pl in (2, 1, 0):
+            pkg.set_option("pipeline", pl)
+            for rep in range(2):
+                out = pkg.match_pairs(bank, pairs_dev, cap=256, out=out)
+                out.check_overflow()
+                per, tot = out.flatten().digest()
+                digests.setdefault(pl, []).append((per.clone(), tot))
+    finally:
+        pkg.set_option("pipeline", DEFAULT_PIPELINE)
+    ref = digests[2][0][0]
+    for pl, runs in digests.items():
+        for per, _ in runs:
+            bad = torch.nonzero(per != ref).flatten()
+            assert bad.numel() == 0, f"pipeline {pl}: {bad.numel()} pairs differ, first {pairs[bad[:5].cpu().numpy()].tolist()}"
+    flat = pkg.match_pairs(bank, pairs_dev, cap=256).flatten().cpu()
+    assert int(flat.offsets[-1]) > 100000
+    d = desc.cpu().numpy()
+    for p in rng.choice(len(pairs), size=400, replace=False).tolist():
+        i, j = map(int, pairs[p])
+        eq, et, ed = oracle_int.match(d[i, :ks[i]], d[j, :ks[j]], 0.75, True)
+        q, t, dd = flat.pair(p)
+        assert np.array_equal(q.numpy(), eq) and np.array_equal(t.numpy(), et), p
+        assert np.array_equal(_bits(dd.numpy()), _bits(ed)), p

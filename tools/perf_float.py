@@ -67,7 +67,10 @@ def run_assign(dim, n_img=128, k=2048, n_pairs=4096, reps=5):
 
 
 if __name__ == "__main__":
-    run(256)
-    run(128)
-    run_assign(256)
-    run_assign(128)
+    for mode in (0, 1):
+        pkg.set_option("float_sweep", mode)
+        print(f"float_sweep = {mode} ({'single sweep, fused column maximum' if mode == 0 else 'one sweep per direction'})", flush=True)
+        run(256)
+        run(128)
+        run_assign(256)
+        run_assign(128)
