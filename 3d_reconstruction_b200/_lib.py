@@ -25,6 +25,7 @@ SYMBOLS = (
     "b200m_bank_sort_range_u8",
     "b200m_workspace_bytes",
     "b200m_knn2_u8",
+    "b200m_knn2_sorted_u8",
     "b200m_match_pairs_u8",
     "b200m_workspace_bytes_bf16",
     "b200m_match_pairs_bf16",
@@ -85,6 +86,8 @@ def lib() -> C.CDLL:
     L.b200m_workspace_bytes.argtypes = [i64, i64]
     L.b200m_knn2_u8.restype = C.c_int
     L.b200m_knn2_u8.argtypes = [vp, vp, vp, i32, i64, vp, i64, vp, vp, vp, sz, vp]
+    L.b200m_knn2_sorted_u8.restype = C.c_int
+    L.b200m_knn2_sorted_u8.argtypes = [vp, vp, vp, vp, vp, i32, i64, vp, i64, vp, vp, vp, sz, vp]
     L.b200m_match_pairs_u8.restype = C.c_int
     L.b200m_match_pairs_u8.argtypes = [vp, vp, vp, vp, vp, i32, i64, vp, i64, dbl, C.c_int, vp, vp, vp, vp, i64, vp, sz, vp]
     L.b200m_workspace_bytes_bf16.restype = sz

@@ -22,6 +22,7 @@
 #include "experimental/match_chunk2.cuh"
 #endif
 #include "match_refine.cuh"
+#include "match_knn.cuh"
 #include "match_sort.cuh"
 #include "match_float.cuh"
 #include "match_float2.cuh"
@@ -215,7 +216,7 @@ int launch_sweep(const CUtensorMap& tmap_a, const CUtensorMap& tmap_a2, const CU
                  const b200m::SweepParams& sp, int grid, cudaStream_t st) {
   CUDA_TRY(ensure_smem_attr(b200m::sweep_kernel<kKind>, kSweepSmemBytes));
   {
-    ProfScope ps(kKind == b200m::kVerify ? &g_prof.verify : kKind == b200m::kTop1G ? &g_prof.fallback : &g_prof.first, st);
+    ProfScope ps(kKind == b200m::kVerify ? &g_prof.verify : b200m::is_gathered(kKind) ? &g_prof.fallback : &g_prof.first, st);
     b200m::sweep_kernel<kKind><<<grid, b200m::kThreads, kSweepSmemBytes, st>>>(tmap_a, tmap_a2, tmap_b, sp);
   }
   CUDA_TRY(cudaGetLastError());
@@ -225,7 +226,17 @@ int launch_sweep(const CUtensorMap& tmap_a, const CUtensorMap& tmap_a2, const CU
 constexpr size_t kChunkSmemBytes = sizeof(b200m::ChunkSmem) + 1024;
 constexpr size_t kChunk256SmemBytes = sizeof(b200m::Chunk256Smem) + 1024;
 
-int launch_chunk_sweep(const CUtensorMap& tmap, const b200m::ChunkParams& cp, int grid, int64_t kernel, cudaStream_t st) {
+int launch_chunk_sweep(const CUtensorMap& tmap, const b200m::ChunkParams& cp, int grid, int64_t kernel, cudaStream_t st,
+                       bool top3 = false) {
+  if (top3) {      // knnMatch form: three bounds + two chunks per row (64-column chunks, N = 256 MMAs)
+    CUDA_TRY((ensure_smem_attr(b200m::chunk_sweep256_kernel<false, 64, true>, kChunk256SmemBytes)));
+    {
+      ProfScope ps(&g_prof.first, st);
+      b200m::chunk_sweep256_kernel<false, 64, true><<<grid, b200m::kThreads256, kChunk256SmemBytes, st>>>(tmap, cp);
+    }
+    CUDA_TRY(cudaGetLastError());
+    return B200M_OK;
+  }
   CUDA_TRY(ensure_smem_attr(b200m::chunk_sweep_kernel, kChunkSmemBytes));
   CUDA_TRY(ensure_smem_attr(b200m::chunk_sweep256_kernel<false, 32>, kChunk256SmemBytes));
   CUDA_TRY(ensure_smem_attr(b200m::chunk_sweep256_kernel<false, 64>, kChunk256SmemBytes));
@@ -738,6 +749,90 @@ int b200m_knn2_u8(const uint8_t* bank, const int32_t* norm_table, const int32_t*
     if (rc) return rc;
     dim3 grid(static_cast<unsigned>((k_stride + 255) / 256), static_cast<unsigned>(nb));
     b200m::knn2_finalize_kernel<<<grid, 256, 0, st>>>(w.rowres, pairs + 2 * p0, k_per_image, n_img, k_stride,
+                                                      out_train_idx + 2 * p0 * k_stride, out_dist + 2 * p0 * k_stride);
+    CUDA_TRY(cudaGetLastError());
+    g_prof.launches.fetch_add(1);
+  }
+  return B200M_OK;
+}
+
+int b200m_knn2_sorted_u8(const uint8_t* bank, const int32_t* norm_table, const uint8_t* sorted_bank,
+                         const int32_t* sort_table, const int32_t* k_per_image, int32_t n_img, int64_t k_stride,
+                         const int32_t* pairs, int64_t n_pairs, int32_t* out_train_idx, float* out_dist, void* workspace,
+                         size_t workspace_bytes, void* stream) {
+  int rc = check_common(bank, norm_table, k_per_image, n_img, k_stride, pairs, n_pairs);
+  if (rc) return rc;
+  if (n_pairs == 0) return B200M_OK;
+  if (!sorted_bank || !sort_table) return fail(B200M_E_BAD_ARG, "null sorted_bank / sort_table (use b200m_knn2_u8 without them)%s");
+  if (!out_train_idx || !out_dist || !workspace) return fail(B200M_E_BAD_ARG, "null output / workspace%s");
+  if (workspace_bytes < b200m_workspace_bytes(k_stride, n_pairs)) return fail(B200M_E_WORKSPACE, "workspace too small%s");
+  if (k_stride / b200m::kKnnChunk > b200m::kKnnMaxChunks)      // beyond 262,144 rows per image: the exact sweep
+    return b200m_knn2_u8(bank, norm_table, k_per_image, n_img, k_stride, pairs, n_pairs, out_train_idx, out_dist, workspace,
+                         workspace_bytes, stream);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int64_t B = batch_pairs(k_stride, n_pairs);
+  Workspace w;
+  carve(&w, workspace, B, k_stride);
+  CUtensorMap tmap_bank, tmap_sbank, tmap_gq;
+  rc = make_row_tmap(&tmap_bank, bank, static_cast<uint64_t>(n_img) * k_stride);
+  if (rc) return rc;
+  rc = make_row_tmap(&tmap_sbank, sorted_bank, static_cast<uint64_t>(n_img) * k_stride);
+  if (rc) return rc;
+  rc = make_row_tmap(&tmap_gq, w.gath_q, static_cast<uint64_t>(B) * k_stride);
+  if (rc) return rc;
+  const SortTable tv = sort_table_view(sort_table, n_img, k_stride);
+  const int64_t R = B * k_stride;
+  for (int64_t p0 = 0; p0 < n_pairs; p0 += B) {
+    const int64_t nb = (n_pairs - p0 < B) ? (n_pairs - p0) : B;
+    const int32_t* pb = pairs + 2 * p0;
+    b200m::ChunkParams cp;
+    cp.cmin = tv.cmin;
+    cp.k_per_image = k_per_image;
+    cp.pairs = pb;
+    cp.k_stride = k_stride;
+    cp.n_pairs = static_cast<int32_t>(nb);
+    cp.blocks_per_pair = static_cast<int32_t>(k_stride / b200m::kRows);
+    cp.n_img = n_img;
+    cp.rowres = w.rowres;
+    cp.peak = 0;
+    cp.chunk_cols = 64;
+    rc = launch_chunk_sweep(tmap_sbank, cp, sweep_grid(nb * cp.blocks_per_pair), 5, st, true);
+    if (rc) return rc;
+    CUDA_TRY(cudaMemsetAsync(w.fb_count, 0, sizeof(int32_t) * (B + 64), st));
+    b200m::KnnParams kp;
+    kp.bank = bank;
+    kp.sbank = sorted_bank;
+    kp.perm = tv.perm;
+    kp.snorm = tv.snorm;
+    kp.k_per_image = k_per_image;
+    kp.pairs = pb;
+    kp.k_stride = k_stride;
+    kp.n_img = n_img;
+    kp.n_chunks = static_cast<int32_t>(k_stride / b200m::kKnnChunk);
+    kp.rowres_s = w.rowres;
+    kp.boff = reinterpret_cast<int32_t*>(w.cand_d);                       // nb * (n_chunks + 1) <= R entries
+    kp.tasks = reinterpret_cast<int32_t*>(w.gath_t);                       // 2 R entries
+    kp.taskres = reinterpret_cast<int4*>(w.gath_t + 8 * R);                // 2 R records of 16 bytes (40 R of the buffer's 128 R bytes)
+    kp.rowres_o = w.rowres_o;
+    kp.fb_count = w.fb_count;
+    kp.fb_total = w.fb_count + B;
+    kp.fb_q = w.fb_q;
+    kp.fb_desc = w.gath_q;
+    {
+      ProfScope ps(&g_prof.refine, st);
+      b200m::knn_bucket_kernel<<<static_cast<unsigned>(nb), 1024, 0, st>>>(kp);
+      b200m::knn_eval_kernel<<<dim3(static_cast<unsigned>(kp.n_chunks), static_cast<unsigned>(nb)), b200m::kKnnEvalThreads, 0, st>>>(kp);
+      b200m::knn_combine_kernel<<<dim3(static_cast<unsigned>((k_stride + 255) / 256), static_cast<unsigned>(nb)), 256, 0, st>>>(kp);
+    }
+    CUDA_TRY(cudaGetLastError());
+    g_prof.launches.fetch_add(2);
+    // exact top-2 sweep over the rows the bounds could not settle (an outside column may tie or beat the runner-up)
+    b200m::SweepParams sp = base_params(norm_table, n_img, k_per_image, k_stride, pb, nb, w);
+    sp.fb_total = w.fb_count + B;
+    rc = launch_sweep<b200m::kTop2G>(tmap_gq, tmap_gq, tmap_bank, sp, sweep_grid(nb * sp.blocks_per_pair), st);
+    if (rc) return rc;
+    dim3 grid(static_cast<unsigned>((k_stride + 255) / 256), static_cast<unsigned>(nb));
+    b200m::knn2_finalize_kernel<<<grid, 256, 0, st>>>(w.rowres_o, pb, k_per_image, n_img, k_stride,
                                                       out_train_idx + 2 * p0 * k_stride, out_dist + 2 * p0 * k_stride);
     CUDA_TRY(cudaGetLastError());
     g_prof.launches.fetch_add(1);

@@ -16,6 +16,8 @@
 // Stands in for lightglue/lightglue.py:223 (dense contraction) + :237 (row arg-best) in the
 // exact-integer L2 form named by BASELINE.json (cv2.BFMatcher NORM_L2 knnMatch).
 #pragma once
+#include <type_traits>
+
 #include "match_sweep.cuh"
 
 namespace b200m {
@@ -74,6 +76,33 @@ __device__ __forceinline__ void chunk_update(ChunkState& s, int L, int g) {
   s.L2 = min(s.L2, max(s.L1, L));
   s.g1 = lt ? g : s.g1;
   s.L1 = min(s.L1, L);
+}
+
+// knnMatch form of the chunk state: the THREE smallest chunk bounds of a row and the chunks holding the two
+// smallest -- the exact two nearest neighbours then lie in chunks g1 / g2 whenever the second of them scores
+// below L3 (match_knn.cuh evaluates the two chunks exactly, the rest falls back to the exact top-2 sweep).
+struct ChunkState3 {
+  int L1, g1, L2, g2, L3;
+};
+__device__ __forceinline__ void chunk_update(ChunkState3& s, int L, int g) {
+  const bool c1 = L < s.L1, c2 = L < s.L2;
+  s.L3 = min(s.L3, max(s.L2, L));
+  s.g2 = c1 ? s.g1 : (c2 ? g : s.g2);
+  s.L2 = min(s.L2, max(s.L1, L));
+  s.g1 = c1 ? g : s.g1;
+  s.L1 = min(s.L1, L);
+}
+__device__ __forceinline__ void chunk_init(ChunkState& s) { s.L1 = kBig; s.g1 = 0; s.L2 = kBig; }
+__device__ __forceinline__ void chunk_init(ChunkState3& s) { s.L1 = kBig; s.g1 = 0; s.L2 = kBig; s.g2 = 0; s.L3 = kBig; }
+// row states travel as int4: (L1, g1, L2, 0) / (L1, g1 | g2 << 16, L2, L3)
+__device__ __forceinline__ int4 chunk_pack(const ChunkState& s) { return make_int4(s.L1, s.g1, s.L2, 0); }
+__device__ __forceinline__ int4 chunk_pack(const ChunkState3& s) { return make_int4(s.L1, s.g1 | (s.g2 << 16), s.L2, s.L3); }
+// merge the state another column quarter handed over (chunks of the quarters interleave tile by tile: order on (L, g))
+__device__ __forceinline__ void chunk_merge(ChunkState& st, const int4 q);
+__device__ __forceinline__ void chunk_merge(ChunkState3& st, const int4 q) {
+  chunk_update(st, q.x, q.y & 0xffff);
+  chunk_update(st, q.z, q.y >> 16);
+  chunk_update(st, q.w, 0);          // third bound of the other quarter: can only land in L3 (q.w >= q.z >= q.x)
 }
 
 __global__ void __launch_bounds__(kThreads, 1)
@@ -288,8 +317,15 @@ constexpr int kThreads256 = kThreads;
 // (Measured alternatives, all slower: pulling all 64 columns first and releasing the accumulator before
 // the max trees, -17 %; two loads of 32 columns through two 32-register buffers, -5..9 %; issuing the first
 // load of the NEXT accumulator before the last max tree of this one, -6 %.)
-template <bool kPeakOnly, int kChunkCols>
-__device__ __forceinline__ void drain64(uint32_t taddr, int cm0, int cm1, int g, ChunkState& st, uint64_t* t_empty,
+__device__ __forceinline__ void chunk_merge(ChunkState& st, const int4 q) {
+  const bool other = lex_less(q.x, q.y, st.L1, st.g1);
+  st.L2 = min(min(q.z, st.L2), other ? st.L1 : q.x);
+  st.g1 = other ? q.y : st.g1;
+  st.L1 = other ? q.x : st.L1;
+}
+
+template <bool kPeakOnly, int kChunkCols, class State>
+__device__ __forceinline__ void drain64(uint32_t taddr, int cm0, int cm1, int g, State& st, uint64_t* t_empty,
                                         uint32_t lane) {
   int va[16], vb[16];
   tmem_ld_32x16(taddr, va);
@@ -320,9 +356,10 @@ __device__ __forceinline__ void drain64(uint32_t taddr, int cm0, int cm1, int g,
   else chunk_update(st, cm0 - 2 * m3, g);       // sorted norms: the 64-column chunk's minimum is its first
 }
 
-template <bool kPeakOnly, int kChunkCols>
+template <bool kPeakOnly, int kChunkCols, bool kTop3 = false>
 __global__ void __launch_bounds__(kThreads256, 1)
 chunk_sweep256_kernel(const __grid_constant__ CUtensorMap tmap, const ChunkParams p) {
+  using State = typename std::conditional<kTop3, ChunkState3, ChunkState>::type;
   extern __shared__ uint8_t smem_raw[];
   Chunk256Smem& sm = *reinterpret_cast<Chunk256Smem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
 
@@ -430,9 +467,9 @@ chunk_sweep256_kernel(const __grid_constant__ CUtensorMap tmap, const ChunkParam
       if (!decode(item, pair, blk, row0, col_img, n_rows, ntiles, nm)) continue;
       const uint32_t par = item_it & 1;
       ++item_it;
-      ChunkState s0, s1;
-      s0.L1 = kBig; s0.g1 = 0; s0.L2 = kBig;
-      s1 = s0;
+      State s0, s1;
+      chunk_init(s0);
+      chunk_init(s1);
       const int2* cm = reinterpret_cast<const int2*>(p.cmin + (static_cast<int64_t>(col_img) * p.k_stride) / kChunk) + cq;
       int2 cm_next = __ldg(cm);
       for (int t = 0; t < ntiles; ++t) {
@@ -442,18 +479,18 @@ chunk_sweep256_kernel(const __grid_constant__ CUtensorMap tmap, const ChunkParam
         mbar_wait(&sm.t_full[0], t_it0 & 1);
         tc_fence_after();
         ++t_it0;
-        drain64<kPeakOnly, kChunkCols>(taddr0, c2.x, c2.y, g, s0, &sm.t_empty[0], lane);
+        drain64<kPeakOnly, kChunkCols, State>(taddr0, c2.x, c2.y, g, s0, &sm.t_empty[0], lane);
         if (nm > 1) {
           mbar_wait(&sm.t_full[1], t_it1 & 1);
           tc_fence_after();
           ++t_it1;
-          drain64<kPeakOnly, kChunkCols>(taddr0 + kTT, c2.x, c2.y, g, s1, &sm.t_empty[1], lane);
+          drain64<kPeakOnly, kChunkCols, State>(taddr0 + kTT, c2.x, c2.y, g, s1, &sm.t_empty[1], lane);
         }
       }
       // the four column quarters of a row meet here: quarters 1..3 -> smem -> quarter 0 -> global
       if (cq > 0) {
-        sm.rowmerge[par][cq - 1][rl] = make_int4(s0.L1, s0.g1, s0.L2, 0);
-        sm.rowmerge[par][cq - 1][kTM + rl] = make_int4(s1.L1, s1.g1, s1.L2, 0);
+        sm.rowmerge[par][cq - 1][rl] = chunk_pack(s0);
+        sm.rowmerge[par][cq - 1][kTM + rl] = chunk_pack(s1);
       }
       named_bar_sync(kEpiBarrier, kEpiWarps * 32);
       if (cq == 0) {
@@ -461,17 +498,10 @@ chunk_sweep256_kernel(const __grid_constant__ CUtensorMap tmap, const ChunkParam
         for (int m = 0; m < 2; ++m) {
           const int row = m * kTM + rl;
           if (row >= n_rows) continue;
-          ChunkState st = m == 0 ? s0 : s1;
+          State st = m == 0 ? s0 : s1;
 #pragma unroll
-          for (int o = 0; o < 3; ++o) {
-            const int4 q = sm.rowmerge[par][o][row];
-            // chunks of the quarters interleave tile by tile: order the pair (L, g) explicitly
-            const bool other = lex_less(q.x, q.y, st.L1, st.g1);
-            st.L2 = min(min(q.z, st.L2), other ? st.L1 : q.x);
-            st.g1 = other ? q.y : st.g1;
-            st.L1 = other ? q.x : st.L1;
-          }
-          p.rowres[static_cast<int64_t>(pair) * p.k_stride + blk * kRows + row] = make_int4(st.L1, st.g1, st.L2, 0);
+          for (int o = 0; o < 3; ++o) chunk_merge(st, sm.rowmerge[par][o][row]);
+          p.rowres[static_cast<int64_t>(pair) * p.k_stride + blk * kRows + row] = chunk_pack(st);
         }
       }
     }

@@ -42,6 +42,7 @@ struct Ip2Smem {
   uint8_t a[kAStages][kNKB][2][kBlockBytes];                  // [stage][K-block][M-tile]
   uint8_t b[kBStages2][kBlockBytes];
   float2 rowmerge[2][3][kRows2];                              // (value, column as int bits) of epilogue sets 1..3
+  int colx[kEpiWarps][2][32];                                 // per warp: column maxima of a 32-column group (warp-uniform -> one per lane)
   uint64_t a_full[kAStages][kNKB], a_empty[kAStages][kNKB];
   uint64_t b_full[kBStages2], b_empty[kBStages2];
   uint64_t t_full[2], t_empty[2];                             // accumulator pair of a tile parity
@@ -232,7 +233,7 @@ ip_sweep2_kernel(const __grid_constant__ CUtensorMap tmap, const Ip2Params p) {
         if (ok1) own1 = __ldg(p.nb + obase + blk * kRows2 + r1);
       }
       int32_t* colkey = p.colkey + obase;
-      int ckey = kColKeyNone;                            // this lane's column of the current 32-column group
+      int (*cx)[32] = sm.colx[warp - kFirstEpiWarp];
 
       for (int t = static_cast<int>((tp + 2 - (t_seen & 1)) & 1); t < ntiles; t += 2) {
         mbar_wait(&sm.t_full[tp], my_it & 1);
@@ -280,16 +281,19 @@ ip_sweep2_kernel(const __grid_constant__ CUtensorMap tmap, const Ip2Params p) {
           ip_process8(va + 8, c0 + 8, best0, bidx0, keep0);
           ip_process8(vb, c0, best1, bidx1, keep1);
           ip_process8(vb + 8, c0 + 8, best1, bidx1, keep1);
-          // columns: max over this thread's two rows, then over the warp's 32 lanes; lane (16 (s & 1) + j) keeps column j
+          // columns: max over this thread's two rows, then over the warp's 32 lanes (REDUX: the result is warp-uniform).
+          // Lane 0 parks the 32 maxima of a column group in shared memory (a store on the idle LSU pipe instead of a
+          // compare + select per column on the busy ALU pipe), then every lane picks up one column for the atomic.
 #pragma unroll
           for (int j = 0; j < 16; ++j) {
             const int key = ordered_key(fmaxf(__int_as_float(va[j]), __int_as_float(vb[j])));
             const int m = __reduce_max_sync(0xffffffffu, key);
-            if (lane == static_cast<uint32_t>((s & 1) * 16 + j)) ckey = m;
+            if (lane == 0) cx[s >> 1][(s & 1) * 16 + j] = m;
           }
           if (s & 1) {
+            __syncwarp();
             const int col = t * kColsF + h * 64 + (s >> 1) * 32 + static_cast<int>(lane);
-            if (col < n_cols) atomicMax(colkey + col, ckey);
+            if (col < n_cols) atomicMax(colkey + col, cx[s >> 1][lane]);
           }
         }
       }

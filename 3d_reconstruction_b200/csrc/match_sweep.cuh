@@ -35,6 +35,8 @@
 //                     image: violated when some query is nearer (or equally near, lower index).
 //   kTop1G   kTop1 over GATHERED query rows (the exact fallback of the chunk pipeline): rows come from a
 //            gathered buffer, results go to the rows' original slots in (d1^2, i1, d2^2 bound, state) form.
+//   kTop2G   kTop2 over gathered query rows (the exact fallback of the chunk-based knnMatch, match_knn.cuh):
+//            results go to the rows' original slots in (d1^2, i1, d2^2, i2) form.
 //   kTop2Exact / kPeak  debugging (every element through the insertion) and MMA-only ceiling.
 #pragma once
 #include "match_common.cuh"
@@ -59,9 +61,11 @@ constexpr int kPadNorm = 1 << 23;   // > 128*255^2: norm of a padding row
 constexpr int kBig = 1 << 28;       // "no candidate yet" score; 2*acc + kBig cannot overflow
 constexpr uint32_t kEpiBarrier = 1; // named barrier of the 16 epilogue warps
 
-enum SweepKind { kTop2 = 0, kVerify = 1, kPeak = 2, kTop2Exact = 3, kTop1 = 4, kTop1G = 5 };
+enum SweepKind { kTop2 = 0, kVerify = 1, kPeak = 2, kTop2Exact = 3, kTop1 = 4, kTop1G = 5, kTop2G = 6 };
 
 __host__ __device__ constexpr bool is_top1(int kind) { return kind == kTop1 || kind == kTop1G; }
+__host__ __device__ constexpr bool is_top2(int kind) { return kind == kTop2 || kind == kTop2G; }
+__host__ __device__ constexpr bool is_gathered(int kind) { return kind == kTop1G || kind == kTop2G; }
 
 struct NormSlot {
   int32_t nb[kTT];      // squared norms of the tile's 256 columns
@@ -152,7 +156,7 @@ __device__ __forceinline__ ItemInfo decode_item(const SweepParams& p, int item) 
     it.n_cols = it.check == 0 ? kt : kq;
     it.col_img = it.check == 0 ? ti : qi;
     it.row_img_row0 = static_cast<int>(it.pair * p.k_stride + it.blk * kRows);   // gathered buffers
-  } else if (kKind == kTop1G) {
+  } else if (is_gathered(kKind)) {
     it.n_rows = __ldg(p.fb_count + it.pair) - it.blk * kRows;
     it.n_cols = kt;
     it.col_img = ti;
@@ -296,7 +300,7 @@ sweep_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
              const __grid_constant__ CUtensorMap tmap_b, const SweepParams p) {
   extern __shared__ uint8_t smem_raw[];
   SweepSmem& sm = *reinterpret_cast<SweepSmem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  if (kKind == kTop1G && __ldg(p.fb_total) == 0) return;   // the usual case: the bounds settled every row
+  if (is_gathered(kKind) && __ldg(p.fb_total) == 0) return;   // the usual case: the bounds settled every row
 
   const uint32_t warp = threadIdx.x >> 5;
   const uint32_t lane = lane_id();
@@ -448,7 +452,7 @@ sweep_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
         mbar_wait(&sm.n_full[ns], nph);
         if (active) {
           const NormSlot& nsl = sm.norms[ns];
-          if (kKind == kTop2 || is_top1(kKind)) {
+          if (is_top2(kKind) || is_top1(kKind)) {
             // Bound from the other column half of this row. kTop2: the union's second best is
             // <= min(max(s1, s1'), s2'); kTop1: the union's best is <= s1'. Anything at or above the
             // bound (strictly above on ties, the halves interleave in column order) cannot matter.
@@ -517,11 +521,12 @@ sweep_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
             r1s = st.s1; r1i = st.i1;
             if (lex_less(o.x, o.y, st.s2, st.i2)) { r2s = o.x; r2i = o.y; } else { r2s = st.s2; r2i = st.i2; }
           }
-          if (kKind == kTop1G) {
+          if (is_gathered(kKind)) {
             const int qi = __ldg(p.pairs + 2 * it.pair);
             const int qrow = __ldg(p.fb_q + orow);
             const int na = __ldg(p.sqnorm + qi * p.k_stride + qrow);
-            p.rowres_o[static_cast<int64_t>(it.pair) * p.k_stride + qrow] = make_int4(r1s + na, r1i, r2s + na, 3);
+            p.rowres_o[static_cast<int64_t>(it.pair) * p.k_stride + qrow] =
+                make_int4(r1s + na, r1i, r2s + na, kKind == kTop2G ? r2i : 3);
           } else {
             const int na = __ldg(p.sqnorm + it.row_img_row0 + rl);
             p.rowres[orow] = make_int4(r1s + na, r1i, r2s + na, r2i);

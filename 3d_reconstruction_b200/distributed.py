@@ -12,7 +12,7 @@ import numpy as np
 import torch
 import torch.distributed as dist
 
-from .scheduler import partition
+from .scheduler import partition, partition_by_owner
 
 
 def is_dist() -> bool:
@@ -149,27 +149,104 @@ def gather_packed(counts: torch.Tensor, fields: list, n_pairs_of: list, dst: int
     return off, out
 
 
+class _SymmBank:
+    """Bank tensors in SYMMETRIC memory (torch.distributed._symmetric_memory: every rank's buffer is mapped into
+    every other rank's address space over NVLink), cached per shape: lets the ranks PULL each other's prepared
+    image slices with plain device-to-device copies on the copy engines -- no SM is taken from the matching
+    kernels that run meanwhile."""
+
+    def __init__(self, n_pad: int, ks: int, dev: torch.device):
+        import torch.distributed._symmetric_memory as symm
+        from . import _lib
+        from .bank import DESC_DIM, DescriptorBank
+        L = _lib.lib()
+        sizes = (n_pad * ks * DESC_DIM, int(L.b200m_norm_table_elems(n_pad, ks)), n_pad * ks * DESC_DIM,
+                 int(L.b200m_sort_table_elems(n_pad, ks)))
+        dtypes = (torch.uint8, torch.int32, torch.uint8, torch.int32)
+        self.tensors = [symm.empty(n, dtype=dt, device=dev) for n, dt in zip(sizes, dtypes)]
+        self.handles = [symm.rendezvous(t, dist.group.WORLD) for t in self.tensors]
+        desc, sqnorm, sdesc, stab = self.tensors
+        stab[3 * n_pad * ks + n_pad * ks // 32:].zero_()
+        kpi = torch.zeros((n_pad,), dtype=torch.int32, device=dev)
+        self.bank = DescriptorBank(desc.view(n_pad, ks, DESC_DIM), kpi, sqnorm, sdesc.view(n_pad, ks, DESC_DIM), stab)
+        self.stream = torch.cuda.Stream(device=dev)
+        # (tensor index, first element, elements per image) of every per-image section, as bank.table_sections() lists them
+        self.sections = []
+        for view, per in self.bank.table_sections():
+            for ti, t in enumerate(self.tensors):
+                if view.untyped_storage().data_ptr() == t.untyped_storage().data_ptr():
+                    self.sections.append((ti, int(view.storage_offset()), per))
+                    break
+        assert len(self.sections) == len(self.bank.table_sections())
+
+    def pull_all(self, n_loc: int) -> None:
+        """On the current stream: device barrier (every rank's slice is prepared), copy every remote slice of every
+        section from its owner's buffer into the same place of the local one, device barrier (nobody overwrites a
+        slice that is still being read)."""
+        rank, ws = world()
+        self.handles[0].barrier()
+        for step in range(1, ws):
+            src = (rank - step) % ws
+            for ti, first, per in self.sections:
+                n = n_loc * per
+                t = self.tensors[ti]
+                t[first + src * n: first + (src + 1) * n].copy_(
+                    self.handles[ti].get_buffer(src, (n,), t.dtype, first + src * n))
+        self.handles[0].barrier()
+
+
+_symm_banks: dict = {}
+
+
+def _symm_bank(n_pad: int, ks: int, dev: torch.device):
+    """Cached symmetric-memory bank, or None when symmetric memory cannot be set up here (then NCCL moves the bank)."""
+    key = (n_pad, ks, dev.index)
+    if key not in _symm_banks:
+        try:
+            _symm_banks[key] = _SymmBank(n_pad, ks, dev)
+        except Exception as ex:      # no P2P mapping between these GPUs, or an older torch: fall back to the NCCL all-gather
+            import warnings
+            warnings.warn(f"symmetric memory unavailable ({type(ex).__name__}: {ex}); using the NCCL all-gather")
+            _symm_banks[key] = None
+    return _symm_banks[key]
+
+
+def transport_in_use() -> str:
+    """What moved the bank between the ranks in the match_pairs_host calls so far: "ce" (copy engines over
+    symmetric memory), "nccl" (in-place all-gathers), or "none"."""
+    if not _symm_banks:
+        return "none"
+    return "ce" if any(v is not None for v in _symm_banks.values()) else "nccl"
+
+
 def match_pairs_host(desc_host_local: torch.Tensor, k_per_image, n_img: int, pairs, ratio: float = 0.75,
                      mutual: bool = True, cap: int | None = None, device="cuda", dst: int = 0, out=None, workspace=None,
-                     staging: bool = False, events: dict | None = None):
+                     staging: bool = False, events: dict | None = None, transport: str = "auto", block: int = 12):
     """matcher.match_pairs_host over all ranks of the job: HOST descriptors in, flat HOST match lists out (on rank
-    `dst`; None elsewhere), the per-pair host -> device -> host unit of matching.py:107-128 sharded and batched.
+    `dst`, in the order of `pairs`; None elsewhere) -- the per-pair host -> device -> host unit of
+    matching.py:107-128, sharded and batched.
 
     desc_host_local: this rank's slice of the host bank, uint8 [<= n_loc, k_stride, 128] = images
-    [rank * n_loc, ...) with n_loc = ceil(n_img / world) (image_slices) -- each process holds the descriptors of the
-    images it extracted or loaded, and uploads only those over its own PCIe link. k_per_image: all n_img counts
-    (tiny, known everywhere). pairs: the WHOLE pair list, identical on every rank. Steps: local upload -> norms +
-    norm sort of the local slice -> in-place all-gather of bank + tables over NVLink -> this rank's static,
-    cost-balanced slice of the pairs (scheduler.partition) -> one packed gather to `dst` -> pinned D2H.
-    With one rank this is matcher.match_pairs_host (chunked upload overlapped with the matching).
-    events: optional dict, filled with (start, stop) CUDA events of the phases "upload_prepare", "allgather",
-    "match", "gather" on the current stream (bench.py reports the warm collective times from them)."""
+    [rank * n_loc, ...) with n_loc = ceil(n_img / world) (image_slices): each process holds the descriptors of the
+    images it extracted or loaded and uploads only those, over its own PCIe link. k_per_image: all n_img counts
+    (tiny, known everywhere). pairs: the WHOLE pair list, identical on every rank.
+      1. own images host -> device in blocks of `block` images on a copy stream, norms + norm sort per block;
+      2. every pair belongs to the owner of one of its images (scheduler.partition_by_owner); the pairs between
+         a rank's OWN images are matched first, block by block as the upload lands,
+      3. while the ranks pull each other's prepared slices (bank, norm-sorted bank, tables) over NVLink with the
+         copy engines (symmetric memory; transport="nccl" or a failed set-up: one in-place NCCL all-gather per
+         section instead, which cannot overlap the persistent matching kernels);
+      4. the remaining pairs, one packed gather to `dst`, results put back into list order, pinned D2H.
+    With one rank this is matcher.match_pairs_host. events: optional dict, filled with (start, stop) CUDA events of
+    the phases "upload_prepare", "exchange", "match_local", "match_rest", "gather" (bench.py reports them)."""
     from . import matcher as M
     from .bank import DescriptorBank
     rank, ws = world()
     if ws == 1:
         return M.match_pairs_host(desc_host_local, k_per_image, pairs, ratio, mutual, cap, device, out=out,
                                   workspace=workspace, staging=staging)
+    if transport not in ("auto", "ce", "nccl"):
+        raise ValueError("transport must be 'auto', 'ce' (copy engines over symmetric memory) or 'nccl'")
     dev = torch.device(device)
     ks = int(desc_host_local.shape[1])
     n_loc, n_pad = image_slices(n_img, ws)
@@ -180,38 +257,108 @@ def match_pairs_host(desc_host_local: torch.Tensor, k_per_image, n_img: int, pai
     kpi = np.zeros(n_pad, np.int32)
     kpi[:n_img] = np.asarray(k_per_image, dtype=np.int32)
     pairs_np = np.ascontiguousarray(np.asarray(pairs, dtype=np.int32).reshape(-1, 2))
+    if pairs_np.size and (pairs_np.min() < 0 or pairs_np.max() >= n_img):
+        raise ValueError(f"pairs must index images in [0, {n_img})")
     cap = ks if cap is None else int(cap)
-    def mark(name, which):
+
+    def mark(name, which, stream=None):
         if events is not None:
             ev = torch.cuda.Event(enable_timing=True)
-            ev.record()
+            ev.record(stream) if stream is not None else ev.record()
             events.setdefault(name, [None, None])[which] = ev
 
     with torch.cuda.device(dev):
-        mark("upload_prepare", 0)
-        bank = DescriptorBank.allocate(n_pad, ks, torch.from_numpy(kpi), dev)
-        if have:
-            bank.desc[lo:lo + have].copy_(desc_host_local, non_blocking=True)
-        bank.prepare_range(lo, n_loc)
-        mark("upload_prepare", 1)
-        mark("allgather", 0)
-        allgather_bank(bank, n_loc)
-        mark("allgather", 1)
-        mine, idx = partition(pairs_np, ws, rank, kpi[:n_img])
-        n_pairs_of = [len(partition(pairs_np, ws, r, kpi[:n_img])[1]) for r in range(ws)]
+        main = torch.cuda.current_stream()
+        symm = _symm_bank(n_pad, ks, dev) if transport in ("auto", "ce") else None
+        if transport == "nccl":
+            _symm_banks.setdefault(("nccl", ks, dev.index), None)
+        if symm is None and transport == "ce":
+            raise RuntimeError("symmetric memory could not be set up on this machine (transport='ce')")
+        if symm is not None:
+            bank = symm.bank
+            bank.k_per_image.copy_(torch.from_numpy(kpi), non_blocking=True)
+        else:
+            bank = DescriptorBank.allocate(n_pad, ks, torch.from_numpy(kpi), dev)
+        parts = [partition_by_owner(pairs_np, ws, r, n_loc) for r in range(ws)]
+        mine, idx, n_local = parts[rank]
+        P = len(mine)
         pd = torch.from_numpy(np.ascontiguousarray(mine)).to(dev, non_blocking=True)
-        mark("match", 0)
-        res = M.match_pairs(bank, pd, ratio=ratio, mutual=mutual, cap=cap, out=out, workspace=workspace)
-        flat = res.flatten()
-        mark("match", 1)
+        if out is None:
+            out = M._new_out(P, cap, dev)
+        else:
+            M._check_out(out, P)
+        ws_t = workspace if workspace is not None else M._workspace(bank, max(P, 1))
+        # 1 + 2: chunked upload of the own images, local pairs as their images land
+        mark("upload_prepare", 0)
+        copy = M._copy_stream(dev)
+        copy.wait_stream(main)
+        n_blocks = (n_loc + block - 1) // block
+        landed = []
+        with torch.cuda.stream(copy):
+            for b in range(n_blocks):
+                b0, b1 = b * block, min(have, (b + 1) * block)
+                if b1 > b0:
+                    bank.desc[lo + b0: lo + b1].copy_(desc_host_local[b0:b1], non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(copy)
+                landed.append(ev)
+        segs = M.upload_segments(mine[:n_local] - lo, n_loc, block) if symm is not None else []
+        todo = []                                           # local segments whose images are resident, not launched yet
+        for b in range(n_blocks):
+            main.wait_event(landed[b])
+            bank.prepare_range(lo + b * block, min(n_loc, (b + 1) * block) - b * block)
+            todo += [s for s in segs if s[0] == b]
+        mark("upload_prepare", 1)
+        prepared = torch.cuda.Event()
+        prepared.record(main)
+        # 3: the exchange, on its own stream when the copy engines do it
+        if symm is not None:
+            symm.stream.wait_event(prepared)
+            with torch.cuda.stream(symm.stream):
+                mark("exchange", 0, symm.stream)
+                symm.pull_all(n_loc)
+                mark("exchange", 1, symm.stream)
+                exchanged = torch.cuda.Event()
+                exchanged.record(symm.stream)
+            mark("match_local", 0)
+            for _, p0, p1 in todo:
+                M.match_pairs(bank, pd[p0:p1], ratio=ratio, mutual=mutual, cap=cap, out=M._out_rows(out, p0, p1), workspace=ws_t)
+            mark("match_local", 1)
+            main.wait_event(exchanged)
+            rest0 = n_local
+        else:
+            mark("exchange", 0)
+            allgather_bank(bank, n_loc)
+            mark("exchange", 1)
+            rest0 = 0
+        # 4: everything else
+        mark("match_rest", 0)
+        if P > rest0:
+            M.match_pairs(bank, pd[rest0:], ratio=ratio, mutual=mutual, cap=cap, out=M._out_rows(out, rest0, P), workspace=ws_t)
+        flat = out.flatten()
+        mark("match_rest", 1)
         counts = (flat.offsets[1:] - flat.offsets[:-1]).to(torch.int32)
         mark("gather", 0)
-        got = gather_packed(counts, [flat.query_idx, flat.train_idx, flat.dist], n_pairs_of, dst)
-        mark("gather", 1)
+        got = gather_packed(counts, [flat.query_idx, flat.train_idx, flat.dist], [len(pp[1]) for pp in parts], dst)
         if got is None:
+            mark("gather", 1)
             return None
-        off, (fq, ft, fd) = got
-        return M.FlatMatches(fq, ft, fd, off).cpu(staging)
+        off, fields = got
+        # rank-ordered concatenation -> the order of `pairs`
+        order = torch.from_numpy(np.concatenate([pp[1] for pp in parts])).to(dev)           # gathered position -> list index
+        cnt = off[1:] - off[:-1]
+        cnt_list = torch.empty_like(cnt)
+        cnt_list[order] = cnt
+        off_list = torch.zeros_like(off)
+        torch.cumsum(cnt_list, 0, out=off_list[1:])
+        dest = torch.repeat_interleave(off_list[:-1][order] - off[:-1], cnt) + torch.arange(int(off[-1]), device=dev)
+        outs = []
+        for f in fields:
+            g = torch.empty_like(f)
+            g[dest] = f
+            outs.append(g)
+        mark("gather", 1)
+        return M.FlatMatches(outs[0], outs[1], outs[2], off_list).cpu(staging)
 
 
 def scatter_bank_window(desc: torch.Tensor | None, k_per_image: torch.Tensor | None, n_img: int, k_stride: int, dim: int,

@@ -271,9 +271,16 @@ def knn2_pairs(bank: DescriptorBank, pairs, workspace: torch.Tensor | None = Non
     ws = workspace if workspace is not None else _workspace(bank, P)
     with torch.cuda.device(bank.device):
         st = torch.cuda.current_stream().cuda_stream
-        _lib.check(_lib.lib().b200m_knn2_u8(
-            bank.desc.data_ptr(), bank.sqnorm.data_ptr(), bank.k_per_image.data_ptr(), bank.n_img, bank.k_stride,
-            pairs_t.data_ptr(), P, idx.data_ptr(), dist.data_ptr(), ws.data_ptr(), ws.numel(), st))
+        if bank.sorted_desc is not None and _lib.get_option("pipeline") == 2 and _lib.get_option("epilogue") == 1:
+            # chunk pipeline: bounds on the norm-sorted bank + exact evaluation of two chunks per row + exact fallback
+            _lib.check(_lib.lib().b200m_knn2_sorted_u8(
+                bank.desc.data_ptr(), bank.sqnorm.data_ptr(), bank.sorted_desc.data_ptr(), bank.sort_table.data_ptr(),
+                bank.k_per_image.data_ptr(), bank.n_img, bank.k_stride, pairs_t.data_ptr(), P, idx.data_ptr(),
+                dist.data_ptr(), ws.data_ptr(), ws.numel(), st))
+        else:
+            _lib.check(_lib.lib().b200m_knn2_u8(
+                bank.desc.data_ptr(), bank.sqnorm.data_ptr(), bank.k_per_image.data_ptr(), bank.n_img, bank.k_stride,
+                pairs_t.data_ptr(), P, idx.data_ptr(), dist.data_ptr(), ws.data_ptr(), ws.numel(), st))
     return idx, dist
 
 

@@ -77,3 +77,45 @@ def window_shard(n_img: int, window: int, world_size: int, rank: int):
     rows = [(i, j) for i in range(lo, hi) for j in range(i + 1, min(n_img, i + 1 + window))]
     gp = np.asarray(rows, dtype=np.int32).reshape(-1, 2)
     return lo, hi, halo_hi, gp - lo, gp
+
+
+def partition_by_owner(pairs: np.ndarray, world_size: int, rank: int, n_loc: int):
+    """Partition for the sharded host-buffer path: rank r OWNS images [r * n_loc, (r + 1) * n_loc) (it uploads and
+    prepares them), and every pair goes to the owner of one of its two images -- of the query image when
+    (query + train) is even, of the train image otherwise -- so each image hands about half of its pairs to
+    either side. Ranks left above the mean by that rule (the last rank usually owns fewer images) pass the tail
+    of their non-local pairs on to the ranks below it. A rank's pairs come back with the pairs BETWEEN ITS OWN
+    images first (in list order): they can be matched while the rest of the bank is still travelling between
+    the GPUs. Deterministic, no communication.
+    -> (pairs_of_rank, indices into `pairs`, number of leading local-only pairs)"""
+    pairs = np.asarray(pairs, dtype=np.int32).reshape(-1, 2)
+    if world_size <= 1:
+        return pairs, np.arange(len(pairs)), len(pairs)
+    q, t = pairs[:, 0].astype(np.int64), pairs[:, 1].astype(np.int64)
+    oq, ot = q // n_loc, t // n_loc
+    owner = np.where((q + t) % 2 == 0, oq, ot)
+    local = oq == ot
+    target = -(-len(pairs) // world_size)
+    pool = []
+    for r in range(world_size):                      # surplus: the tail of a rank's non-local pairs
+        mine = np.nonzero((owner == r) & ~local)[0]
+        extra = int((owner == r).sum()) - target
+        if extra > 0:
+            pool.append(mine[len(mine) - min(extra, len(mine)):])
+    if pool:
+        pool = np.concatenate(pool)
+        owner = owner.copy()
+        owner[pool] = -1
+        at = 0
+        for r in range(world_size):                  # deficit: filled from the pool in rank order
+            room = target - int((owner == r).sum())
+            if room > 0 and at < len(pool):
+                take = pool[at: at + room]
+                owner[take] = r
+                at += len(take)
+        if at < len(pool):                           # rounding leftovers
+            owner[pool[at:]] = world_size - 1
+    mine = np.nonzero(owner == rank)[0]
+    loc = local[mine] & (oq[mine] == rank)
+    idx = np.concatenate([mine[loc], mine[~loc]])
+    return pairs[idx], idx, int(loc.sum())

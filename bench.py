@@ -619,9 +619,11 @@ def main():
                        "l2": "inputs larger than L2: 539 MB bank, every step sweeps all of it",
                        "bank_generate_s": t_gen,
                        "collectives_ms": {"bank_broadcast_cold": bcast_ms[0], "bank_broadcast_warm": bcast_ms[-1] if world > 1 else None,
-                                          "e2e_first_call": e2e_cold_ms, "e2e_phases_warm": phases or None},
+                                          "e2e_first_call": e2e_cold_ms, "e2e_phases_warm": phases or None,
+                                          "e2e_bank_transport": dmod.transport_in_use()},
                        "parallelism": f"pairs sharded over {world} GPU(s); value leg: no collective in the data path; e2e leg: "
-                                      "sharded upload + bank all-gather + one packed gather per step"},
+                                      "sharded upload, pairs between a rank's own images matched while the prepared bank slices "
+                                      "travel between the GPUs (copy engines over NVLink), one packed gather per step"},
             "e2e": {"value": P_all / (e2e_ms / 1e3), "unit": "pairs/s", "ms_per_step": e2e_ms,
                     "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "api": "3d_reconstruction_b200.distributed.match_pairs_host (matcher.match_pairs_host on one rank)"},

@@ -112,6 +112,17 @@ int b200m_knn2_u8(const uint8_t* bank, const int32_t* norm_table, const int32_t*
                   int32_t* out_train_idx, float* out_dist,
                   void* workspace, size_t workspace_bytes, void* stream);
 
+/* The same knnMatch(k=2) table on the chunk pipeline (needs the outputs of b200m_bank_sort_u8): one chunk sweep on the
+ * norm-sorted bank keeps the three smallest chunk bounds of every query row, the two winning 64-column chunks are
+ * evaluated exactly (rows bucketed by chunk, dp4a), rows whose runner-up is not provably ahead of every other
+ * column go through the exact top-2 sweep. Bit-identical outputs, about 1.5x the throughput of b200m_knn2_u8. */
+int b200m_knn2_sorted_u8(const uint8_t* bank, const int32_t* norm_table,
+                         const uint8_t* sorted_bank, const int32_t* sort_table,
+                         const int32_t* k_per_image, int32_t n_img, int64_t k_stride,
+                         const int32_t* pairs, int64_t n_pairs,
+                         int32_t* out_train_idx, float* out_dist,
+                         void* workspace, size_t workspace_bytes, void* stream);
+
 /* The full matching rule of the hot path for every pair:
  *   2-NN in L2  ->  keep q if dist1 < ratio * dist2 (float32 distances, double compare,
  *   exactly `m.distance < ratio * n.distance` on cv2 DMatch)  ->  if mutual != 0 keep (q,t) only

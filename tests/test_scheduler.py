@@ -63,3 +63,25 @@ def test_window_shard_covers_the_schedule(pkg):
                 assert max(counts) - min(counts) <= 2 * w          # balanced on pair counts
                 lo, hi, halo, _, _ = pkg.window_shard(n, w, 8, 3)
                 assert halo - lo <= 2000 // 8 + w + 2                 # ~282 images per rank instead of 2,000
+
+
+def test_partition_by_owner_is_balanced_and_local_first(pkg):
+    sched = importlib.import_module("3d_reconstruction_b200.scheduler")
+    for n_img, ws in ((257, 8), (257, 4), (64, 8), (12, 2), (5, 2), (9, 4)):
+        pairs = sched.blocked_order(sched.exhaustive_pairs(n_img))
+        n_loc = -(-n_img // ws)
+        seen = np.zeros(len(pairs), int)
+        sizes = []
+        for r in range(ws):
+            p, idx, n_local = sched.partition_by_owner(pairs, ws, r, n_loc)
+            assert np.array_equal(p, pairs[idx])
+            seen[idx] += 1
+            sizes.append(len(p))
+            lo = r * n_loc
+            assert ((p[:n_local] >= lo) & (p[:n_local] < lo + n_loc)).all()        # leading pairs: own images only
+            assert not (((p[n_local:] >= lo) & (p[n_local:] < lo + n_loc)).all(axis=1)).any()
+            assert np.all(np.diff(idx[:n_local]) > 0) and np.all(np.diff(idx[n_local:]) > 0)   # list order inside both parts
+        assert (seen == 1).all()                                                     # every pair exactly once
+        assert max(sizes) - min(sizes) <= max(1, ws), (n_img, ws, sizes)
+    p, idx, n_local = sched.partition_by_owner(pairs, 1, 0, 9)
+    assert len(p) == len(pairs) and n_local == len(pairs)
