@@ -11,4 +11,5 @@ from .matcher import (B200Matcher, FlatMatches, MatchConfig, PairMatches, digest
 from .assignment import AssignmentHead, assign_pairs  # noqa: F401
 from .geometry import PoseBatch, essential_ransac  # noqa: F401
 from .driver import Gates, bow_view_graph, match_view_graph, run_matching_stage, save_matches, vq_words  # noqa: F401
-from .scheduler import blocked_order, exhaustive_pairs, partition, window_pairs, window_shard  # noqa: F401
+from .scheduler import (blocked_order, exhaustive_pairs, partition, partition_by_owner, window_pairs,  # noqa: F401
+                        window_shard)

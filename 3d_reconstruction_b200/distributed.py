@@ -303,26 +303,32 @@ def match_pairs_host(desc_host_local: torch.Tensor, k_per_image, n_img: int, pai
                 ev.record(copy)
                 landed.append(ev)
         segs = M.upload_segments(mine[:n_local] - lo, n_loc, block) if symm is not None else []
-        todo = []                                           # local segments whose images are resident, not launched yet
+
+        def match(p0, p1):
+            if p1 > p0:
+                M.match_pairs(bank, pd[p0:p1], ratio=ratio, mutual=mutual, cap=cap, out=M._out_rows(out, p0, p1), workspace=ws_t)
+
+        prepared = torch.cuda.Event()
         for b in range(n_blocks):
             main.wait_event(landed[b])
             bank.prepare_range(lo + b * block, min(n_loc, (b + 1) * block) - b * block)
-            todo += [s for s in segs if s[0] == b]
-        mark("upload_prepare", 1)
-        prepared = torch.cuda.Event()
-        prepared.record(main)
-        # 3: the exchange, on its own stream when the copy engines do it
+            if b == n_blocks - 1:
+                prepared.record(main)                       # the whole slice is ready for the other ranks
+                mark("upload_prepare", 1)
+                if symm is not None:                        # 3: the exchange, on its own stream: the copy engines do it
+                    symm.stream.wait_event(prepared)
+                    with torch.cuda.stream(symm.stream):
+                        mark("exchange", 0, symm.stream)
+                        symm.pull_all(n_loc)
+                        mark("exchange", 1, symm.stream)
+                        exchanged = torch.cuda.Event()
+                        exchanged.record(symm.stream)
+            if b == 0:
+                mark("match_local", 0)
+            for sg in segs:                                 # local pairs whose images are resident by now
+                if sg[0] == b:
+                    match(sg[1], sg[2])
         if symm is not None:
-            symm.stream.wait_event(prepared)
-            with torch.cuda.stream(symm.stream):
-                mark("exchange", 0, symm.stream)
-                symm.pull_all(n_loc)
-                mark("exchange", 1, symm.stream)
-                exchanged = torch.cuda.Event()
-                exchanged.record(symm.stream)
-            mark("match_local", 0)
-            for _, p0, p1 in todo:
-                M.match_pairs(bank, pd[p0:p1], ratio=ratio, mutual=mutual, cap=cap, out=M._out_rows(out, p0, p1), workspace=ws_t)
             mark("match_local", 1)
             main.wait_event(exchanged)
             rest0 = n_local
@@ -333,8 +339,7 @@ def match_pairs_host(desc_host_local: torch.Tensor, k_per_image, n_img: int, pai
             rest0 = 0
         # 4: everything else
         mark("match_rest", 0)
-        if P > rest0:
-            M.match_pairs(bank, pd[rest0:], ratio=ratio, mutual=mutual, cap=cap, out=M._out_rows(out, rest0, P), workspace=ws_t)
+        match(rest0, P)
         flat = out.flatten()
         mark("match_rest", 1)
         counts = (flat.offsets[1:] - flat.offsets[:-1]).to(torch.int32)

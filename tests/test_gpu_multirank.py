@@ -44,12 +44,17 @@ def _worker(rank, world, port, out_path):
     n_img = desc.shape[0]
     n_loc, _ = dmod.image_slices(n_img, world)
     local = desc[rank * n_loc: min(n_img, (rank + 1) * n_loc)].clone().pin_memory()
-    for _ in range(2):                                               # twice: the second call reuses cached buffers
-        got = dmod.match_pairs_host(local, kpi.numpy(), n_img, pairs, cap=1536, device=dev)
+    res = {}
+    for transport in ("auto", "nccl", "auto"):                       # copy engines over symmetric memory (twice: cached buffers), NCCL
+        got = dmod.match_pairs_host(local, kpi.numpy(), n_img, pairs, cap=1536, device=dev, transport=transport, block=2)
+        if rank == 0:
+            res[transport] = {"off": got.offsets.clone(), "q": got.query_idx.clone(), "t": got.train_idx.clone(),
+                              "d": got.dist.clone()}
+        else:
+            assert got is None
     if rank == 0:
-        torch.save({"off": got.offsets, "q": got.query_idx, "t": got.train_idx, "d": got.dist}, out_path)
-    else:
-        assert got is None
+        res["transport"] = dmod.transport_in_use()
+        torch.save(res, out_path)
     dist.barrier()
     dist.destroy_process_group()
 
@@ -59,11 +64,14 @@ def test_two_ranks_equal_one_rank_bitwise(pkg, tmp_path):
     import torch.multiprocessing as mp
     out = str(tmp_path / "gathered.pt")
     mp.spawn(_worker, args=(2, _free_port(), out), nprocs=2, join=True)
-    r = torch.load(out)
+    res = torch.load(out)
     desc, kpi, pairs = _inputs()
     bank = pkg.DescriptorBank.from_packed(desc.cuda(), kpi)
     ref = pkg.match_pairs(bank, pairs, cap=1536).flatten().cpu()
-    assert torch.equal(r["off"], ref.offsets)
-    assert torch.equal(r["q"], ref.query_idx) and torch.equal(r["t"], ref.train_idx)
-    assert torch.equal(r["d"].view(torch.int32), ref.dist.view(torch.int32))
+    print("bank transport of the 'auto' calls:", res["transport"])
+    for transport in ("auto", "nccl"):
+        r = res[transport]
+        assert torch.equal(r["off"], ref.offsets), transport
+        assert torch.equal(r["q"], ref.query_idx) and torch.equal(r["t"], ref.train_idx), transport
+        assert torch.equal(r["d"].view(torch.int32), ref.dist.view(torch.int32)), transport
     assert int(ref.offsets[-1]) > 1000
