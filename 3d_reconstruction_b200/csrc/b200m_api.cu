@@ -49,6 +49,9 @@ struct Options {
   // float path: 0 = one sweep per pair with the column maximum fused into it (match_float2.cuh, default),
   // 1 = one sweep per direction (match_float.cuh; resolves exact ties between different rows like the reference)
   std::atomic<int64_t> float_sweep{0};
+  // knnMatch chunk pipeline, exact evaluation of the two winning chunks: 0 = tensor cores over gathered rows
+  // (knn_eval_tc_kernel, default), 1 = dp4a (knn_eval_kernel)
+  std::atomic<int64_t> knn_eval{0};
 } g_opt;
 
 // Optional per-launch timing of the sweeps with CUDA events on the launching stream ("profile" option).
@@ -590,6 +593,11 @@ int b200m_set_option(const char* name, int64_t value) {
     g_opt.float_sweep = value;
     return B200M_OK;
   }
+  if (!strcmp(name, "knn_eval")) {
+    if (value != 0 && value != 1) return fail(B200M_E_BAD_ARG, "knn_eval must be 0 (tensor cores) or 1 (dp4a)%s");
+    g_opt.knn_eval = value;
+    return B200M_OK;
+  }
   return fail(B200M_E_BAD_ARG, "unknown option %s", name);
 }
 
@@ -603,6 +611,7 @@ int64_t b200m_get_option(const char* name) {
   if (!strcmp(name, "chunk")) return g_opt.chunk;
   if (!strcmp(name, "profile")) return g_prof.on ? 1 : 0;
   if (!strcmp(name, "float_sweep")) return g_opt.float_sweep;
+  if (!strcmp(name, "knn_eval")) return g_opt.knn_eval;
   return -1;
 }
 
@@ -821,7 +830,10 @@ int b200m_knn2_sorted_u8(const uint8_t* bank, const int32_t* norm_table, const u
     {
       ProfScope ps(&g_prof.refine, st);
       b200m::knn_bucket_kernel<<<static_cast<unsigned>(nb), 1024, 0, st>>>(kp);
-      b200m::knn_eval_kernel<<<dim3(static_cast<unsigned>(kp.n_chunks), static_cast<unsigned>(nb)), b200m::kKnnEvalThreads, 0, st>>>(kp);
+      if (g_opt.knn_eval == 0)
+        b200m::knn_eval_tc_kernel<<<dim3(static_cast<unsigned>(kp.n_chunks), static_cast<unsigned>(nb)), b200m::kKnnTcThreads, 0, st>>>(kp);
+      else
+        b200m::knn_eval_kernel<<<dim3(static_cast<unsigned>(kp.n_chunks), static_cast<unsigned>(nb)), b200m::kKnnEvalThreads, 0, st>>>(kp);
       b200m::knn_combine_kernel<<<dim3(static_cast<unsigned>((k_stride + 255) / 256), static_cast<unsigned>(nb)), 256, 0, st>>>(kp);
     }
     CUDA_TRY(cudaGetLastError());

@@ -21,6 +21,7 @@
 #include <stdint.h>
 
 #include "match_refine.cuh"
+#include "ptx_sm100.cuh"
 
 namespace b200m {
 
@@ -173,6 +174,123 @@ knn_eval_kernel(const KnnParams p) {
       p.taskres[(static_cast<int64_t>(pair) * p.k_stride + pos) * 2 + slot] = out;
     }
   }
+}
+
+// Tensor-core version of knn_eval_kernel (the one the library launches): one CTA of 128 threads per (chunk, pair),
+// several CTAs per SM. The chunk's 64 columns are staged once as a K-major SWIZZLE_128B operand (the layout TMA
+// would produce: 16-byte word w of row r at r * 128 + ((w ^ (r & 7)) << 4)); the task rows are GATHERED by index
+// into the same layout, 128 at a time, with plain 16-byte loads / stores (eight lanes per row: whole 128-byte lines
+// both ways), made visible to the tensor core with fence.proxy.async; one elected thread issues the four
+// tcgen05.mma.kind::i8 of a 128 x 64 x 128 tile into 64 TMEM columns and every thread then reduces ITS task's 64
+// dot products to the two smallest keys (score << 6 | rank of the original train row) -- no cross-lane traffic.
+constexpr int kKnnTcThreads = 128;
+
+__global__ void __launch_bounds__(kKnnTcThreads)
+knn_eval_tc_kernel(const KnnParams p) {
+  __shared__ alignas(1024) uint8_t a_tile[128 * 128];
+  __shared__ alignas(1024) uint8_t b_tile[kKnnChunk * 128];
+  __shared__ alignas(16) uint32_t s_nkey[kKnnChunk];           // ((norm + 2^25) << 6) | rank; >= 0xffffffc0 for padding
+  __shared__ int s_orig[kKnnChunk], s_byrank[kKnnChunk], s_task[128];
+  __shared__ alignas(8) uint64_t bar;
+  __shared__ uint32_t tmem_slot;
+  const int g = blockIdx.x, pair = blockIdx.y;
+  const int32_t* boff = p.boff + static_cast<int64_t>(pair) * (p.n_chunks + 1);
+  const int t0 = __ldg(boff + g), n_tasks = __ldg(boff + g + 1) - t0;
+  if (n_tasks <= 0) return;
+  const PairInfo pi = load_pair(p.pairs, p.k_per_image, pair, p.n_img, p.k_stride);
+  const int64_t qbase = static_cast<int64_t>(pi.qi) * p.k_stride, tbase = static_cast<int64_t>(pi.ti) * p.k_stride;
+  const int c0 = g * kKnnChunk;
+  const int n_valid = min(pi.kt - c0, kKnnChunk);              // real columns of this chunk (>= 1 for a chunk with tasks)
+  const int t = threadIdx.x, warp = t >> 5;
+  if (warp == 0) tmem_alloc<64>(&tmem_slot);
+  if (t == 32) {
+    mbar_init(&bar, 1);
+    fence_mbar_init();
+  }
+  // the chunk: 64 rows x 128 B, padding columns as zeros (their dot products are 0, their keys stay >= 0xffffffc0)
+#pragma unroll
+  for (int it = 0; it < 4; ++it) {
+    const int idx = it * kKnnTcThreads + t, r = idx >> 3, w = idx & 7;
+    uint4 v = make_uint4(0, 0, 0, 0);
+    if (r < n_valid) v = __ldg(reinterpret_cast<const uint4*>(p.sbank + (tbase + c0 + r) * 128) + w);
+    *reinterpret_cast<uint4*>(b_tile + r * 128 + ((w ^ (r & 7)) << 4)) = v;
+  }
+  if (t < kKnnChunk) s_orig[t] = t < n_valid ? __ldg(p.perm + tbase + c0 + t) : 0x7fffffff - (kKnnChunk - t);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = tmem_slot;
+  if (t < kKnnChunk) {
+    const int mine = s_orig[t];
+    int rank = 0;
+#pragma unroll 8
+    for (int o = 0; o < kKnnChunk; ++o) rank += s_orig[o] < mine;
+    s_byrank[rank] = mine;
+    s_nkey[t] = t < n_valid ? (static_cast<uint32_t>(__ldg(p.snorm + tbase + c0 + t) + kKnnScoreOff) << 6) | rank
+                            : 0xffffffc0u | rank;
+  }
+  const int32_t* tasks = p.tasks + 2 * static_cast<int64_t>(pair) * p.k_stride + t0;
+  constexpr uint32_t idesc = make_idesc_u8(128, kKnnChunk);
+  const uint64_t adesc = make_desc_k128(smem_u32(a_tile)), bdesc = make_desc_k128(smem_u32(b_tile));
+  uint32_t phase = 0;
+  for (int base = 0; base < n_tasks; base += 128) {
+    const int mytask = base + t < n_tasks ? __ldg(tasks + base + t) : -1;
+    s_task[t] = mytask;
+    __syncthreads();                                           // also: s_nkey / s_byrank written, previous tile drained
+#pragma unroll
+    for (int it = 0; it < 8; ++it) {
+      const int idx = it * kKnnTcThreads + t, r = idx >> 3, w = idx & 7;
+      const int task = s_task[r];
+      if (task >= 0) {                                         // rows past the last task keep stale bytes: never read back
+        const uint4 v = __ldg(reinterpret_cast<const uint4*>(p.sbank + (qbase + (task & 0x3fffffff)) * 128) + w);
+        *reinterpret_cast<uint4*>(a_tile + r * 128 + ((w ^ (r & 7)) << 4)) = v;
+      }
+    }
+    fence_proxy_async_smem();                                  // generic-proxy stores -> visible to the tensor core
+    tc_fence_before();
+    __syncthreads();
+    if (t == 0) {
+      tc_fence_after();
+#pragma unroll
+      for (int k = 0; k < 4; ++k) mma_i8_ss(tmem, adesc + 2 * k, bdesc + 2 * k, idesc, k > 0 ? 1u : 0u);
+      tc_commit(&bar);
+    }
+    mbar_wait(&bar, phase);
+    phase ^= 1;
+    tc_fence_after();
+    uint32_t m1 = 0xffffffffu, m2 = 0xffffffffu;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      int v[32];
+      tmem_ld_32x32(tmem + (static_cast<uint32_t>(warp * 32) << 16) + h * 32, v);
+      tmem_ld_fence(v);
+#pragma unroll
+      for (int j4 = 0; j4 < 8; ++j4) {
+        const uint4 nk = *reinterpret_cast<const uint4*>(s_nkey + h * 32 + j4 * 4);
+        const uint32_t n4[4] = {nk.x, nk.y, nk.z, nk.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const uint32_t key = n4[j] - (static_cast<uint32_t>(v[j4 * 4 + j]) << 7);   // (norm - 2 dot + 2^25) << 6 | rank
+          const uint32_t hi = max(m1, key);
+          m1 = min(m1, key);
+          m2 = min(m2, hi);
+        }
+      }
+    }
+    if (mytask >= 0) {
+      const int pos = mytask & 0x3fffffff, slot = mytask >> 30;
+      const bool second = m2 < 0xffffffc0u;
+      int4 out;
+      out.x = static_cast<int>(m1 >> 6) - kKnnScoreOff;
+      out.y = s_byrank[m1 & 63];
+      out.z = second ? static_cast<int>(m2 >> 6) - kKnnScoreOff : kBigScore;
+      out.w = second ? s_byrank[m2 & 63] : -1;
+      p.taskres[(static_cast<int64_t>(pair) * p.k_stride + pos) * 2 + slot] = out;
+    }
+    tc_fence_before();
+  }
+  __syncthreads();
+  if (warp == 0) tmem_dealloc<64>(tmem);
 }
 
 // Per (pair, sorted query row): merge the row's two tasks, settle or fall back.

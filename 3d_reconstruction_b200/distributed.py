@@ -12,7 +12,7 @@ import numpy as np
 import torch
 import torch.distributed as dist
 
-from .scheduler import partition, partition_by_owner
+from .scheduler import partition, partition_all_by_owner
 
 
 def is_dist() -> bool:
@@ -279,16 +279,7 @@ def match_pairs_host(desc_host_local: torch.Tensor, k_per_image, n_img: int, pai
             bank.k_per_image.copy_(torch.from_numpy(kpi), non_blocking=True)
         else:
             bank = DescriptorBank.allocate(n_pad, ks, torch.from_numpy(kpi), dev)
-        parts = [partition_by_owner(pairs_np, ws, r, n_loc) for r in range(ws)]
-        mine, idx, n_local = parts[rank]
-        P = len(mine)
-        pd = torch.from_numpy(np.ascontiguousarray(mine)).to(dev, non_blocking=True)
-        if out is None:
-            out = M._new_out(P, cap, dev)
-        else:
-            M._check_out(out, P)
-        ws_t = workspace if workspace is not None else M._workspace(bank, max(P, 1))
-        # 1 + 2: chunked upload of the own images, local pairs as their images land
+        # 1: chunked upload of the own images -- enqueued before any host-side planning, which then runs under it
         mark("upload_prepare", 0)
         copy = M._copy_stream(dev)
         copy.wait_stream(main)
@@ -302,6 +293,17 @@ def match_pairs_host(desc_host_local: torch.Tensor, k_per_image, n_img: int, pai
                 ev = torch.cuda.Event()
                 ev.record(copy)
                 landed.append(ev)
+        parts = partition_all_by_owner(pairs_np, ws, n_loc)
+        idx, n_local = parts[rank]
+        mine = pairs_np[idx]
+        P = len(mine)
+        pd = torch.from_numpy(np.ascontiguousarray(mine)).to(dev, non_blocking=True)
+        if out is None:
+            out = M._new_out(P, cap, dev)
+        else:
+            M._check_out(out, P)
+        ws_t = workspace if workspace is not None else M._workspace(bank, max(P, 1))
+        # 2: local pairs as their images land
         segs = M.upload_segments(mine[:n_local] - lo, n_loc, block) if symm is not None else []
 
         def match(p0, p1):
@@ -340,17 +342,18 @@ def match_pairs_host(desc_host_local: torch.Tensor, k_per_image, n_img: int, pai
         # 4: everything else
         mark("match_rest", 0)
         match(rest0, P)
+        if rank == dst:                                 # host work under the running kernels: gathered position -> list index
+            order = torch.from_numpy(np.concatenate([pp[0] for pp in parts])).to(dev, non_blocking=True)
         flat = out.flatten()
         mark("match_rest", 1)
         counts = (flat.offsets[1:] - flat.offsets[:-1]).to(torch.int32)
         mark("gather", 0)
-        got = gather_packed(counts, [flat.query_idx, flat.train_idx, flat.dist], [len(pp[1]) for pp in parts], dst)
+        got = gather_packed(counts, [flat.query_idx, flat.train_idx, flat.dist], [len(pp[0]) for pp in parts], dst)
         if got is None:
             mark("gather", 1)
             return None
         off, fields = got
         # rank-ordered concatenation -> the order of `pairs`
-        order = torch.from_numpy(np.concatenate([pp[1] for pp in parts])).to(dev)           # gathered position -> list index
         cnt = off[1:] - off[:-1]
         cnt_list = torch.empty_like(cnt)
         cnt_list[order] = cnt

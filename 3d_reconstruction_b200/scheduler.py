@@ -91,31 +91,50 @@ def partition_by_owner(pairs: np.ndarray, world_size: int, rank: int, n_loc: int
     pairs = np.asarray(pairs, dtype=np.int32).reshape(-1, 2)
     if world_size <= 1:
         return pairs, np.arange(len(pairs)), len(pairs)
+    idx, n_local = partition_all_by_owner(pairs, world_size, n_loc)[rank]
+    return pairs[idx], idx, n_local
+
+
+def partition_all_by_owner(pairs: np.ndarray, world_size: int, n_loc: int):
+    """partition_by_owner for every rank in one pass over the list (the sharded host path needs all of them: its
+    own pairs to match, everybody's to put the gathered results back into list order).
+    -> [(indices into `pairs`, number of leading local-only pairs)] per rank"""
+    pairs = np.asarray(pairs, dtype=np.int32).reshape(-1, 2)
     q, t = pairs[:, 0].astype(np.int64), pairs[:, 1].astype(np.int64)
     oq, ot = q // n_loc, t // n_loc
-    owner = np.where((q + t) % 2 == 0, oq, ot)
+    owner = np.where(((q + t) & 1) == 0, oq, ot)
     local = oq == ot
     target = -(-len(pairs) // world_size)
+    counts = np.bincount(owner, minlength=world_size)
+    small = np.int16 if world_size < 32000 else np.int64                       # int16: numpy's stable sort is a radix sort
+    by_owner = np.argsort(owner.astype(small), kind="stable")                  # grouped by owner, list order inside
+    starts = np.concatenate([[0], np.cumsum(counts)])
     pool = []
-    for r in range(world_size):                      # surplus: the tail of a rank's non-local pairs
-        mine = np.nonzero((owner == r) & ~local)[0]
-        extra = int((owner == r).sum()) - target
-        if extra > 0:
-            pool.append(mine[len(mine) - min(extra, len(mine)):])
+    for r in np.nonzero(counts > target)[0]:         # surplus: the tail of a rank's non-local pairs
+        grp = by_owner[starts[r]: starts[r + 1]]
+        mine = grp[~local[grp]]
+        extra = int(counts[r]) - target
+        pool.append(mine[len(mine) - min(extra, len(mine)):])
     if pool:
         pool = np.concatenate(pool)
         owner = owner.copy()
         owner[pool] = -1
+        counts = np.bincount(owner[owner >= 0], minlength=world_size)
         at = 0
         for r in range(world_size):                  # deficit: filled from the pool in rank order
-            room = target - int((owner == r).sum())
+            room = target - int(counts[r])
             if room > 0 and at < len(pool):
                 take = pool[at: at + room]
                 owner[take] = r
                 at += len(take)
         if at < len(pool):                           # rounding leftovers
             owner[pool[at:]] = world_size - 1
-    mine = np.nonzero(owner == rank)[0]
-    loc = local[mine] & (oq[mine] == rank)
-    idx = np.concatenate([mine[loc], mine[~loc]])
-    return pairs[idx], idx, int(loc.sum())
+        counts = np.bincount(owner, minlength=world_size)
+        by_owner = np.argsort(owner.astype(small), kind="stable")
+        starts = np.concatenate([[0], np.cumsum(counts)])
+    parts = []
+    for r in range(world_size):
+        mine = by_owner[starts[r]: starts[r + 1]]
+        loc = local[mine] & (oq[mine] == r)
+        parts.append((np.concatenate([mine[loc], mine[~loc]]), int(loc.sum())))
+    return parts

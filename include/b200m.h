@@ -226,6 +226,9 @@ int b200m_five_point_f64(const double* x0, const double* x1, double* out_E, int3
  *   "chunk"     columns per chunk of the chunk sweep: 64 (default, kernel 5 only) or 32
  *   "grid"      number of persistent CTAs, 0 = one per SM (default)
  *   "batch"     pairs per internal batch, 0 = default
+ *   "float_sweep" 0 = float path as ONE tensor sweep per pair, column maxima fused (default), 1 = one sweep per direction
+ *   "knn_eval"  b200m_knn2_sorted_u8, exact evaluation of the two winning chunks: 0 = tensor cores over gathered
+ *               rows (default), 1 = dp4a
  *   "profile"   1 = time sweep launches with CUDA events (see b200m_profile_read) */
 int b200m_set_option(const char* name, int64_t value);
 int64_t b200m_get_option(const char* name);

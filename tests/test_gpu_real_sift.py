@@ -91,3 +91,36 @@ def _last_workspace(pkg, bank):
     ws = torch.empty(int(pkg._lib.lib().b200m_workspace_bytes(bank.k_stride, 1)), dtype=torch.uint8, device=bank.device)
     pkg.match_pairs(bank, [[0, 1]], ratio=0.75, mutual=True, workspace=ws)
     return ws
+
+
+@pytest.mark.parametrize("knn_eval", [0, 1])
+def test_knn2_chunk_pipeline_eval_variants(pkg, cases, golden_dir, knn_eval):
+    """knnMatch(k=2) on the chunk pipeline with both evaluators of the two winning chunks (0 = tensor cores over
+    gathered rows, the default; 1 = dp4a): the complete cv2 table on the real 16k / ragged cases, the tie fixture
+    (equal distances -> lowest train index) and a ragged synthetic pair whose last chunk is partly padding."""
+    data, ref = cases
+    pkg.set_option("knn_eval", knn_eval)
+    try:
+        assert pkg.get_option("knn_eval") == knn_eval
+        for case in ("16k", "ragged_8k_16k"):
+            q, t = data[case]
+            idx, dist = pkg.knn_match(q, t)
+            eidx, edist = ref[case]["knn"]
+            assert np.array_equal(idx, eidx), f"{case}: knn rows differ: {np.nonzero((idx != eidx).any(1))[0][:8]}"
+            assert np.array_equal(_bits(dist), _bits(edist)), case
+        g = np.load(os.path.join(golden_dir, "ties.npz"))
+        idx, dist = pkg.knn_match(g["q"], g["t"])
+        assert np.array_equal(idx, g["knn_idx"]) and np.array_equal(_bits(dist), _bits(g["knn_dist"]))
+        rng = np.random.default_rng(11)
+        base = rng.integers(0, 256, size=(40, 128))
+        for kq, kt in ((700, 515), (300, 1), (129, 65), (64, 2000)):
+            q = np.clip(base[rng.integers(0, 40, kq)] + rng.integers(-9, 10, (kq, 128)), 0, 255).astype(np.uint8)
+            t = np.clip(base[rng.integers(0, 40, kt)] + rng.integers(-9, 10, (kt, 128)), 0, 255).astype(np.uint8)
+            t[kt // 2] = t[0]                       # an exact duplicate column: stable order decides
+            idx, dist = pkg.knn_match(q, t)
+            eidx, edist = oracle_cv2.knn2(q, t)
+            assert np.array_equal(idx, eidx), (kq, kt)
+            assert np.array_equal(_bits(dist), _bits(edist)), (kq, kt)
+    finally:
+        pkg.set_option("knn_eval", 0)
+        torch.cuda.synchronize()
