@@ -791,6 +791,7 @@ int b200m_knn2_sorted_u8(const uint8_t* bank, const int32_t* norm_table, const u
   if (rc) return rc;
   const SortTable tv = sort_table_view(sort_table, n_img, k_stride);
   const int64_t R = B * k_stride;
+  CUDA_TRY(cudaMemsetAsync(w.stats, 0, sizeof(unsigned long long) * b200m::kStatSlots * b200m::kStatFields, st));
   for (int64_t p0 = 0; p0 < n_pairs; p0 += B) {
     const int64_t nb = (n_pairs - p0 < B) ? (n_pairs - p0) : B;
     const int32_t* pb = pairs + 2 * p0;
@@ -827,6 +828,7 @@ int b200m_knn2_sorted_u8(const uint8_t* bank, const int32_t* norm_table, const u
     kp.fb_total = w.fb_count + B;
     kp.fb_q = w.fb_q;
     kp.fb_desc = w.gath_q;
+    kp.stats = w.stats;
     {
       ProfScope ps(&g_prof.refine, st);
       b200m::knn_bucket_kernel<<<static_cast<unsigned>(nb), 1024, 0, st>>>(kp);

@@ -49,6 +49,7 @@ struct KnnParams {
   int32_t* fb_total;            // [1]
   int32_t* fb_q;                // [n_pairs][k_stride] their original query rows
   uint8_t* fb_desc;             // [n_pairs][k_stride][128] their descriptors
+  unsigned long long* stats;    // call counters (match_common.cuh): 0 rows, 1 settled by the two chunks, 2 fallback
 };
 
 // One CTA per pair: tasks (row, chunk g1) and (row, chunk g2) bucketed by chunk.
@@ -320,6 +321,14 @@ knn_combine_kernel(const KnnParams p) {
   // every column outside the two chunks scores >= L3: with s2 < L3 nothing outside can tie or beat the runner-up
   // (a row with a single train column has no runner-up and no outside column: L3 stays at its initial value)
   const bool settled = i2 < 0 ? v.w >= kPadScore : s2 < v.w;
+  {
+    const unsigned act = __activemask(), ok = __ballot_sync(act, settled);
+    if ((threadIdx.x & 31) == __ffs(act) - 1) {
+      stat_add(p.stats, 0, __popc(act));
+      stat_add(p.stats, 1, __popc(ok));
+      stat_add(p.stats, 2, __popc(act & ~ok));
+    }
+  }
   if (settled) {
     p.rowres_o[base + row] = make_int4(s1 + nq, i1, i2 >= 0 ? s2 + nq : 0, i2);
   } else {

@@ -144,8 +144,15 @@ __device__ __forceinline__ ItemInfo decode_item(const SweepParams& p, int item) 
       it.check = item & 1;
       item >>= 1;
     }
-    it.pair = item / p.blocks_per_pair;
-    it.blk = item - it.pair * p.blocks_per_pair;
+    if (is_gathered(kKind)) {
+      // block-major: the few non-empty items of a fallback sweep (block 0 of most pairs, seldom more) are
+      // consecutive, so the persistent CTAs share them evenly (pair-major put them 64 apart: 37 of 148 CTAs)
+      it.blk = item / p.n_pairs;
+      it.pair = item - it.blk * p.n_pairs;
+    } else {
+      it.pair = item / p.blocks_per_pair;
+      it.blk = item - it.pair * p.blocks_per_pair;
+    }
   }
   const PairInfo pi = load_pair(p.pairs, p.k_per_image, it.pair, p.n_img, p.k_stride);
   const int qi = pi.qi, ti = pi.ti, kq = pi.kq, kt = pi.kt;

@@ -230,7 +230,7 @@ def match_pairs_host(desc_host_local: torch.Tensor, k_per_image, n_img: int, pai
     [rank * n_loc, ...) with n_loc = ceil(n_img / world) (image_slices): each process holds the descriptors of the
     images it extracted or loaded and uploads only those, over its own PCIe link. k_per_image: all n_img counts
     (tiny, known everywhere). pairs: the WHOLE pair list, identical on every rank.
-      1. own images host -> device in blocks of `block` images on a copy stream, norms + norm sort per block;
+      1. own images host -> device in blocks (2, 4, 8, then `block` images) on a copy stream, norms + norm sort per block;
       2. every pair belongs to the owner of one of its images (scheduler.partition_by_owner); the pairs between
          a rank's OWN images are matched first, block by block as the upload lands,
       3. while the ranks pull each other's prepared slices (bank, norm-sorted bank, tables) over NVLink with the
@@ -283,17 +283,21 @@ def match_pairs_host(desc_host_local: torch.Tensor, k_per_image, n_img: int, pai
         mark("upload_prepare", 0)
         copy = M._copy_stream(dev)
         copy.wait_stream(main)
-        n_blocks = (n_loc + block - 1) // block
+        bounds = M.upload_blocks(n_loc, block, ramp=True)
+        n_blocks = len(bounds) - 1
         landed = []
         with torch.cuda.stream(copy):
             for b in range(n_blocks):
-                b0, b1 = b * block, min(have, (b + 1) * block)
+                b0, b1 = min(have, bounds[b]), min(have, bounds[b + 1])
                 if b1 > b0:
                     bank.desc[lo + b0: lo + b1].copy_(desc_host_local[b0:b1], non_blocking=True)
                 ev = torch.cuda.Event()
                 ev.record(copy)
                 landed.append(ev)
         parts = partition_all_by_owner(pairs_np, ws, n_loc)
+        for r, (ix, nl) in enumerate(parts):               # local pairs in the order their images land (stable)
+            need = np.searchsorted(np.asarray(bounds[1:]), pairs_np[ix[:nl]].max(axis=1) - r * n_loc, side="right")
+            ix[:nl] = ix[:nl][np.argsort(need.astype(np.int16), kind="stable")]
         idx, n_local = parts[rank]
         mine = pairs_np[idx]
         P = len(mine)
@@ -304,7 +308,7 @@ def match_pairs_host(desc_host_local: torch.Tensor, k_per_image, n_img: int, pai
             M._check_out(out, P)
         ws_t = workspace if workspace is not None else M._workspace(bank, max(P, 1))
         # 2: local pairs as their images land
-        segs = M.upload_segments(mine[:n_local] - lo, n_loc, block) if symm is not None else []
+        segs = M.upload_segments(mine[:n_local] - lo, n_loc, bounds) if symm is not None else []
 
         def match(p0, p1):
             if p1 > p0:
@@ -313,7 +317,7 @@ def match_pairs_host(desc_host_local: torch.Tensor, k_per_image, n_img: int, pai
         prepared = torch.cuda.Event()
         for b in range(n_blocks):
             main.wait_event(landed[b])
-            bank.prepare_range(lo + b * block, min(n_loc, (b + 1) * block) - b * block)
+            bank.prepare_range(lo + bounds[b], bounds[b + 1] - bounds[b])
             if b == n_blocks - 1:
                 prepared.record(main)                       # the whole slice is ready for the other ranks
                 mark("upload_prepare", 1)

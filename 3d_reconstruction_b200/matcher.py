@@ -295,14 +295,26 @@ def _out_rows(out: PairMatches, lo: int, hi: int) -> PairMatches:
     return PairMatches(out.query_idx[lo:hi], out.train_idx[lo:hi], out.dist[lo:hi], out.count[lo:hi], out.cap)
 
 
-def upload_segments(pairs: np.ndarray, n_img: int, block: int):
+def upload_blocks(n_img: int, block: int, ramp: bool = False):
+    """Image-block boundaries of a chunked upload: [0, b1, b2, ..., n_img]. ramp=True starts small (2, 4, 8 images,
+    then `block`): the first pairs can start after two images instead of after a whole block."""
+    bounds, size = [0], (2 if ramp else block)
+    while bounds[-1] < n_img:
+        bounds.append(min(n_img, bounds[-1] + min(size, block)))
+        size *= 2
+    return bounds
+
+
+def upload_segments(pairs: np.ndarray, n_img: int, block):
     """Split a pair list, IN ORDER, into segments that can start as soon as a prefix of the image blocks is
-    resident: -> list of (last image block needed, first pair, end pair). The blocked order of the scheduler
-    (16 x 16 patches of the pair grid) needs the blocks one after the other; any other order still works (its
-    first segment simply waits for more of the bank)."""
+    resident: -> list of (last image block needed, first pair, end pair). block: images per block, or the block
+    boundaries of upload_blocks. The blocked order of the scheduler (16 x 16 patches of the pair grid) needs the
+    blocks one after the other; any other order still works (its first segment simply waits for more of the bank)."""
     if len(pairs) == 0:
         return []
-    need = np.maximum.accumulate(pairs.max(axis=1) // block)
+    hi = pairs.max(axis=1)
+    blk = hi // block if np.isscalar(block) else np.searchsorted(np.asarray(block[1:]), hi, side="right")
+    need = np.maximum.accumulate(blk)
     cuts = np.nonzero(np.diff(need))[0] + 1
     starts = np.concatenate([[0], cuts])
     ends = np.concatenate([cuts, [len(pairs)]])

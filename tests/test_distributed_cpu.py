@@ -189,3 +189,20 @@ def test_upload_segments_follow_the_pair_order(pkg):
     segs = m.upload_segments(row_major, 70, 16)
     assert segs[-1][0] == 4 and segs[-1][2] == len(row_major) and sum(b - a for _, a, b in segs) == len(row_major)
     assert m.upload_segments(np.zeros((0, 2), np.int64), 70, 16) == []
+
+
+def test_upload_blocks_ramp_and_segments_on_boundaries(pkg):
+    m = importlib.import_module("3d_reconstruction_b200.matcher")
+    assert m.upload_blocks(33, 12, ramp=True) == [0, 2, 6, 14, 26, 33]
+    assert m.upload_blocks(33, 12) == [0, 12, 24, 33]
+    assert m.upload_blocks(1, 12, ramp=True) == [0, 1] and m.upload_blocks(0, 12, ramp=True) == [0]
+    bounds = m.upload_blocks(33, 12, ramp=True)
+    pairs = pkg.exhaustive_pairs(33)
+    need = np.searchsorted(np.asarray(bounds[1:]), pairs.max(axis=1), side="right")
+    pairs = pairs[np.argsort(need, kind="stable")]                         # what distributed.match_pairs_host does
+    segs = m.upload_segments(pairs, 33, bounds)
+    assert [s[0] for s in segs] == [0, 1, 2, 3, 4]
+    assert (segs[0][1], segs[0][2]) == (0, 1)                              # the pair (0, 1) can start after two images
+    for need_b, a, b in segs:
+        assert pairs[a:b].max() < bounds[need_b + 1] and pairs[a:b].max() >= bounds[need_b]
+    assert sum(b - a for _, a, b in segs) == len(pairs)

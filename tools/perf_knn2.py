@@ -37,9 +37,11 @@ def run(n_img=33, k=16384, reps=3):
         pkg.set_option("profile", 0)
         t = min(ts)
         res[name] = (idx.clone(), dist.clone())
+        st = pkg.match_stats(ws) if pipeline == 2 else {}
         print(json.dumps({"knn2": name, "k": k, "pairs": P, "sec": round(t, 5), "pairs_per_s": round(P / t, 1),
                           "TOPS": round(2.0 * k * k * 128 * P / t / 1e12, 1),
-                          "per_rep_ms": {kk: round(v / reps, 3) for kk, v in prof.items() if kk.endswith("_ms")}}), flush=True)
+                          "per_rep_ms": {kk: round(v / reps, 3) for kk, v in prof.items() if kk.endswith("_ms")},
+                          "stats": st}), flush=True)
     pkg.set_option("pipeline", 2)
     a, b = res["chunk_pipeline"], res["exact_top2_sweep"]
     print("identical:", bool(torch.equal(a[0], b[0]) and torch.equal(a[1].view(torch.int32), b[1].view(torch.int32))))
