@@ -520,7 +520,7 @@ def main():
         int8_peak = float(probe.get("mma_only_sweep_sustained_tops") or 2.0 * float(peaks.get("bf16_tflops_sustained", 1400.0)))
         peak_source = "no clock sample: this library's MMA-only sweep, sustained (measured in this run)"
     traffic, traffic_src = None, None
-    tpath = os.path.join(ROOT, "profiles", "r01e_traffic.json")
+    tpath = os.path.join(ROOT, "profiles", "r02q_traffic.json")
     if os.path.exists(tpath) and pkg.get_option("kernel") == 5 and pkg.get_option("chunk") == 64 and K == 16384:
         with open(tpath) as f:
             tj = json.load(f)
