@@ -505,7 +505,7 @@ int launch_ip_sweep2(const CUtensorMap& tmap, const b200m::ip::Ip2Params& ip, in
   constexpr size_t smem = sizeof(b200m::ip::Ip2Smem<kDim>) + 1024;
   CUDA_TRY((ensure_smem_attr(b200m::ip::ip_sweep2_kernel<kDim, kMode>, smem)));
   {
-    ProfScope ps(&g_prof.first, st);
+    ProfScope ps(kMode == b200m::ip::kIpLse ? &g_prof.verify : &g_prof.first, st);
     b200m::ip::ip_sweep2_kernel<kDim, kMode><<<grid, b200m::kThreads, smem, st>>>(tmap, ip);
   }
   CUDA_TRY(cudaGetLastError());
@@ -1052,6 +1052,7 @@ int b200m_match_pairs_bf16(const void* bank_bf16, const int32_t* k_per_image, in
     ip.rowbest = rowbest;
     ip.z = nullptr;
     ip.nb = nullptr;
+    ip.gate = nullptr;
     const int grid = sweep_grid(static_cast<int64_t>(ip.n_dirs) * nb * ip.blocks_per_image);
     rc = dim == 256 ? launch_ip_sweep<256>(tmap, ip, grid, st) : launch_ip_sweep<128>(tmap, ip, grid, st);
     if (rc) return rc;
@@ -1066,9 +1067,15 @@ int b200m_match_pairs_bf16(const void* bank_bf16, const int32_t* k_per_image, in
   return mark_invalid_pairs(pairs, n_pairs, n_img, out_count, st);
 }
 
+// Head workspace: row results float2 [2][B][k_stride] (pass 2 reuses the second half for column keys and claims) |
+// nb float [2][B][k_stride] | largest row norm per image float [kMaxNormImgs] | flag | column partial sums of the
+// single-sweep log-sum-exp float [B][k_stride / 64][k_stride].
+constexpr int64_t kMaxNormImgs = 1 << 18;
 size_t b200m_workspace_bytes_assign(int64_t k_stride, int64_t n_pairs) {
   if (k_stride <= 0 || n_pairs <= 0) return 256;
-  return static_cast<size_t>(2) * batch_cap(k_stride, n_pairs) * k_stride * (sizeof(float2) + sizeof(float)) + 1024;
+  const size_t B = static_cast<size_t>(batch_cap(k_stride, n_pairs));
+  return 2 * B * k_stride * (sizeof(float2) + sizeof(float)) + kMaxNormImgs * sizeof(float) + 1024 +
+         B * static_cast<size_t>(k_stride / 64) * k_stride * sizeof(float) + 1024;
 }
 
 int b200m_assign_pairs_bf16(const void* mdesc_bf16, const float* matchability, const int32_t* k_per_image,
@@ -1095,6 +1102,22 @@ int b200m_assign_pairs_bf16(const void* mdesc_bf16, const float* matchability, c
   const int64_t B = batch_pairs(k_stride, n_pairs);
   float2* rowbest = reinterpret_cast<float2*>((reinterpret_cast<uintptr_t>(workspace) + 255) & ~uintptr_t(255));
   float* nbuf = reinterpret_cast<float*>(rowbest + 2 * B * k_stride);
+  float* maxnorm = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(nbuf + 2 * B * k_stride) + 255) & ~uintptr_t(255));
+  int32_t* lse_flag = reinterpret_cast<int32_t*>(maxnorm + kMaxNormImgs);
+  float* colpart = reinterpret_cast<float*>(lse_flag + 64);
+  // pass 1 as ONE sweep per pair too (row and column log-sum-exp from the same exponentials) unless the two-direction
+  // sweeps are asked for; needs the largest row norm of every image as the common reference point
+  const bool lse_single = g_opt.float_sweep == 0 && n_img <= kMaxNormImgs;
+  if (lse_single) {
+    CUDA_TRY(cudaMemsetAsync(maxnorm, 0, sizeof(float) * n_img, st));
+    const int64_t rows = static_cast<int64_t>(n_img) * k_stride;
+    const unsigned blocks = static_cast<unsigned>((rows + 7) / 8);
+    if (dim == 256)
+      b200m::ip::ip_maxnorm_kernel<256><<<blocks, 256, 0, st>>>(static_cast<const uint16_t*>(mdesc_bf16), k_per_image, k_stride, n_img, maxnorm);
+    else
+      b200m::ip::ip_maxnorm_kernel<128><<<blocks, 256, 0, st>>>(static_cast<const uint16_t*>(mdesc_bf16), k_per_image, k_stride, n_img, maxnorm);
+    CUDA_TRY(cudaGetLastError());
+  }
   for (int64_t p0 = 0; p0 < n_pairs; p0 += B) {
     const int64_t nb = (n_pairs - p0 < B) ? (n_pairs - p0) : B;
     b200m::ip::IpParams ip;
@@ -1108,8 +1131,35 @@ int b200m_assign_pairs_bf16(const void* mdesc_bf16, const float* matchability, c
     ip.rowbest = rowbest;
     ip.z = matchability;
     ip.nb = nbuf;
+    ip.gate = nullptr;
     const int grid = sweep_grid(static_cast<int64_t>(2) * nb * ip.blocks_per_image);
-    // pass 1: row and column log-sum-exp (both directions) -> nb; pass 2: arg-max of the log assignment
+    if (lse_single) {
+      CUDA_TRY(cudaMemsetAsync(lse_flag, 0, sizeof(int32_t), st));
+      b200m::ip::Ip2Params lp;
+      lp.k_per_image = k_per_image;
+      lp.pairs = pairs + 2 * p0;
+      lp.k_stride = k_stride;
+      lp.n_pairs = static_cast<int32_t>(nb);
+      lp.blocks_per_image = static_cast<int32_t>(k_stride / b200m::ip::kRows2);
+      lp.n_img = n_img;
+      lp.rowbest = nullptr;
+      lp.colkey = nullptr;
+      lp.nb = nullptr;
+      lp.z = matchability;
+      lp.maxnorm = maxnorm;
+      lp.nbw = nbuf;
+      lp.colpart = colpart;
+      lp.lse_flag = lse_flag;
+      const int grid2 = sweep_grid(nb * lp.blocks_per_image);
+      rc = dim == 256 ? launch_ip_sweep2<256, b200m::ip::kIpLse>(tmap, lp, grid2, st)
+                      : launch_ip_sweep2<128, b200m::ip::kIpLse>(tmap, lp, grid2, st);
+      if (rc) return rc;
+      b200m::ip::ip_lse_finalize_kernel<<<dim3(static_cast<unsigned>((k_stride + 255) / 256), static_cast<unsigned>(nb)), 256, 0, st>>>(
+          colpart, maxnorm, matchability, pairs + 2 * p0, k_per_image, n_img, k_stride, static_cast<int32_t>(nb), nbuf, lse_flag);
+      CUDA_TRY(cudaGetLastError());
+      ip.gate = lse_flag;      // a sum left the fp32 range around the common reference: redo the batch with per-row maxima
+    }
+    // pass 1 (two-direction form): row and column log-sum-exp -> nb; pass 2: arg-max of the log assignment
     rc = dim == 256 ? launch_ip_sweep<256, b200m::ip::kIpLse>(tmap, ip, grid, st)
                     : launch_ip_sweep<128, b200m::ip::kIpLse>(tmap, ip, grid, st);
     if (rc) return rc;

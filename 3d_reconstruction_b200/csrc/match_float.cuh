@@ -72,6 +72,7 @@ struct IpParams {
   // dual-softmax head only (kIpLse writes, kIpBiasArgmax reads):
   const float* z;               // [n_img, k_stride] matchability logits (lightglue.py:224-225)
   float* nb;                    // [2][n_pairs][k_stride] logsigmoid(z_row) - log-sum-exp of the row
+  const int32_t* gate;          // optional: the launch does nothing unless *gate != 0 (fallback of the single-sweep log-sum-exp)
 };
 
 // kind::f16 instruction descriptor: bf16 A and B (K-major), fp32 accumulator
@@ -171,6 +172,7 @@ ip_sweep_kernel(const __grid_constant__ CUtensorMap tmap, const IpParams p) {
   constexpr int kNKB = kDim / kKB;          // K-blocks per descriptor
   extern __shared__ uint8_t smem_raw[];
   IpSmem<kDim>& sm = *reinterpret_cast<IpSmem<kDim>*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  if (p.gate && __ldg(p.gate) == 0) return;
 
   const uint32_t warp = threadIdx.x >> 5;
   const uint32_t lane = lane_id();

@@ -59,7 +59,33 @@ struct Ip2Params {
   float2* rowbest;              // out [n_pairs][k_stride]: (best score, best column) of every query row
   int32_t* colkey;              // out [n_pairs][k_stride]: ordered key of every train column's maximum (pre-set to kColKeyNone)
   const float* nb;              // head only: [2][n_pairs][k_stride] logsigmoid(z) - log-sum-exp (written by the kIpLse sweep)
+  // kIpLse (single-sweep log-sum-exp, see the epilogue) only:
+  const float* z;               // [n_img, k_stride] matchability logits
+  const float* maxnorm;         // [n_img] largest squared row norm of every image (ip_maxnorm_kernel)
+  float* nbw;                   // out: nb, direction 0 (rows); direction 1 is written by ip_lse_finalize_kernel
+  float* colpart;               // out [n_pairs][4 * blocks_per_image][k_stride]: column sums of exp over 32 rows x 2 M-tiles
+  int32_t* lse_flag;            // out: set when a sum left the fp32 range (the caller re-runs the batch on the two-direction sweep)
 };
+
+constexpr float kLseTiny = 7.9e-31f;   // 2^-100: a sum below it had its largest term within 2^26 of the smallest normal
+
+// Column sums over the 32 lanes of a warp for 32 columns at once: c[k] (k = 0..31) holds this lane's value of
+// column k; afterwards c[0] of lane l is the sum over all lanes of column l. Butterfly: at every step a lane keeps
+// one half of its columns and hands the other half to its partner -- 31 shuffles for 32 columns instead of 5 each.
+__device__ __forceinline__ float warp_colsum32(float (&c)[32], uint32_t lane) {
+#pragma unroll
+  for (int w = 16; w >= 1; w >>= 1) {
+    const bool up = (lane & w) != 0;
+#pragma unroll
+    for (int k = 0; k < w; ++k) {
+      const float keep = up ? c[k + w] : c[k];
+      const float send = up ? c[k] : c[k + w];
+      c[k] = keep + __shfl_xor_sync(0xffffffffu, send, w);
+    }
+  }
+  return c[0];
+}
+
 
 // order-preserving map fp32 -> int32 (compares like the floats, -0 just below +0)
 __device__ __forceinline__ int ordered_key(float f) {
@@ -95,7 +121,7 @@ __device__ __forceinline__ int ip_locate8(const int (&keep)[8], float best, int 
 template <int kDim, int kMode>
 __global__ void __launch_bounds__(kThreads, 1)
 ip_sweep2_kernel(const __grid_constant__ CUtensorMap tmap, const Ip2Params p) {
-  static_assert(kMode == kIpArgmax || kMode == kIpBiasArgmax, "the single-sweep kernel has the two arg-max modes");
+  static_assert(kMode == kIpArgmax || kMode == kIpBiasArgmax || kMode == kIpLse, "arg-max, head arg-max or log-sum-exp");
   using Smem = Ip2Smem<kDim>;
   constexpr int kNKB = Smem::kNKB;
   constexpr int kAStages = Smem::kAStages;
@@ -220,6 +246,87 @@ ip_sweep2_kernel(const __grid_constant__ CUtensorMap tmap, const Ip2Params p) {
       const bool ok0 = r0 < n_rows, ok1 = r1 < n_rows;
       const bool full_rows = n_rows == kRows2;          // warp-uniform
       const int64_t obase = static_cast<int64_t>(pair) * p.k_stride;
+      if constexpr (kMode == kIpLse) {
+        // ---- log-sum-exp of every row AND every column of sim (lightglue.py:196-208) from ONE sweep.
+        // Reference point of the exponentials: ref = |longest query row| * |longest train row| >= every sim[i, j]
+        // (Cauchy-Schwarz), the same for the whole pair, so that exp(sim - ref) <= 1 serves the row sums and the
+        // column sums alike -- one ex2 per score. A row / column whose largest term sits more than ~ 69 nats below
+        // ref would lose it to the fp32 range: such sums raise lse_flag and the caller falls back.
+        const float ref = sqrtf(__ldg(p.maxnorm + row_img) * __ldg(p.maxnorm + col_img));
+        const float ref2 = ref * kLog2e;
+        float rs0 = 0.f, rs1 = 0.f;
+        float csum[32];
+        float* cpart = p.colpart + (static_cast<int64_t>(pair) * (4 * p.blocks_per_image) + blk * 4 + quad) * p.k_stride;
+        for (int t = static_cast<int>((tp + 2 - (t_seen & 1)) & 1); t < ntiles; t += 2) {
+          mbar_wait(&sm.t_full[tp], my_it & 1);
+          tc_fence_after();
+          ++my_it;
+#pragma unroll
+          for (int s = 0; s < 4; ++s) {
+            const int c0 = t * kColsF + h * 64 + s * 16;
+            int va[16], vb[16];
+            tmem_ld_32x16(taddr + s * 16, va);
+            tmem_ld_32x16(taddr + kColsF + s * 16, vb);
+            tmem_ld_fence16(va);
+            tmem_ld_fence16(vb);
+            if (s == 3) {
+              tc_fence_before();
+              __syncwarp();
+              if (lane == 0) mbar_arrive(&sm.t_empty[tp]);
+            }
+            if (c0 + 16 > n_cols) {                      // ragged end: exp -> 0
+#pragma unroll
+              for (int j = 0; j < 16; ++j)
+                if (c0 + j >= n_cols) { va[j] = __float_as_int(kLseFloor); vb[j] = __float_as_int(kLseFloor); }
+            }
+            if (!full_rows) {                            // rows past the image add nothing to a column
+#pragma unroll
+              for (int j = 0; j < 16; ++j) {
+                if (!ok0) va[j] = __float_as_int(kLseFloor);
+                if (!ok1) vb[j] = __float_as_int(kLseFloor);
+              }
+            }
+            float a0 = 0.f, a1 = 0.f, b0 = 0.f, b1 = 0.f;
+#pragma unroll
+            for (int j = 0; j < 16; j += 2) {
+              const float ea0 = exp2f(fmaf(__int_as_float(va[j]), kLog2e, -ref2));
+              const float ea1 = exp2f(fmaf(__int_as_float(va[j + 1]), kLog2e, -ref2));
+              const float eb0 = exp2f(fmaf(__int_as_float(vb[j]), kLog2e, -ref2));
+              const float eb1 = exp2f(fmaf(__int_as_float(vb[j + 1]), kLog2e, -ref2));
+              a0 += ea0; a1 += ea1; b0 += eb0; b1 += eb1;
+              csum[(s & 1) * 16 + j] = ea0 + eb0;
+              csum[(s & 1) * 16 + j + 1] = ea1 + eb1;
+            }
+            rs0 += a0 + a1;
+            rs1 += b0 + b1;
+            if (s & 1) {
+              const float mine = warp_colsum32(csum, lane);
+              const int col = t * kColsF + h * 64 + (s >> 1) * 32 + static_cast<int>(lane);
+              if (col < n_cols) cpart[col] = mine;       // every (pair, block, quadrant, column) is written exactly once
+            }
+          }
+        }
+        t_seen += ntiles;
+        if (e > 0) {
+          sm.rowmerge[par][e - 1][r0] = make_float2(rs0, 0.f);
+          sm.rowmerge[par][e - 1][r1] = make_float2(rs1, 0.f);
+        }
+        named_bar_sync(kEpiBarrier, kEpiWarps * 32);
+        if (e == 0) {
+#pragma unroll
+          for (int m = 0; m < 2; ++m) {
+            const int r = m ? r1 : r0;
+            if (r >= n_rows) continue;
+            float ss = m ? rs1 : rs0;
+#pragma unroll
+            for (int oo = 0; oo < 3; ++oo) ss += sm.rowmerge[par][oo][r].x;
+            if (!(ss >= kLseTiny) || ss > 3.0e38f) atomicOr(p.lse_flag, 1);
+            const int64_t row = static_cast<int64_t>(blk) * kRows2 + r;
+            p.nbw[obase + row] = log_sigmoid(__ldg(p.z + static_cast<int64_t>(row_img) * p.k_stride + row)) - (ref + logf(ss));
+          }
+        }
+        continue;
+      }
       float best0 = kNegInf, best1 = kNegInf;
       int bidx0 = -1, bidx1 = -1;
       int keep0[8], keep1[8];
@@ -382,6 +489,53 @@ ip_finalize2_kernel(const float2* __restrict__ rowbest, const int32_t* __restric
   }
   __syncthreads();
   if (threadIdx.x == 0) out_count[pair] = running;
+}
+
+// Largest squared row norm per image (bf16 rows, fp32 sum): the reference point of the single-sweep log-sum-exp.
+// maxnorm must be zeroed first; non-negative floats order like their bit patterns.
+template <int kDim>
+__global__ void __launch_bounds__(256)
+ip_maxnorm_kernel(const uint16_t* __restrict__ desc, const int32_t* __restrict__ k_per_image, int64_t k_stride,
+                  int32_t n_img, float* __restrict__ maxnorm) {
+  const int64_t row = static_cast<int64_t>(blockIdx.x) * 8 + (threadIdx.x >> 5);       // one warp per row
+  const int img = static_cast<int>(row / k_stride);
+  if (img >= n_img) return;
+  const int r = static_cast<int>(row - static_cast<int64_t>(img) * k_stride);
+  if (r >= min(max(__ldg(k_per_image + img), 0), static_cast<int>(k_stride))) return;
+  const uint32_t lane = threadIdx.x & 31;
+  const uint2* src = reinterpret_cast<const uint2*>(desc + row * kDim);                   // four bf16 per lane and step
+  float acc = 0.f;
+#pragma unroll
+  for (int i = 0; i < kDim / 128; ++i) {
+    const uint2 v = __ldg(src + i * 32 + lane);
+    const float x0 = __uint_as_float(v.x << 16), x1 = __uint_as_float(v.x & 0xffff0000u);
+    const float x2 = __uint_as_float(v.y << 16), x3 = __uint_as_float(v.y & 0xffff0000u);
+    acc += x0 * x0 + x1 * x1 + x2 * x2 + x3 * x3;
+  }
+#pragma unroll
+  for (int d = 16; d >= 1; d >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, d);
+  if (lane == 0) atomicMax(reinterpret_cast<int*>(maxnorm + img), __float_as_int(acc));
+}
+
+// Columns of the single-sweep log-sum-exp: the partial sums of every (row block, lane quadrant) in a fixed order
+// -> nb[1][pair][column] = logsigmoid(z_column) - log-sum-exp over the rows.
+__global__ void __launch_bounds__(256)
+ip_lse_finalize_kernel(const float* __restrict__ colpart, const float* __restrict__ maxnorm, const float* __restrict__ z,
+                       const int32_t* __restrict__ pairs, const int32_t* __restrict__ k_per_image, int n_img, int64_t k_stride,
+                       int n_pairs, float* __restrict__ nb, int32_t* __restrict__ lse_flag) {
+  const int pair = blockIdx.y;
+  const PairInfo pi = load_pair(pairs, k_per_image, pair, n_img, k_stride);
+  const int col = blockIdx.x * blockDim.x + threadIdx.x;
+  if (col >= pi.kt || pi.kq <= 0) return;
+  const int parts_all = static_cast<int>(4 * (k_stride / kRows2));
+  const int parts = 4 * ((pi.kq + kRows2 - 1) / kRows2);
+  const float* src = colpart + static_cast<int64_t>(pair) * parts_all * k_stride + col;
+  float ss = 0.f;
+  for (int q = 0; q < parts; ++q) ss += src[static_cast<int64_t>(q) * k_stride];
+  if (!(ss >= kLseTiny) || ss > 3.0e38f) atomicOr(lse_flag, 1);
+  const float ref = sqrtf(__ldg(maxnorm + pi.qi) * __ldg(maxnorm + pi.ti));
+  nb[(static_cast<int64_t>(n_pairs) + pair) * k_stride + col] =
+      log_sigmoid(__ldg(z + static_cast<int64_t>(pi.ti) * k_stride + col)) - (ref + logf(ss));
 }
 
 }  // namespace ip

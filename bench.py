@@ -483,9 +483,15 @@ def main():
     sampler.join(timeout=3)
     prof = pkg.profile_read()
     pkg.set_option("profile", 0)
-    ms_step = max_over_ranks(e0.elapsed_time(e1) / args.steps)
+    ms_mine = e0.elapsed_time(e1) / args.steps
+    ms_step = max_over_ranks(ms_mine)
     value = P_all / (ms_step / 1e3)
     stats = pkg.match_stats(workspace)
+    ms_ranks = [ms_mine]
+    if world > 1:                       # per-rank step times: how much of the max is skew between the GPUs
+        t = torch.zeros((world,), dtype=torch.float64, device=dev)
+        dist.all_gather_into_tensor(t, torch.tensor([ms_mine], dtype=torch.float64, device=dev))
+        ms_ranks = [round(float(x), 3) for x in t.tolist()]
 
     # every match record of this rank -> 64-bit digest; counts and digests add over the ranks (mod 2^64): the same
     # pair of numbers at every N <=> the N-GPU lists are the 1-GPU lists (outside the timed region)
@@ -617,7 +623,7 @@ def main():
             "metric": METRIC, "value": value, "unit": "pairs/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "u8",
             "data": "synthetic",
-            "config": {"workload": WORKLOAD, "n_img": n_img, "k": K, "d": D, "pairs": P_all, "pairs_per_rank": P,
+            "config": {"workload": WORKLOAD, "n_img": n_img, "k": K, "d": D, "pairs": P_all, "pairs_per_rank": P, "ms_per_step_ranks": ms_ranks,
                        "cap": CAP, "seed": SEED, "matches_total": matches_total, "result_digest": f"{result_digest:016x}",
                        "e2e_lists_equal_value_lists": e2e_same,
                        "l2": "inputs larger than L2: 539 MB bank, every step sweeps all of it",

@@ -143,3 +143,29 @@ def test_assignment_head_module_vs_fp32_restatement(pkg):
         q, t = out["matches"][i][:, 0], out["matches"][i][:, 1]
         assert torch.equal(got[q], t) and torch.equal(out["matches1"][i][t], q)
         assert torch.all(out["scores"][i] > 0.1)
+
+
+@pytest.mark.parametrize("case", ["all_rows_long", "one_long_row"])
+def test_assign_scores_outside_the_common_reference_range(pkg, case):
+    """The single-sweep log-sum-exp measures every exponential of a pair from ONE reference point (the product of the
+    longest row norms). Rows whose largest score lies far below it (> ~69 nats) would lose their sums to the fp32
+    range: the kernel flags that and the batch is redone with per-row maxima. Long descriptors (|d| = 30: scores up
+    to 900) and a single outlier row that inflates the reference must give the oracle's result all the same."""
+    dim, m, n = 128, 600, 520
+    gen = torch.Generator().manual_seed(77)
+    world = torch.nn.functional.normalize(torch.randn(900, dim, generator=gen), dim=1)
+    d0 = torch.nn.functional.normalize(world[torch.randperm(900, generator=gen)[:m]] + 0.04 * torch.randn(m, dim, generator=gen), dim=1)
+    d1 = torch.nn.functional.normalize(world[torch.randperm(900, generator=gen)[:n]] + 0.04 * torch.randn(n, dim, generator=gen), dim=1)
+    if case == "all_rows_long":
+        d0, d1 = 30.0 * d0, 30.0 * d1
+    else:
+        d0, d1 = 4.5 * d0, 4.5 * d1
+        d0[17] *= 40.0                                     # |d| = 180: the reference point moves to 810
+    d0, d1 = d0.to(torch.bfloat16).float().numpy(), d1.to(torch.bfloat16).float().numpy()
+    z0 = (1.0 + 1.5 * torch.randn(m, generator=gen)).numpy()
+    z1 = (1.0 + 1.5 * torch.randn(n, generator=gen)).numpy()
+    for th in (None, 0.1):
+        q, t, s = _run_pair(pkg, d0, d1, z0, z1, th)
+        _, _, _, (m0, _, ms0, _), _ = oracle_float.assign(d0, d1, z0, z1, th)
+        _compare(q, t, s, m0, ms0, min_agree=0.99)
+        assert len(q) > 50
