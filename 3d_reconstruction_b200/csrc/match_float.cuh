@@ -130,6 +130,14 @@ __device__ __forceinline__ int ip_locate(const int (&keep)[16], float best, int 
   return bidx + j;
 }
 
+// ex2.approx.ftz.f32, one MUFU instruction: exp2f() without -use_fast_math wraps it in a range test and two scalings
+// for results below 2^-126; such terms are below fp32 resolution of every sum they enter here.
+__device__ __forceinline__ float ex2_ftz(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 // sixteen columns of one row: online log-sum-exp, (m, s) with sum_j exp(v_j) = s * exp(m)
 __device__ __forceinline__ void lse_process16(int (&v)[16], int c0, int n_cols, float& m, float& s) {
   if (c0 + 16 > n_cols) {
@@ -144,8 +152,8 @@ __device__ __forceinline__ void lse_process16(int (&v)[16], int c0, int n_cols, 
   float acc0 = 0.f, acc1 = 0.f;
 #pragma unroll
   for (int j = 0; j < 16; j += 2) {
-    acc0 += exp2f(fmaf(__int_as_float(v[j]), kLog2e, -mb));
-    acc1 += exp2f(fmaf(__int_as_float(v[j + 1]), kLog2e, -mb));
+    acc0 += ex2_ftz(fmaf(__int_as_float(v[j]), kLog2e, -mb));
+    acc1 += ex2_ftz(fmaf(__int_as_float(v[j + 1]), kLog2e, -mb));
   }
   s += acc0 + acc1;
 }

@@ -289,10 +289,10 @@ ip_sweep2_kernel(const __grid_constant__ CUtensorMap tmap, const Ip2Params p) {
             float a0 = 0.f, a1 = 0.f, b0 = 0.f, b1 = 0.f;
 #pragma unroll
             for (int j = 0; j < 16; j += 2) {
-              const float ea0 = exp2f(fmaf(__int_as_float(va[j]), kLog2e, -ref2));
-              const float ea1 = exp2f(fmaf(__int_as_float(va[j + 1]), kLog2e, -ref2));
-              const float eb0 = exp2f(fmaf(__int_as_float(vb[j]), kLog2e, -ref2));
-              const float eb1 = exp2f(fmaf(__int_as_float(vb[j + 1]), kLog2e, -ref2));
+              const float ea0 = ex2_ftz(fmaf(__int_as_float(va[j]), kLog2e, -ref2));
+              const float ea1 = ex2_ftz(fmaf(__int_as_float(va[j + 1]), kLog2e, -ref2));
+              const float eb0 = ex2_ftz(fmaf(__int_as_float(vb[j]), kLog2e, -ref2));
+              const float eb1 = ex2_ftz(fmaf(__int_as_float(vb[j + 1]), kLog2e, -ref2));
               a0 += ea0; a1 += ea1; b0 += eb0; b1 += eb1;
               csum[(s & 1) * 16 + j] = ea0 + eb0;
               csum[(s & 1) * 16 + j + 1] = ea1 + eb1;
