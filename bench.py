@@ -244,6 +244,59 @@ def secondary_c2(pkg, torch, dev, int8_peak):
     return r
 
 
+def secondary_knn2(pkg, torch, dev, int8_peak):
+    """The literal cv2.BFMatcher(NORM_L2).knnMatch(k=2) table (best + second-best train row of EVERY query row) on
+    BASELINE config 3 shapes: 512 pairs over 33 images x 16,384; chunk pipeline against the exact top-2 sweep, outputs
+    compared bit for bit."""
+    syn = importlib.import_module("3d_reconstruction_b200.synthetic")
+    n_img, k = 33, 16384
+    desc, kpi = syn.make_bank_tensor(n_img, k, seed=SEED, device=dev)
+    bank = pkg.DescriptorBank.from_packed(desc, kpi)
+    pairs = torch.from_numpy(pkg.blocked_order(pkg.exhaustive_pairs(n_img))[:512]).to(dev)
+    ws = torch.empty(int(pkg._lib.lib().b200m_workspace_bytes(k, len(pairs))), dtype=torch.uint8, device=dev)
+    res = {}
+    r = {}
+    for name, pipeline in (("chunk_pipeline", 2), ("exact_top2_sweep", 1)):
+        pkg.set_option("pipeline", pipeline)
+        try:
+            res[name] = pkg.knn2_pairs(bank, pairs, workspace=ws)
+            torch.cuda.synchronize()
+            best, med = _timed(torch, lambda: pkg.knn2_pairs(bank, pairs, workspace=ws), 3)
+        finally:
+            pkg.set_option("pipeline", 2)
+        r[name] = _int8_line(len(pairs), k, best, med, int8_peak)
+    a, b = res["chunk_pipeline"], res["exact_top2_sweep"]
+    r["identical_outputs"] = bool(torch.equal(a[0], b[0]) and torch.equal(a[1].view(torch.int32), b[1].view(torch.int32)))
+    r["workload"] = "knnMatch(k=2) tables of 512 pairs over 33 images x 16384 u8 descriptors"
+    return r
+
+
+def secondary_real_sift(pkg, torch, dev, int8_peak):
+    """BASELINE.json configs[0] as a throughput figure: every SIFT descriptor of the reference's DSC_0001 / DSC_0002
+    (tests/golden/sift_full.npz, 56,041 x 52,421), both directions, the whole rule. A strongly overlapping real pair:
+    a third of the rows survive the Lowe test, so refine and the mutual check cost far more than on the headline bank."""
+    path = os.path.join(ROOT, "tests", "golden", "sift_full.npz")
+    if not os.path.exists(path):
+        return {"unavailable": "tests/golden/sift_full.npz not found"}
+    g = np.load(path)
+    bank = pkg.DescriptorBank.from_arrays([g["q"], g["t"]], device=dev)
+    pairs = torch.tensor([[0, 1], [1, 0]] * 8, dtype=torch.int32, device=dev)
+    ks = int(bank.k_stride)
+    ws = torch.empty(int(pkg._lib.lib().b200m_workspace_bytes(ks, len(pairs))), dtype=torch.uint8, device=dev)
+    out = pkg.match_pairs(bank, pairs, cap=ks, workspace=ws)
+    torch.cuda.synchronize()
+    out.check_overflow()
+    best, med = _timed(torch, lambda: pkg.match_pairs(bank, pairs, cap=ks, out=out, workspace=ws), 3)
+    st = pkg.match_stats(ws)
+    kq, kt = int(g["q"].shape[0]), int(g["t"].shape[0])
+    ops = 2.0 * kq * kt * 128 * len(pairs)
+    return {"pairs": len(pairs), "pairs_per_s": len(pairs) / med, "ms": 1e3 * med, "tops": ops / med / 1e12,
+            "frac_of_peak": ops / med / 1e12 / int8_peak if int8_peak else None,
+            "matches_per_pair": int(out.count[0].item()), "matches_expected_cv2": int(g["n_mutual_full"]),
+            "rows": {kk: st[kk] for kk in ("rows", "rows_chunk_evaluated", "rows_fallback", "rows_ratio_verify")},
+            "workload": f"real SIFT, DSC_0001 <-> DSC_0002, {kq} x {kt} descriptors, ratio 0.75 + mutual, both directions x 8"}
+
+
 def secondary_c4(pkg, dmod, torch, dist, dev, rank, world, int8_peak):
     """BASELINE.json configs[3]: 2,000 images x 8,192 keypoints, each image against the next 32 (63,472 pairs).
     One GPU: the whole bank resident. N GPUs: rank 0 holds the bank on the host and every rank receives only its
@@ -613,6 +666,11 @@ def main():
         torch.cuda.empty_cache()
         if world == 1:
             secondary["c2"] = secondary_c2(pkg, torch, dev, int8_peak)
+            torch.cuda.empty_cache()
+            secondary["knn2"] = secondary_knn2(pkg, torch, dev, int8_peak)
+            torch.cuda.empty_cache()
+            secondary["c1_real_sift"] = secondary_real_sift(pkg, torch, dev, int8_peak)
+            torch.cuda.empty_cache()
             secondary.update(secondary_c5(pkg, torch, dev, peaks))
 
     if rank == 0:
