@@ -5,9 +5,10 @@
 //   lightglue/lightglue.py:223      sim = einsum('bmd,bnd->bmn')              one dense contraction per pair
 //   lightglue/lightglue.py:237      scores.max(2)  -> per-thread running (best, column) as before
 //                                   scores.max(1)  -> per column: max over the two rows a thread owns (FMNMX),
-//                                                     order-preserving integer key, REDUX.MAX over the warp's 32
-//                                                     lanes (one warp instruction per column), one 32-bit
-//                                                     atomicMax per (warp, column) into colkey[pair][column]
+//                                                     redux.sync.max.f32 over the warp's 32 lanes (CREDUX.MAX.F32,
+//                                                     one warp instruction per column), order-preserving integer
+//                                                     key of the result and one 32-bit atomicMax per (warp, column)
+//                                                     into colkey[pair][column]
 //   lightglue/lightglue.py:239-250  mutual check + threshold in ip_finalize2_kernel: row r keeps its partner j iff
 //                                   its value IS the column maximum (same accumulator value on both sides, so the
 //                                   comparison is exact) and r is the lowest such row (claim array, atomicMin).
@@ -87,7 +88,15 @@ __device__ __forceinline__ float warp_colsum32(float (&c)[32], uint32_t lane) {
 }
 
 
-// order-preserving map fp32 -> int32 (compares like the floats, -0 just below +0)
+// redux.sync.max.f32 (sm_100a: CREDUX.MAX.F32): the maximum over the warp's 32 lanes in one instruction, no integer key
+__device__ __forceinline__ float warp_max_f32(float v) {
+  float r;
+  asm volatile("redux.sync.max.f32 %0, %1, 0xffffffff;" : "=f"(r) : "f"(v));
+  return r;
+}
+
+// order-preserving map fp32 -> int32 (compares like the floats, -0 just below +0; callers add +0.0f first, so that
+// the two zeros -- equal as scores -- share a key)
 __device__ __forceinline__ int ordered_key(float f) {
   const int b = __float_as_int(f);
   return b ^ ((b >> 31) & 0x7fffffff);
@@ -393,14 +402,13 @@ ip_sweep2_kernel(const __grid_constant__ CUtensorMap tmap, const Ip2Params p) {
           // compare + select per column on the busy ALU pipe), then every lane picks up one column for the atomic.
 #pragma unroll
           for (int j = 0; j < 16; ++j) {
-            const int key = ordered_key(fmaxf(__int_as_float(va[j]), __int_as_float(vb[j])));
-            const int m = __reduce_max_sync(0xffffffffu, key);
-            if (lane == 0) cx[s >> 1][(s & 1) * 16 + j] = m;
+            const float m = warp_max_f32(fmaxf(__int_as_float(va[j]), __int_as_float(vb[j])));
+            if (lane == 0) cx[s >> 1][(s & 1) * 16 + j] = __float_as_int(m);
           }
           if (s & 1) {
             __syncwarp();
             const int col = t * kColsF + h * 64 + (s >> 1) * 32 + static_cast<int>(lane);
-            if (col < n_cols) atomicMax(colkey + col, cx[s >> 1][lane]);
+            if (col < n_cols) atomicMax(colkey + col, ordered_key(__int_as_float(cx[s >> 1][lane]) + 0.0f));
           }
         }
       }
@@ -460,7 +468,7 @@ ip_finalize2_kernel(const float2* __restrict__ rowbest, const int32_t* __restric
     for (int r = threadIdx.x; r < kq; r += kBlock) {
       const float2 v = fwd[r];
       const int j = __float_as_int(v.y);
-      if (j >= 0 && j < kt && ordered_key(v.x) == colkey[base + j]) atomicMin(claim + base + j, r);
+      if (j >= 0 && j < kt && ordered_key(v.x + 0.0f) == colkey[base + j]) atomicMin(claim + base + j, r);
     }
     __threadfence();
   }

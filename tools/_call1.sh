@@ -1,2 +1,2 @@
-timeout 400 ncu --set full --clock-control none --import-source on -k regex:ip_sweep2_kernel -s 2 -c 1 -f -o gpurun_out/r02y_lse256 python tools/prof_float_case.py 256 1024 head > gpurun_out/r02y_ncu1.log 2>&1; echo "ncu rc=$?"
-timeout 400 ncu --set full --clock-control none --import-source on -k regex:ip_sweep2_kernel -s 2 -c 1 -f -o gpurun_out/r02y_lse128 python tools/prof_float_case.py 128 1024 head > gpurun_out/r02y_ncu2.log 2>&1; echo "ncu rc=$?"
+timeout 900 python -m pytest tests/test_gpu_assign.py tests/test_gpu_float.py -m gpu -x -q > gpurun_out/r03a_tests.log 2>&1; echo "tests rc=$?"; tail -4 gpurun_out/r03a_tests.log
+timeout 300 python tools/perf_float.py > gpurun_out/r03a_perf_float.log 2>&1; echo "float rc=$?"; head -5 gpurun_out/r03a_perf_float.log | cut -c1-260
