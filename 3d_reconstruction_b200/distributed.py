@@ -314,26 +314,35 @@ def match_pairs_host(desc_host_local: torch.Tensor, k_per_image, n_img: int, pai
             if p1 > p0:
                 M.match_pairs(bank, pd[p0:p1], ratio=ratio, mutual=mutual, cap=cap, out=M._out_rows(out, p0, p1), workspace=ws_t)
 
-        prepared = torch.cuda.Event()
+        # Every block is prepared (norms, padding, norm sort) as it lands; between two blocks only as many local pairs
+        # are matched as the next block's upload lasts (~66,000 / k_stride pairs per image on a B200 behind PCIe 5), so
+        # that the GPU is busy during the upload but the LAST preparation -- which the other ranks wait for -- is not
+        # queued behind the bulk of the local pairs: those run while the slices travel.
+        avail_end = {sg[0]: sg[2] for sg in segs}           # block -> end of the local pairs that need no later block
+        done = 0
         for b in range(n_blocks):
             main.wait_event(landed[b])
             bank.prepare_range(lo + bounds[b], bounds[b + 1] - bounds[b])
-            if b == n_blocks - 1:
-                prepared.record(main)                       # the whole slice is ready for the other ranks
-                mark("upload_prepare", 1)
-                if symm is not None:                        # 3: the exchange, on its own stream: the copy engines do it
-                    symm.stream.wait_event(prepared)
-                    with torch.cuda.stream(symm.stream):
-                        mark("exchange", 0, symm.stream)
-                        symm.pull_all(n_loc)
-                        mark("exchange", 1, symm.stream)
-                        exchanged = torch.cuda.Event()
-                        exchanged.record(symm.stream)
             if b == 0:
                 mark("match_local", 0)
-            for sg in segs:                                 # local pairs whose images are resident by now
-                if sg[0] == b:
-                    match(sg[1], sg[2])
+            if b < n_blocks - 1:
+                end_b = max([e for bb, e in avail_end.items() if bb <= b], default=0)
+                budget = -(-(bounds[b + 2] - bounds[b + 1]) * 66000 // ks)
+                take = min(end_b, done + budget)
+                match(done, take)
+                done = max(done, take)
+        mark("upload_prepare", 1)
+        if symm is not None:                                # 3: the exchange, on its own stream: the copy engines do it
+            prepared = torch.cuda.Event()
+            prepared.record(main)                           # the whole slice is ready for the other ranks
+            symm.stream.wait_event(prepared)
+            with torch.cuda.stream(symm.stream):
+                mark("exchange", 0, symm.stream)
+                symm.pull_all(n_loc)
+                mark("exchange", 1, symm.stream)
+                exchanged = torch.cuda.Event()
+                exchanged.record(symm.stream)
+            match(done, n_local)                            # the rest of the local pairs, under the exchange
         if symm is not None:
             mark("match_local", 1)
             main.wait_event(exchanged)

@@ -168,9 +168,12 @@ int b200m_match_pairs_bf16(const void* bank_bf16, const int32_t* k_per_image, in
  * and the match list (:417-426).
  *   mdesc_bf16    bf16 [n_img, k_stride, dim]: final_proj(desc) / dim^0.25 (:220-222), dim 128 or 256
  *   matchability  float32 [n_img, k_stride]: the logits z = matchability(desc) (:224-225)
- * Per pair and direction the kernel sweeps the similarity twice: pass 1 row log-sum-exp (both
- * directions = row and column soft-max normalisers), pass 2 the arg-max of
+ * Two tensor sweeps per pair (option "float_sweep" = 0, default): pass 1 the log-sum-exp of every row AND every
+ * column of sim from one sweep (all exponentials measured from one reference point, the product of the longest row
+ * norms; sums that leave the fp32 range around it are detected on the device and the batch is redone by the
+ * two-direction sweep with per-row maxima), pass 2 row arg-max + column maxima of
  *   score[i,j] = 2 sim[i,j] - lse_row[i] - lse_col[j] + logsigmoid(z0[i]) + logsigmoid(z1[j]).
+ * ("float_sweep" = 1: one sweep per direction and pass, four per pair.)
  * A row i matches j when j = arg-max_j score[i,:], i = arg-max_i score[:,j] and (use_threshold != 0)
  * exp(score) > filter_threshold. out_score = exp(score) (= matching_scores0 of the reference);
  * other outputs as b200m_match_pairs_u8. With use_threshold == 0 the list holds every mutual pair,
@@ -227,7 +230,8 @@ int b200m_five_point_f64(const double* x0, const double* x1, double* out_E, int3
  *   "chunk"     columns per chunk of the chunk sweep: 64 (default, kernel 5 only) or 32
  *   "grid"      number of persistent CTAs, 0 = one per SM (default)
  *   "batch"     pairs per internal batch, 0 = default
- *   "float_sweep" 0 = float path as ONE tensor sweep per pair, column maxima fused (default), 1 = one sweep per direction
+ *   "float_sweep" 0 = float path as ONE tensor sweep per pair and pass: column maxima / column log-sum-exp fused into the
+ *               row sweep (default), 1 = one sweep per direction
  *   "knn_eval"  b200m_knn2_sorted_u8, exact evaluation of the two winning chunks: 0 = tensor cores over gathered
  *               rows (default), 1 = dp4a
  *   "profile"   1 = time sweep launches with CUDA events (see b200m_profile_read) */
