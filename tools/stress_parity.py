@@ -47,6 +47,15 @@ def main(rounds=40, seed=0):
         mutual = bool(rng.integers(0, 2))
         res = pkg.match_pairs(bank, pairs, ratio=ratio, mutual=mutual)
         res.check_overflow()
+        kidx, kdist = pkg.knn2_pairs(bank, pairs)           # the knnMatch(k=2) face on the same bank (chunk pipeline + tensor-core evaluator)
+        kidx, kdist = kidx.cpu().numpy(), kdist.cpu().numpy()
+        for pi, (a, b) in enumerate(pairs):
+            eidx, edist, _ = oracle_int.knn2(descs[a], descs[b])
+            n = len(descs[a])
+            if not (np.array_equal(kidx[pi, :n], eidx) and np.array_equal(kdist[pi, :n].view(np.uint32), np.asarray(edist, np.float32).view(np.uint32))):
+                bad = np.nonzero((kidx[pi, :n] != eidx).any(1))[0][:5]
+                print("KNN MISMATCH round", r, "kind", kind, "pair", (a, b), "sizes", sizes[a], sizes[b], "rows", bad, flush=True)
+                sys.exit(1)
         for (a, b), (q, t, d) in zip(pairs, res.to_lists()):
             eq, et, ed = oracle_int.match(descs[a], descs[b], ratio, mutual)
             ok = np.array_equal(q, eq) and np.array_equal(t, et) and np.array_equal(
@@ -56,7 +65,7 @@ def main(rounds=40, seed=0):
                       "got", len(q), "expected", len(eq), flush=True)
                 sys.exit(1)
             checked += 1
-    print("stress parity OK:", checked, "pairs over", rounds, "banks", flush=True)
+    print("stress parity OK:", checked, "pairs over", rounds, "banks (match lists and knnMatch tables)", flush=True)
 
 
 if __name__ == "__main__":
