@@ -401,7 +401,7 @@ chunk_sweep256_kernel(const __grid_constant__ CUtensorMap tmap, const ChunkParam
         int pair, blk, row0, col_img, n_rows, ntiles, nm;
         if (!decode(item, pair, blk, row0, col_img, n_rows, ntiles, nm)) continue;
         const uint32_t as = a_it % kAStages, aph = (a_it / kAStages) & 1;
-        mbar_wait(&sm.a_empty[as], aph ^ 1);
+        mbar_wait_ahead(&sm.a_empty[as], aph ^ 1);
         mbar_arrive_expect_tx(&sm.a_full[as], nm * kMBytes);
         for (int m = 0; m < nm; ++m) tma_load_2d(sm.a[as][m], &tmap, 0, row0 + m * kTM, &sm.a_full[as]);
         ++a_it;
@@ -409,7 +409,7 @@ chunk_sweep256_kernel(const __grid_constant__ CUtensorMap tmap, const ChunkParam
         for (int t = 0; t < ntiles; ++t) {
           const int32_t crow = static_cast<int32_t>(crow0 + t * kTT);
           const uint32_t bs = b_it % kBStages, bph = (b_it / kBStages) & 1;
-          mbar_wait(&sm.b_empty[bs], bph ^ 1);
+          mbar_wait_ahead(&sm.b_empty[bs], bph ^ 1);
           mbar_arrive_expect_tx(&sm.b_full[bs], kBBytes);
           tma_load_2d(sm.b[bs], &tmap, 0, crow, &sm.b_full[bs]);
           tma_load_2d(sm.b[bs] + kBBytes / 2, &tmap, 0, crow + 128, &sm.b_full[bs]);

@@ -77,6 +77,31 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   }
 }
 
+// Wait of a thread that runs AHEAD of its consumers (the TMA producer waiting for a free ring slot): test, then sleep
+// on the timer. try_wait's NANOSLEEP.SYNCS wakes at every barrier event of the CTA (seven instructions per spurious
+// wake, per waiter); a producer several tiles ahead can afford to look only every few hundred nanoseconds.
+__device__ __forceinline__ void mbar_wait_ahead(uint64_t* bar, uint32_t parity) {
+  uint32_t polls = 0;
+  for (;;) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t"
+        "}\n"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    if (ok) return;
+    __nanosleep(300);
+    if (++polls > B200M_WAIT_LIMIT_POLLS) {
+      printf("b200m: mbarrier wait timeout (producer) block %d bar@%u parity %u\n", (int)blockIdx.x, smem_u32(bar), parity);
+      __trap();
+    }
+  }
+}
+
 // ---------------------------------------------------------------- TMA
 __device__ __forceinline__ void tma_prefetch_desc(const void* tmap) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(tmap)) : "memory");

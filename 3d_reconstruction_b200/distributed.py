@@ -221,7 +221,8 @@ def transport_in_use() -> str:
 
 def match_pairs_host(desc_host_local: torch.Tensor, k_per_image, n_img: int, pairs, ratio: float = 0.75,
                      mutual: bool = True, cap: int | None = None, device="cuda", dst: int = 0, out=None, workspace=None,
-                     staging: bool = False, events: dict | None = None, transport: str = "auto", block: int = 12):
+                     staging: bool = False, events: dict | None = None, transport: str = "auto", block: int = 12,
+                     rank_weights=None):
     """matcher.match_pairs_host over all ranks of the job: HOST descriptors in, flat HOST match lists out (on rank
     `dst`, in the order of `pairs`; None elsewhere) -- the per-pair host -> device -> host unit of
     matching.py:107-128, sharded and batched.
@@ -237,7 +238,8 @@ def match_pairs_host(desc_host_local: torch.Tensor, k_per_image, n_img: int, pai
          copy engines (symmetric memory; transport="nccl" or a failed set-up: one in-place NCCL all-gather per
          section instead, which cannot overlap the persistent matching kernels);
       4. the remaining pairs, one packed gather to `dst`, results put back into list order, pinned D2H.
-    With one rank this is matcher.match_pairs_host. events: optional dict, filled with (start, stop) CUDA events of
+    rank_weights: optional relative throughput of the ranks (identical everywhere, see rank_throughput): the
+    partition hands out pairs in that proportion. With one rank this is matcher.match_pairs_host. events: optional dict, filled with (start, stop) CUDA events of
     the phases "upload_prepare", "exchange", "match_local", "match_rest", "gather" (bench.py reports them)."""
     from . import matcher as M
     from .bank import DescriptorBank
@@ -294,7 +296,7 @@ def match_pairs_host(desc_host_local: torch.Tensor, k_per_image, n_img: int, pai
                 ev = torch.cuda.Event()
                 ev.record(copy)
                 landed.append(ev)
-        parts = partition_all_by_owner(pairs_np, ws, n_loc)
+        parts = partition_all_by_owner(pairs_np, ws, n_loc, rank_weights)
         for r, (ix, nl) in enumerate(parts):               # local pairs in the order their images land (stable)
             need = np.searchsorted(np.asarray(bounds[1:]), pairs_np[ix[:nl]].max(axis=1) - r * n_loc, side="right")
             ix[:nl] = ix[:nl][np.argsort(need.astype(np.int16), kind="stable")]
@@ -380,6 +382,27 @@ def match_pairs_host(desc_host_local: torch.Tensor, k_per_image, n_img: int, pai
             outs.append(g)
         mark("gather", 1)
         return M.FlatMatches(outs[0], outs[1], outs[2], off_list).cpu(staging)
+
+
+def rank_throughput(ms_mine: float, n_pairs_mine: int, device="cuda"):
+    """All-gather of every rank's measured pairs / ms (e.g. over warm-up steps), rounded so that every rank holds the
+    same numbers: the `weights` of scheduler.partition_by_owner / the `rank_weights` of match_pairs_host. A rank that
+    measured nothing counts as average. -> list of world_size floats (None without torch.distributed)."""
+    rank, ws = world()
+    if ws == 1:
+        return None
+    backend = dist.get_backend()
+    dev = torch.device(device) if backend == "nccl" else torch.device("cpu")
+    mine = torch.tensor([n_pairs_mine / ms_mine if ms_mine > 0 and n_pairs_mine > 0 else 0.0], dtype=torch.float64, device=dev)
+    allv = torch.zeros((ws,), dtype=torch.float64, device=dev)
+    dist.all_gather_into_tensor(allv, mine)
+    v = allv.cpu().numpy()
+    good = v > 0
+    if not good.any():
+        return None
+    v[~good] = v[good].mean()
+    v = np.clip(v / v.mean(), 0.8, 1.25)                    # a wild measurement must not starve a rank
+    return [round(float(x), 4) for x in v]
 
 
 def scatter_bank_window(desc: torch.Tensor | None, k_per_image: torch.Tensor | None, n_img: int, k_stride: int, dim: int,

@@ -79,23 +79,40 @@ def window_shard(n_img: int, window: int, world_size: int, rank: int):
     return lo, hi, halo_hi, gp - lo, gp
 
 
-def partition_by_owner(pairs: np.ndarray, world_size: int, rank: int, n_loc: int):
+def partition_by_owner(pairs: np.ndarray, world_size: int, rank: int, n_loc: int, weights=None):
     """Partition for the sharded host-buffer path: rank r OWNS images [r * n_loc, (r + 1) * n_loc) (it uploads and
     prepares them), and every pair goes to the owner of one of its two images -- of the query image when
     (query + train) is even, of the train image otherwise -- so each image hands about half of its pairs to
     either side. Ranks left above the mean by that rule (the last rank usually owns fewer images) pass the tail
     of their non-local pairs on to the ranks below it. A rank's pairs come back with the pairs BETWEEN ITS OWN
     images first (in list order): they can be matched while the rest of the bank is still travelling between
-    the GPUs. Deterministic, no communication.
+    the GPUs. Deterministic, no communication. weights: optional relative throughput of every rank (identical on
+    all ranks, e.g. all-gathered from a measured warm-up): rank r then gets about weights[r] / sum(weights) of the
+    pairs instead of 1 / world_size -- GPUs under a power cap and pair sets of different match density do not all
+    run at the same pairs/s.
     -> (pairs_of_rank, indices into `pairs`, number of leading local-only pairs)"""
     pairs = np.asarray(pairs, dtype=np.int32).reshape(-1, 2)
     if world_size <= 1:
         return pairs, np.arange(len(pairs)), len(pairs)
-    idx, n_local = partition_all_by_owner(pairs, world_size, n_loc)[rank]
+    idx, n_local = partition_all_by_owner(pairs, world_size, n_loc, weights)[rank]
     return pairs[idx], idx, n_local
 
 
-def partition_all_by_owner(pairs: np.ndarray, world_size: int, n_loc: int):
+def rank_targets(n_pairs: int, world_size: int, weights=None) -> np.ndarray:
+    """Pairs per rank: ceil(n / world) each, or proportional to `weights` (largest remainders first, ties by rank)."""
+    if weights is None:
+        return np.full(world_size, -(-n_pairs // world_size), np.int64)
+    w = np.asarray(weights, dtype=np.float64)
+    if w.shape != (world_size,) or not np.all(np.isfinite(w)) or np.any(w <= 0):
+        raise ValueError(f"weights must be {world_size} positive numbers")
+    share = n_pairs * w / w.sum()
+    t = np.floor(share).astype(np.int64)
+    order = np.argsort(-(share - t), kind="stable")
+    t[order[: n_pairs - int(t.sum())]] += 1
+    return t
+
+
+def partition_all_by_owner(pairs: np.ndarray, world_size: int, n_loc: int, weights=None):
     """partition_by_owner for every rank in one pass over the list (the sharded host path needs all of them: its
     own pairs to match, everybody's to put the gathered results back into list order).
     -> [(indices into `pairs`, number of leading local-only pairs)] per rank"""
@@ -104,7 +121,7 @@ def partition_all_by_owner(pairs: np.ndarray, world_size: int, n_loc: int):
     oq, ot = q // n_loc, t // n_loc
     owner = np.where(((q + t) & 1) == 0, oq, ot)
     local = oq == ot
-    target = -(-len(pairs) // world_size)
+    target = rank_targets(len(pairs), world_size, weights)
     counts = np.bincount(owner, minlength=world_size)
     small = np.int16 if world_size < 32000 else np.int64                       # int16: numpy's stable sort is a radix sort
     by_owner = np.argsort(owner.astype(small), kind="stable")                  # grouped by owner, list order inside
@@ -113,7 +130,7 @@ def partition_all_by_owner(pairs: np.ndarray, world_size: int, n_loc: int):
     for r in np.nonzero(counts > target)[0]:         # surplus: the tail of a rank's non-local pairs
         grp = by_owner[starts[r]: starts[r + 1]]
         mine = grp[~local[grp]]
-        extra = int(counts[r]) - target
+        extra = int(counts[r]) - int(target[r])
         pool.append(mine[len(mine) - min(extra, len(mine)):])
     if pool:
         pool = np.concatenate(pool)
@@ -122,7 +139,7 @@ def partition_all_by_owner(pairs: np.ndarray, world_size: int, n_loc: int):
         counts = np.bincount(owner[owner >= 0], minlength=world_size)
         at = 0
         for r in range(world_size):                  # deficit: filled from the pool in rank order
-            room = target - int(counts[r])
+            room = int(target[r]) - int(counts[r])
             if room > 0 and at < len(pool):
                 take = pool[at: at + room]
                 owner[take] = r

@@ -435,6 +435,8 @@ def main():
     ap.add_argument("--n-img", type=int, default=N_IMG, help="development only: fewer images (invalid as a bench number)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-secondary", action="store_true", help="skip the configs 2 / 4 / 5 measurements")
+    ap.add_argument("--no-rebalance", action="store_true",
+                    help="N > 1: keep the equal-count partition instead of the one weighted by the warm-up's per-rank throughput")
     ap.add_argument("--chunk", type=int, default=None, help="development only: columns per chunk of the chunk sweep (32 / 64)")
     ap.add_argument("--kernel", type=int, default=None, help="development only: sweep kernel variant (library option 'kernel')")
     args = ap.parse_args()
@@ -518,9 +520,30 @@ def main():
         return float(t.item())
 
     # ------------------------------------------------------------------ device-resident leg (value)
-    for _ in range(args.warmup):
-        pkg.match_pairs(bank, pairs_dev, ratio=RATIO, mutual=True, cap=CAP, out=out, workspace=workspace)
     barrier()
+    w0, w1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    n_meas = max(1, args.warmup - 1)                    # the first warm-up step is cold: measure the others
+    for i in range(args.warmup):
+        if i == args.warmup - n_meas:
+            w0.record()
+        pkg.match_pairs(bank, pairs_dev, ratio=RATIO, mutual=True, cap=CAP, out=out, workspace=workspace)
+    w1.record()
+    barrier()
+    # The ranks do not all run at the same pairs/s (GPUs under a power cap differ by a few per cent, and so does the
+    # match density of the pair sets): the warm-up steps measure every rank's throughput and the owner partition then
+    # hands out the pairs in that proportion (scheduler.partition_by_owner(weights=...)); untimed, like the warm-up.
+    rank_weights = None
+    if world > 1 and args.warmup > 0 and not args.no_rebalance:
+        rank_weights = dmod.rank_throughput(w0.elapsed_time(w1) / n_meas, P, dev)
+    if rank_weights is not None:
+        pairs_mine, idx_mine, _ = pkg.partition_by_owner(pairs_all, world, rank, n_loc, weights=rank_weights)
+        pairs_dev = torch.from_numpy(np.ascontiguousarray(pairs_mine)).to(dev)
+        P = len(pairs_mine)
+        del out, workspace
+        out = pkg.match_pairs(bank, pairs_dev, ratio=RATIO, mutual=True, cap=CAP)
+        workspace = torch.empty(int(pkg._lib.lib().b200m_workspace_bytes(bank.k_stride, P)), dtype=torch.uint8, device=dev)
+        pkg.match_pairs(bank, pairs_dev, ratio=RATIO, mutual=True, cap=CAP, out=out, workspace=workspace)
+        barrier()
     pkg.set_option("profile", 1)
     pkg.profile_read()
     sampler = ClockSampler(local_rank)
@@ -617,7 +640,7 @@ def main():
     def e2e_step(record):
         evs = {} if record else None
         res = dmod.match_pairs_host(host_local, k_host, n_img, pairs_all, ratio=RATIO, mutual=True, cap=CAP, device=dev,
-                                    out=out, workspace=workspace, staging=True, events=evs)
+                                    out=out, workspace=workspace, staging=True, events=evs, rank_weights=rank_weights)
         if evs:
             torch.cuda.synchronize()
             for name, (a, b) in evs.items():
@@ -682,6 +705,7 @@ def main():
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "u8",
             "data": "synthetic",
             "config": {"workload": WORKLOAD, "n_img": n_img, "k": K, "d": D, "pairs": P_all, "pairs_per_rank": P, "ms_per_step_ranks": ms_ranks,
+                       "rank_weights": rank_weights,
                        "cap": CAP, "seed": SEED, "matches_total": matches_total, "result_digest": f"{result_digest:016x}",
                        "e2e_lists_equal_value_lists": e2e_same,
                        "l2": "inputs larger than L2: 539 MB bank, every step sweeps all of it",
@@ -690,7 +714,9 @@ def main():
                                           "e2e_first_call": e2e_cold_ms, "e2e_phases_warm": phases or None,
                                           "e2e_phases_warm_min_over_ranks": phases_min or None,
                                           "e2e_bank_transport": dmod.transport_in_use()},
-                       "parallelism": f"pairs sharded over {world} GPU(s); value leg: no collective in the data path; e2e leg: "
+                       "parallelism": f"pairs sharded over {world} GPU(s)"
+                                      + ("" if rank_weights is None else " in proportion to every rank's throughput measured over the warm-up steps (rank_weights)")
+                                      + "; value leg: no collective in the data path; e2e leg: "
                                       "sharded upload, pairs between a rank's own images matched while the prepared bank slices "
                                       "travel between the GPUs (copy engines over NVLink), one packed gather per step"},
             "e2e": {"value": P_all / (e2e_ms / 1e3), "unit": "pairs/s", "ms_per_step": e2e_ms,

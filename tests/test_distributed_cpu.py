@@ -206,3 +206,29 @@ def test_upload_blocks_ramp_and_segments_on_boundaries(pkg):
     for need_b, a, b in segs:
         assert pairs[a:b].max() < bounds[need_b + 1] and pairs[a:b].max() >= bounds[need_b]
     assert sum(b - a for _, a, b in segs) == len(pairs)
+
+
+def _throughput_worker(rank, world, port, out_path):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    dmod = importlib.import_module("3d_reconstruction_b200.distributed")
+    sched = importlib.import_module("3d_reconstruction_b200.scheduler")
+    w = dmod.rank_throughput(100.0 if rank == 0 else 110.0, 1000, "cpu")      # rank 1 is 10 % slower
+    pairs = sched.exhaustive_pairs(40)
+    p, idx, n_local = sched.partition_by_owner(pairs, world, rank, 20, weights=w)
+    torch.save({"w": w, "idx": idx}, f"{out_path}.{rank}")
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_rank_throughput_weights_agree_on_all_ranks(tmp_path):
+    """distributed.rank_throughput: every rank ends up with the same weights (they feed a partition that must be
+    identical everywhere), the slower rank gets fewer pairs, nothing is lost."""
+    out = str(tmp_path / "w")
+    mp.spawn(_throughput_worker, args=(2, _free_port(), out), nprocs=2, join=True)
+    a, b = torch.load(out + ".0", weights_only=False), torch.load(out + ".1", weights_only=False)
+    assert a["w"] == b["w"] and a["w"][0] > a["w"][1]
+    assert abs(a["w"][0] / a["w"][1] - 1.1) < 0.01
+    assert len(a["idx"]) > len(b["idx"])
+    assert np.array_equal(np.sort(np.concatenate([a["idx"], b["idx"]])), np.arange(40 * 39 // 2))

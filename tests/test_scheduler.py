@@ -1,6 +1,7 @@
 import importlib
 
 import numpy as np
+import pytest
 
 
 def test_exhaustive_and_window_counts(pkg):
@@ -85,3 +86,27 @@ def test_partition_by_owner_is_balanced_and_local_first(pkg):
         assert max(sizes) - min(sizes) <= max(1, ws), (n_img, ws, sizes)
     p, idx, n_local = sched.partition_by_owner(pairs, 1, 0, 9)
     assert len(p) == len(pairs) and n_local == len(pairs)
+
+
+def test_partition_by_owner_weighted_targets(pkg):
+    """weights = measured relative throughput of the ranks: the pair counts follow them, every pair is still owned
+    exactly once, local pairs still come first, and equal weights reproduce the unweighted partition."""
+    sched = importlib.import_module("3d_reconstruction_b200.scheduler")
+    n_img, ws = 257, 8
+    n_loc = -(-n_img // ws)
+    pairs = pkg.blocked_order(pkg.exhaustive_pairs(n_img))
+    w = [1.0, 1.02, 0.98, 1.0, 1.0, 1.0, 0.96, 1.04]
+    tgt = sched.rank_targets(len(pairs), ws, w)
+    assert int(tgt.sum()) == len(pairs) and tgt[7] > tgt[0] > tgt[6]
+    seen = []
+    for r in range(ws):
+        p, idx, n_local = sched.partition_by_owner(pairs, ws, r, n_loc, weights=w)
+        assert len(p) == int(tgt[r])
+        assert np.all(p[:n_local] // n_loc == r) and np.array_equal(pairs[idx], p)
+        seen.append(idx)
+        p0, idx0, nl0 = sched.partition_by_owner(pairs, ws, r, n_loc)
+        p1, idx1, nl1 = sched.partition_by_owner(pairs, ws, r, n_loc, weights=[1.0] * ws)
+        assert np.array_equal(idx0, idx1) and nl0 == nl1
+    assert np.array_equal(np.sort(np.concatenate(seen)), np.arange(len(pairs)))
+    with pytest.raises(ValueError):
+        sched.rank_targets(10, 2, [1.0, 0.0])
