@@ -158,9 +158,15 @@ def cpu_baseline(desc_cpu, pairs, budget_s=20.0, max_pairs=8, min_pairs=2):
         if p + 1 >= min_pairs and time.perf_counter() - t_total > budget_s:
             break
     per_pair = float(np.median(times))
+    # beside the headline: the forward knnMatch(k=2) call alone, and the whole rule on uint8 inputs
+    a, b = int(pairs[0][0]), int(pairs[0][1])
+    t_knn = min(oracle_cv2.time_knn2(desc_cpu[a], desc_cpu[b], repeats=1, full_rule=False)[0] for _ in range(2))
+    t_u8 = oracle_cv2.time_knn2(desc_cpu[a], desc_cpu[b], repeats=1, full_rule=True, as_u8=True)[0]
     return {"value": 1.0 / per_pair, "unit": "pairs/s", "cores": int(threads or os.cpu_count() or 1), "kind": "reference",
             "sample": f"{len(times)} pairs of the workload (16384x16384x128), cv2.BFMatcher(NORM_L2).knnMatch k=2 on float32 "
-                      f"+ reverse knnMatch k=1 + ratio filter, median {per_pair:.3f} s/pair"}
+                      f"+ reverse knnMatch k=1 + ratio filter, median {per_pair:.3f} s/pair",
+            "knn_only_pairs_per_s": 1.0 / t_knn, "u8_input_pairs_per_s": 1.0 / t_u8,
+            "gops": 2.0 * K * K * D / per_pair / 1e9}
 
 
 def run_reference(args):

@@ -57,14 +57,16 @@ def match(q: np.ndarray, t: np.ndarray, ratio: float = 0.75, mutual: bool = True
     return qi, ti, di
 
 
-def time_knn2(q: np.ndarray, t: np.ndarray, repeats: int = 1, full_rule: bool = True, threads: int | None = None):
-    """Seconds per pair for the cv2 path (float32 inputs: cv2's fastest route for this data)."""
+def time_knn2(q: np.ndarray, t: np.ndarray, repeats: int = 1, full_rule: bool = True, threads: int | None = None,
+              as_u8: bool = False):
+    """Seconds per pair for the cv2 path (float32 inputs: cv2's fastest route for this data; as_u8: the descriptors
+    as uint8, the ~4x slower route SURVEY.md section 8(d) asks to report beside it)."""
     import os
     import time
     cv2 = _cv2()
     cv2.setNumThreads(threads if threads else (os.cpu_count() or 1))
-    q32 = np.ascontiguousarray(q, dtype=np.float32)
-    t32 = np.ascontiguousarray(t, dtype=np.float32)
+    q32 = np.ascontiguousarray(q, dtype=np.uint8 if as_u8 else np.float32)
+    t32 = np.ascontiguousarray(t, dtype=np.uint8 if as_u8 else np.float32)
     bf = cv2.BFMatcher(cv2.NORM_L2)
     best = float("inf")
     for _ in range(repeats):
