@@ -1069,13 +1069,13 @@ int b200m_match_pairs_bf16(const void* bank_bf16, const int32_t* k_per_image, in
 
 // Head workspace: row results float2 [2][B][k_stride] (pass 2 reuses the second half for column keys and claims) |
 // nb float [2][B][k_stride] | largest row norm per image float [kMaxNormImgs] | flag | column partial sums of the
-// single-sweep log-sum-exp float [B][k_stride / 64][k_stride].
+// single-sweep log-sum-exp float [B][k_stride / 256][k_stride].
 constexpr int64_t kMaxNormImgs = 1 << 18;
 size_t b200m_workspace_bytes_assign(int64_t k_stride, int64_t n_pairs) {
   if (k_stride <= 0 || n_pairs <= 0) return 256;
   const size_t B = static_cast<size_t>(batch_cap(k_stride, n_pairs));
   return 2 * B * k_stride * (sizeof(float2) + sizeof(float)) + kMaxNormImgs * sizeof(float) + 1024 +
-         B * static_cast<size_t>(k_stride / 64) * k_stride * sizeof(float) + 1024;
+         B * static_cast<size_t>(k_stride / 256) * k_stride * sizeof(float) + 1024;
 }
 
 int b200m_assign_pairs_bf16(const void* mdesc_bf16, const float* matchability, const int32_t* k_per_image,

@@ -48,6 +48,7 @@ struct Ip2Smem {
   uint64_t b_full[kBStages2], b_empty[kBStages2];
   uint64_t t_full[2], t_empty[2];                             // accumulator pair of a tile parity
   uint32_t tmem_base;
+  int lse_cnt[16];                                            // kIpLse: arrivals of the four lane quadrants per (round parity, tile parity, column half, group)
 };
 
 struct Ip2Params {
@@ -64,7 +65,7 @@ struct Ip2Params {
   const float* z;               // [n_img, k_stride] matchability logits
   const float* maxnorm;         // [n_img] largest squared row norm of every image (ip_maxnorm_kernel)
   float* nbw;                   // out: nb, direction 0 (rows); direction 1 is written by ip_lse_finalize_kernel
-  float* colpart;               // out [n_pairs][4 * blocks_per_image][k_stride]: column sums of exp over 32 rows x 2 M-tiles
+  float* colpart;               // out [n_pairs][blocks_per_image][k_stride]: column sums of exp over the 256 rows of a block
   int32_t* lse_flag;            // out: set when a sum left the fp32 range (the caller re-runs the batch on the two-direction sweep)
 };
 
@@ -147,6 +148,7 @@ ip_sweep2_kernel(const __grid_constant__ CUtensorMap tmap, const Ip2Params p) {
       for (int kb = 0; kb < kNKB; ++kb) { mbar_init(&sm.a_full[s][kb], 1); mbar_init(&sm.a_empty[s][kb], 1); }
     for (int i = 0; i < kBStages2; ++i) { mbar_init(&sm.b_full[i], 1); mbar_init(&sm.b_empty[i], 1); }
     for (int i = 0; i < 2; ++i) { mbar_init(&sm.t_full[i], 1); mbar_init(&sm.t_empty[i], 8); }
+    for (int i = 0; i < 16; ++i) sm.lse_cnt[i] = 0;
     fence_mbar_init();
   }
   if (warp == 2) tmem_alloc<512>(&sm.tmem_base);
@@ -265,10 +267,20 @@ ip_sweep2_kernel(const __grid_constant__ CUtensorMap tmap, const Ip2Params p) {
         const float ref2 = ref * kLog2e;
         float rs0 = 0.f, rs1 = 0.f;
         float csum[32];
-        float* cpart = p.colpart + (static_cast<int64_t>(pair) * (4 * p.blocks_per_image) + blk * 4 + quad) * p.k_stride;
+        uint32_t rnd = my_it;                              // tiles this warp has drained so far (same for the eight warps of a pair)
+        float* cpart = p.colpart + (static_cast<int64_t>(pair) * p.blocks_per_image + blk) * p.k_stride;
+        // The four lane quadrants of a column group meet in shared memory: every warp parks its 32 column sums, the
+        // last of the four to arrive adds them in a fixed order (deterministic) and writes ONE partial per (row block,
+        // column). Slots are double buffered by the parity of the warp's tile count: a warp can be at most one of its
+        // tiles ahead of the slowest warp of its accumulator pair (t_empty needs all eight arrivals). In this mode the
+        // row sums use the first half of `rowmerge` as plain floats; its second half and `colx` hold the slots.
+        float* rsum = reinterpret_cast<float*>(sm.rowmerge);                     // [par][3][256]
+        volatile float* cq0 = reinterpret_cast<volatile float*>(sm.colx);      // [tp][h][grp][quad][32], even rounds
+        volatile float* cq1 = rsum + 2 * 3 * kRows2;                           // the same, odd rounds
         for (int t = static_cast<int>((tp + 2 - (t_seen & 1)) & 1); t < ntiles; t += 2) {
           mbar_wait(&sm.t_full[tp], my_it & 1);
           tc_fence_after();
+          rnd = my_it;
           ++my_it;
 #pragma unroll
           for (int s = 0; s < 4; ++s) {
@@ -311,14 +323,29 @@ ip_sweep2_kernel(const __grid_constant__ CUtensorMap tmap, const Ip2Params p) {
             if (s & 1) {
               const float mine = warp_colsum32(csum, lane);
               const int col = t * kColsF + h * 64 + (s >> 1) * 32 + static_cast<int>(lane);
-              if (col < n_cols) cpart[col] = mine;       // every (pair, block, quadrant, column) is written exactly once
+              const uint32_t rp = rnd & 1, g4 = ((tp * 2 + h) * 2 + (s >> 1));
+              volatile float* slot = (rp ? cq1 : cq0) + g4 * 128;
+              slot[quad * 32 + lane] = mine;
+              __syncwarp();
+              int old = 0;
+              if (lane == 0) {
+                __threadfence_block();
+                old = atomicAdd(&sm.lse_cnt[rp * 8 + g4], 1);
+              }
+              old = __shfl_sync(0xffffffffu, old, 0);
+              if (old == 3) {                            // the other three quadrants are in
+                __threadfence_block();
+                const float tot = ((slot[lane] + slot[32 + lane]) + slot[64 + lane]) + slot[96 + lane];
+                if (col < n_cols) cpart[col] = tot;      // every (pair, block, column) is written exactly once
+                if (lane == 0) atomicExch(&sm.lse_cnt[rp * 8 + g4], 0);
+              }
             }
           }
         }
         t_seen += ntiles;
         if (e > 0) {
-          sm.rowmerge[par][e - 1][r0] = make_float2(rs0, 0.f);
-          sm.rowmerge[par][e - 1][r1] = make_float2(rs1, 0.f);
+          rsum[(par * 3 + (e - 1)) * kRows2 + r0] = rs0;
+          rsum[(par * 3 + (e - 1)) * kRows2 + r1] = rs1;
         }
         named_bar_sync(kEpiBarrier, kEpiWarps * 32);
         if (e == 0) {
@@ -328,7 +355,7 @@ ip_sweep2_kernel(const __grid_constant__ CUtensorMap tmap, const Ip2Params p) {
             if (r >= n_rows) continue;
             float ss = m ? rs1 : rs0;
 #pragma unroll
-            for (int oo = 0; oo < 3; ++oo) ss += sm.rowmerge[par][oo][r].x;
+            for (int oo = 0; oo < 3; ++oo) ss += rsum[(par * 3 + oo) * kRows2 + r];
             if (!(ss >= kLseTiny) || ss > 3.0e38f) atomicOr(p.lse_flag, 1);
             const int64_t row = static_cast<int64_t>(blk) * kRows2 + r;
             p.nbw[obase + row] = log_sigmoid(__ldg(p.z + static_cast<int64_t>(row_img) * p.k_stride + row)) - (ref + logf(ss));
@@ -525,7 +552,7 @@ ip_maxnorm_kernel(const uint16_t* __restrict__ desc, const int32_t* __restrict__
   if (lane == 0) atomicMax(reinterpret_cast<int*>(maxnorm + img), __float_as_int(acc));
 }
 
-// Columns of the single-sweep log-sum-exp: the partial sums of every (row block, lane quadrant) in a fixed order
+// Columns of the single-sweep log-sum-exp: the partial sums of the row blocks in a fixed order
 // -> nb[1][pair][column] = logsigmoid(z_column) - log-sum-exp over the rows.
 __global__ void __launch_bounds__(256)
 ip_lse_finalize_kernel(const float* __restrict__ colpart, const float* __restrict__ maxnorm, const float* __restrict__ z,
@@ -535,8 +562,8 @@ ip_lse_finalize_kernel(const float* __restrict__ colpart, const float* __restric
   const PairInfo pi = load_pair(pairs, k_per_image, pair, n_img, k_stride);
   const int col = blockIdx.x * blockDim.x + threadIdx.x;
   if (col >= pi.kt || pi.kq <= 0) return;
-  const int parts_all = static_cast<int>(4 * (k_stride / kRows2));
-  const int parts = 4 * ((pi.kq + kRows2 - 1) / kRows2);
+  const int parts_all = static_cast<int>(k_stride / kRows2);
+  const int parts = (pi.kq + kRows2 - 1) / kRows2;
   const float* src = colpart + static_cast<int64_t>(pair) * parts_all * k_stride + col;
   float ss = 0.f;
   for (int q = 0; q < parts; ++q) ss += src[static_cast<int64_t>(q) * k_stride];

@@ -169,3 +169,31 @@ def test_assign_scores_outside_the_common_reference_range(pkg, case):
         _, _, _, (m0, _, ms0, _), _ = oracle_float.assign(d0, d1, z0, z1, th)
         _compare(q, t, s, m0, ms0, min_agree=0.99)
         assert len(q) > 50
+
+
+def test_assign_is_repeatable_bit_for_bit(pkg):
+    """Two calls on the same inputs give the same lists and the same float32 score bits: the column sums of the
+    single-sweep log-sum-exp are combined in a fixed order (lane quadrants in shared memory, row blocks in the
+    finalize kernel), never with floating-point atomics."""
+    dim, sizes = 128, [1500, 1300, 2048, 700, 1024, 1800]
+    gen = torch.Generator().manual_seed(9)
+    world = torch.nn.functional.normalize(torch.randn(2600, dim, generator=gen), dim=1)
+    descs = [(4.5 * torch.nn.functional.normalize(world[torch.randperm(2600, generator=gen)[:k]] + 0.04 * torch.randn(k, dim, generator=gen), dim=1))
+             .to(torch.bfloat16).float() for k in sizes]
+    bank = pkg.FloatBank.from_arrays(descs, device="cuda")
+    z = torch.zeros((len(sizes), bank.k_stride), dtype=torch.float32, device="cuda")
+    for i, k in enumerate(sizes):
+        z[i, :k] = 1.0 + torch.randn(k, generator=gen)
+    pairs = [[a, b] for a in range(len(sizes)) for b in range(len(sizes)) if a != b]
+    runs = []
+    for _ in range(3):
+        res = pkg.assign_pairs(bank, z, pairs, filter_threshold=0.05)
+        res.check_overflow()
+        runs.append(res.to_lists())
+    total = 0
+    for other in runs[1:]:
+        for (q0, t0, s0), (q1, t1, s1) in zip(runs[0], other):
+            assert np.array_equal(q0, q1) and np.array_equal(t0, t1)
+            assert np.array_equal(np.asarray(s0, np.float32).view(np.uint32), np.asarray(s1, np.float32).view(np.uint32))
+            total += len(q0)
+    assert total > 5000
