@@ -102,9 +102,11 @@ __device__ __forceinline__ int block_compact_slot(bool keep, int* warp_sums, int
 // whose best float32 distance is d1f:  D* = min { D : double(d1f) < ratio * double(sqrtf(D)) }.
 // The row passes  <=>  every other train row has d^2 >= D*  (sqrtf is monotone), which turns the
 // float-exact `m.distance < ratio * n.distance` into an integer threshold for the verify sweep.
-__device__ __forceinline__ int ratio_radius_sq(float d1f, double ratio) {
+// inv_ratio = 1 / ratio, computed once by the caller: the double division is the most expensive step here and the
+// estimate it feeds is corrected by the two loops anyway.
+__device__ __forceinline__ int ratio_radius_sq(float d1f, double ratio, double inv_ratio) {
   const double d1 = static_cast<double>(d1f);
-  double est = d1 / ratio;
+  double est = d1 * inv_ratio;
   est = est * est;
   long long D = est > 33554432.0 ? 33554432ll : static_cast<long long>(est);
   auto passes = [&](long long x) { return d1 < ratio * static_cast<double>(__fsqrt_rn(static_cast<float>(x))); };
@@ -112,6 +114,7 @@ __device__ __forceinline__ int ratio_radius_sq(float d1f, double ratio) {
   while (D < 33554432ll && !passes(D)) ++D;
   return static_cast<int>(D);
 }
+__device__ __forceinline__ int ratio_radius_sq(float d1f, double ratio) { return ratio_radius_sq(d1f, ratio, 1.0 / ratio); }
 
 // Candidate selection after the first sweep; candidates are compacted in ascending query order.
 //   exact2 != 0: rowres holds the exact second neighbour (kTop2 sweep): the Lowe test is decided here.

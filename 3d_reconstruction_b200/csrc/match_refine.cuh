@@ -70,6 +70,7 @@ refine_kernel(const RefineParams p) {
   const int64_t qbase = static_cast<int64_t>(qi) * p.k_stride;
   const int64_t tbase = static_cast<int64_t>(ti) * p.k_stride;
   const bool use_ratio = p.ratio > 0.0;
+  const double inv_ratio = use_ratio ? 1.0 / p.ratio : 0.0;
 
   int4 v = make_int4(kBigScore, 0, kBigScore, 0);
   int na = 0;
@@ -88,7 +89,7 @@ refine_kernel(const RefineParams p) {
         // D*(d1) = d1^2 / ratio^2 up to float rounding (relative 3e-7): a cheap test with a wide margin
         // settles almost every row, the exact radius is only computed for the rest
         if (static_cast<double>(ub2) < static_cast<double>(d1lb) * p.inv_ratio_sq * 0.999 - 2.0) need = false;
-        else if (ub2 < ratio_radius_sq(dist_from_sq(d1lb), p.ratio)) need = false;   // a second column lies inside the radius for sure
+        else if (ub2 < ratio_radius_sq(dist_from_sq(d1lb), p.ratio, inv_ratio)) need = false;   // a second column lies inside the radius for sure
       }
     }
   }
@@ -112,28 +113,33 @@ refine_kernel(const RefineParams p) {
       int s = 0x7fffffff, orig = 0x7fffffff;
       if (c < kt) {
         const uint4* colp = reinterpret_cast<const uint4*>(p.sbank + (tbase + c) * 128);
-        uint32_t dot = 0;
+        // all sixteen loads first, then the arithmetic: one memory round trip per 32 columns instead of four
+        uint4 a[8], b[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) b[i] = __ldg(colp + i);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) a[i] = __ldg(rowp + i);
+        uint32_t dot = 0, dot2 = 0;
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-          const uint4 a = __ldg(rowp + i), b = __ldg(colp + i);
-          dot = __dp4a(a.x, b.x, dot);
-          dot = __dp4a(a.y, b.y, dot);
-          dot = __dp4a(a.z, b.z, dot);
-          dot = __dp4a(a.w, b.w, dot);
+          dot = __dp4a(a[i].x, b[i].x, dot);
+          dot2 = __dp4a(a[i].y, b[i].y, dot2);
+          dot = __dp4a(a[i].z, b[i].z, dot);
+          dot2 = __dp4a(a[i].w, b[i].w, dot2);
         }
+        dot += dot2;
         s = p.snorm[tbase + c] - 2 * static_cast<int>(dot);
         orig = p.perm[tbase + c];
       }
-      // best of these 32 columns by (score, original index), then the runner-up among the other lanes
-      int ws = s, wo = orig;
-#pragma unroll
-      for (int off = 16; off >= 1; off >>= 1) {
-        const int os = __shfl_xor_sync(0xffffffffu, ws, off), oo = __shfl_xor_sync(0xffffffffu, wo, off);
-        if (os < ws || (os == ws && oo < wo)) { ws = os; wo = oo; }
-      }
-      int w2 = (orig == wo) ? 0x7fffffff : s;
-#pragma unroll
-      for (int off = 16; off >= 1; off >>= 1) w2 = min(w2, __shfl_xor_sync(0xffffffffu, w2, off));
+      // best of these 32 columns by (score, original index), then the runner-up among the other lanes: three
+      // redux.sync.min on offset keys (scores lie in (-2^25, 2^23)) instead of three 5-step shuffle butterflies
+      const unsigned ks = c < kt ? static_cast<unsigned>(s + (1 << 25)) : 0xffffffffu;
+      const unsigned km = __reduce_min_sync(0xffffffffu, ks);
+      const unsigned ko = __reduce_min_sync(0xffffffffu, ks == km ? static_cast<unsigned>(orig) : 0xffffffffu);
+      const unsigned k2 = __reduce_min_sync(0xffffffffu, (ks == km && static_cast<unsigned>(orig) == ko) ? 0xffffffffu : ks);
+      const int ws = km == 0xffffffffu ? 0x7fffffff : static_cast<int>(km) - (1 << 25);
+      const int wo = km == 0xffffffffu ? 0x7fffffff : static_cast<int>(ko);
+      const int w2 = k2 == 0xffffffffu ? 0x7fffffff : static_cast<int>(k2) - (1 << 25);
       // merge into the chunk's running (best, runner-up)
       if (ws < bs || (ws == bs && wo < bo)) {
         s2 = min(min(s2, w2), bs);
@@ -151,7 +157,7 @@ refine_kernel(const RefineParams p) {
         const int d1 = bs + na;
         int state = kRowPass;
         if (use_ratio) {
-          const int thr = ratio_radius_sq(dist_from_sq(d1), p.ratio) - na;   // a second column scoring < thr spoils the test
+          const int thr = ratio_radius_sq(dist_from_sq(d1), p.ratio, inv_ratio) - na;   // a second column scoring < thr spoils the test
           if (s2 < thr) state = kRowReject;
           else if (v.z >= thr) state = kRowPass;
           else if (v.z < kPadScore && static_cast<long long>(v.z) + p.spread[ti] < thr) state = kRowReject;
