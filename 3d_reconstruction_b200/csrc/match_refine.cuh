@@ -113,21 +113,15 @@ refine_kernel(const RefineParams p) {
       int s = 0x7fffffff, orig = 0x7fffffff;
       if (c < kt) {
         const uint4* colp = reinterpret_cast<const uint4*>(p.sbank + (tbase + c) * 128);
-        // all sixteen loads first, then the arithmetic: one memory round trip per 32 columns instead of four
-        uint4 a[8], b[8];
-#pragma unroll
-        for (int i = 0; i < 8; ++i) b[i] = __ldg(colp + i);
-#pragma unroll
-        for (int i = 0; i < 8; ++i) a[i] = __ldg(rowp + i);
-        uint32_t dot = 0, dot2 = 0;
+        uint32_t dot = 0;
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-          dot = __dp4a(a[i].x, b[i].x, dot);
-          dot2 = __dp4a(a[i].y, b[i].y, dot2);
-          dot = __dp4a(a[i].z, b[i].z, dot);
-          dot2 = __dp4a(a[i].w, b[i].w, dot2);
+          const uint4 a = __ldg(rowp + i), b = __ldg(colp + i);
+          dot = __dp4a(a.x, b.x, dot);
+          dot = __dp4a(a.y, b.y, dot);
+          dot = __dp4a(a.z, b.z, dot);
+          dot = __dp4a(a.w, b.w, dot);
         }
-        dot += dot2;
         s = p.snorm[tbase + c] - 2 * static_cast<int>(dot);
         orig = p.perm[tbase + c];
       }
