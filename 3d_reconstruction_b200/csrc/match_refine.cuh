@@ -51,11 +51,30 @@ struct RefineParams {
   double inv_ratio_sq;          // 1 / ratio^2 (0 when the ratio test is off)
   int32_t chunk_cols;           // 32 or 64: columns per chunk of the sweep that produced rowres_s
   unsigned long long* stats;    // counters of the call (match_common.cuh), may be NULL
+  // split form (refine_classify_kernel + refine_eval_kernel) only:
+  int32_t* need_count;          // [n_pairs] rows whose winning chunk has to be evaluated (zeroed by the caller)
+  int32_t* need_list;           // [n_pairs, k_stride] their original query rows (any order)
 };
 
 constexpr int kRefineThreads = 256;
 constexpr int kBigScore = 1 << 28;
 constexpr int kPadScore = 1 << 23;   // bound of an all-padding chunk (B200M_PAD_NORM - 0): no real column behind it
+
+// Step 1 for one row: does its winning chunk have to be evaluated? v = (L1, g1, L2), na = the row's squared norm.
+__device__ __forceinline__ bool refine_needs_eval(const RefineParams& p, const int4 v, int na, int kt, int ti, double inv_ratio) {
+  if (!(p.ratio > 0.0)) return true;
+  if (kt < 2) return false;                             // no second neighbour: dropped by the ratio test
+  if (v.z < kPadScore) {                                // a second chunk with real columns exists
+    const int spread = p.spread[ti];
+    const int d1lb = max(v.x + na, 0);
+    const long long ub2 = static_cast<long long>(v.z) + spread + na;
+    // D*(d1) = d1^2 / ratio^2 up to float rounding (relative 3e-7): a cheap test with a wide margin
+    // settles almost every row, the exact radius is only computed for the rest
+    if (static_cast<double>(ub2) < static_cast<double>(d1lb) * p.inv_ratio_sq * 0.999 - 2.0) return false;
+    if (ub2 < ratio_radius_sq(dist_from_sq(d1lb), p.ratio, inv_ratio)) return false;   // a second column lies inside the radius for sure
+  }
+  return true;
+}
 
 __global__ void __launch_bounds__(kRefineThreads)
 refine_kernel(const RefineParams p) {
@@ -78,20 +97,7 @@ refine_kernel(const RefineParams p) {
   if (r < kq && kt > 0) {
     na = p.sqnorm[qbase + r];
     v = p.rowres_s[base + p.inv[qbase + r]];
-    need = true;
-    if (use_ratio) {
-      if (kt < 2) {
-        need = false;                                   // no second neighbour: dropped by the ratio test
-      } else if (v.z < kPadScore) {                     // a second chunk with real columns exists
-        const int spread = p.spread[ti];
-        const int d1lb = max(v.x + na, 0);
-        const long long ub2 = static_cast<long long>(v.z) + spread + na;
-        // D*(d1) = d1^2 / ratio^2 up to float rounding (relative 3e-7): a cheap test with a wide margin
-        // settles almost every row, the exact radius is only computed for the rest
-        if (static_cast<double>(ub2) < static_cast<double>(d1lb) * p.inv_ratio_sq * 0.999 - 2.0) need = false;
-        else if (ub2 < ratio_radius_sq(dist_from_sq(d1lb), p.ratio, inv_ratio)) need = false;   // a second column lies inside the radius for sure
-      }
-    }
+    need = refine_needs_eval(p, v, na, kt, ti, inv_ratio);
   }
   int4 out = make_int4(0, -1, 0, kRowReject);
   bool fallback = false;
@@ -177,6 +183,132 @@ refine_kernel(const RefineParams p) {
       p.rowres_o[base + r] = out;
     }
   }
+}
+
+// ---- The same refinement as two kernels (option "refine" = 1). refine_kernel walks the rows that need their chunk evaluated one after
+// the other inside each warp (a serial chain of memory round trips per row: fine when 2 % of the rows need it, 0.6 ms
+// per 16 pairs when a third do, as on strongly overlapping real images). Split: a streaming pass settles step 1 for
+// every row and lists the rest; a persistent pass gives every listed row its own warp, so rows are evaluated side by
+// side. Same decisions, same outputs (the order of the fallback list differs, which nothing depends on).
+__global__ void __launch_bounds__(kRefineThreads)
+refine_classify_kernel(const RefineParams p) {
+  const int pair = blockIdx.y;
+  const PairInfo pi = load_pair(p.pairs, p.k_per_image, pair, p.n_img, p.k_stride);
+  const int kq = pi.kq, kt = pi.kt;
+  const int lane = threadIdx.x & 31;
+  const int r_warp0 = (blockIdx.x * kRefineThreads + threadIdx.x) & ~31;
+  if (r_warp0 >= kq) return;
+  const int r = r_warp0 + lane;
+  const int64_t base = static_cast<int64_t>(pair) * p.k_stride;
+  const int64_t qbase = static_cast<int64_t>(pi.qi) * p.k_stride;
+  const double inv_ratio = p.ratio > 0.0 ? 1.0 / p.ratio : 0.0;
+  bool need = false;
+  if (r < kq && kt > 0) {
+    const int na = p.sqnorm[qbase + r];
+    const int4 v = p.rowres_s[base + p.inv[qbase + r]];
+    need = refine_needs_eval(p, v, na, kt, pi.ti, inv_ratio);
+  }
+  const unsigned todo = __ballot_sync(0xffffffffu, need);
+  int slot0 = 0;
+  if (lane == 0) {
+    stat_add(p.stats, 0, static_cast<unsigned>(min(kq - r_warp0, 32)));
+    stat_add(p.stats, 1, __popc(todo));
+    if (todo) slot0 = atomicAdd(p.need_count + pair, __popc(todo));
+  }
+  slot0 = __shfl_sync(0xffffffffu, slot0, 0);
+  if (r < kq) {
+    if (need) p.need_list[base + slot0 + __popc(todo & ((1u << lane) - 1u))] = r;
+    else p.rowres_o[base + r] = make_int4(0, -1, 0, kRowReject);
+  }
+}
+
+// Persistent grid; warp w of the grid takes the listed rows w, w + W, w + 2 W, ... of every pair of the batch.
+__global__ void __launch_bounds__(kRefineThreads)
+refine_eval_kernel(const RefineParams p, int n_pairs) {
+  const int lane = threadIdx.x & 31;
+  const int warps = gridDim.x * (kRefineThreads / 32);
+  const int gw = blockIdx.x * (kRefineThreads / 32) + (threadIdx.x >> 5);
+  const bool use_ratio = p.ratio > 0.0;
+  const double inv_ratio = use_ratio ? 1.0 / p.ratio : 0.0;
+  unsigned n_fb = 0;
+  int carry = gw;                                        // position of this warp's next row in the concatenated lists
+  for (int pair = 0; pair < n_pairs; ++pair) {
+    const int n_need = __ldg(p.need_count + pair);
+    if (carry >= n_need) { carry -= n_need; continue; }
+    const PairInfo pi = load_pair(p.pairs, p.k_per_image, pair, p.n_img, p.k_stride);
+    const int kt = pi.kt;
+    const int64_t base = static_cast<int64_t>(pair) * p.k_stride;
+    const int64_t qbase = static_cast<int64_t>(pi.qi) * p.k_stride;
+    const int64_t tbase = static_cast<int64_t>(pi.ti) * p.k_stride;
+    int idx = carry;
+    for (; idx < n_need; idx += warps) {
+      const int r = __ldg(p.need_list + base + idx);
+      const int na = p.sqnorm[qbase + r];
+      const int4 v = p.rowres_s[base + p.inv[qbase + r]];
+      const uint4* rowp = reinterpret_cast<const uint4*>(p.bank + (qbase + r) * 128);
+      int bs = 0x7fffffff, bo = 0x7fffffff, s2 = 0x7fffffff;   // best (score, original index), runner-up score
+      for (int sub = 0; sub < p.chunk_cols; sub += 32) {
+        const int c = v.y * p.chunk_cols + sub + lane;         // sorted train column of this lane
+        int s = 0x7fffffff, orig = 0x7fffffff;
+        if (c < kt) {
+          const uint4* colp = reinterpret_cast<const uint4*>(p.sbank + (tbase + c) * 128);
+          uint4 a[8], b[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) b[i] = __ldg(colp + i);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) a[i] = __ldg(rowp + i);
+          uint32_t d0 = 0, d1 = 0;
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            d0 = __dp4a(a[i].x, b[i].x, d0);
+            d1 = __dp4a(a[i].y, b[i].y, d1);
+            d0 = __dp4a(a[i].z, b[i].z, d0);
+            d1 = __dp4a(a[i].w, b[i].w, d1);
+          }
+          s = p.snorm[tbase + c] - 2 * static_cast<int>(d0 + d1);
+          orig = p.perm[tbase + c];
+        }
+        const unsigned ks = c < kt ? static_cast<unsigned>(s + (1 << 25)) : 0xffffffffu;
+        const unsigned km = __reduce_min_sync(0xffffffffu, ks);
+        const unsigned ko = __reduce_min_sync(0xffffffffu, ks == km ? static_cast<unsigned>(orig) : 0xffffffffu);
+        const unsigned k2 = __reduce_min_sync(0xffffffffu, (ks == km && static_cast<unsigned>(orig) == ko) ? 0xffffffffu : ks);
+        const int ws = km == 0xffffffffu ? 0x7fffffff : static_cast<int>(km) - (1 << 25);
+        const int wo = km == 0xffffffffu ? 0x7fffffff : static_cast<int>(ko);
+        const int w2 = k2 == 0xffffffffu ? 0x7fffffff : static_cast<int>(k2) - (1 << 25);
+        if (ws < bs || (ws == bs && wo < bo)) {
+          s2 = min(min(s2, w2), bs);
+          bs = ws;
+          bo = wo;
+        } else {
+          s2 = min(min(s2, w2), ws);
+        }
+      }
+      if (!(bs < v.z)) {                                       // another chunk may hold the nearest (or an equal) column
+        int slot = 0;
+        if (lane == 0) {
+          slot = atomicAdd(p.fb_count + pair, 1);
+          if (slot == 0) atomicOr(p.fb_total, 1);
+          p.fb_q[base + slot] = r;
+          ++n_fb;
+        }
+        slot = __shfl_sync(0xffffffffu, slot, 0);
+        if (lane < 8) reinterpret_cast<uint4*>(p.fb_desc + (base + slot) * 128)[lane] = __ldg(rowp + lane);
+      } else if (lane == 0) {
+        const int d1 = bs + na;
+        int state = kRowPass;
+        if (use_ratio) {
+          const int thr = ratio_radius_sq(dist_from_sq(d1), p.ratio, inv_ratio) - na;   // a second column scoring < thr spoils the test
+          if (s2 < thr) state = kRowReject;
+          else if (v.z >= thr) state = kRowPass;
+          else if (v.z < kPadScore && static_cast<long long>(v.z) + p.spread[pi.ti] < thr) state = kRowReject;
+          else state = kRowNeedRatio;
+        }
+        p.rowres_o[base + r] = make_int4(d1, bo, 0, state);
+      }
+    }
+    carry = idx - n_need;
+  }
+  if (lane == 0) stat_add(p.stats, 2, n_fb);
 }
 
 // Candidate selection of pipeline 2, ascending original query order (one CTA per pair).

@@ -232,6 +232,9 @@ int b200m_five_point_f64(const double* x0, const double* x1, double* out_E, int3
  *   "batch"     pairs per internal batch, 0 = default
  *   "float_sweep" 0 = float path as ONE tensor sweep per pair and pass: column maxima / column log-sum-exp fused into the
  *               row sweep (default), 1 = one sweep per direction
+ *   "refine"    pipeline 2, from chunk bounds to exact rows: 0 = one fused kernel (default), 1 = streaming
+ *               classification + one warp per row whose winning chunk has to be evaluated (pays on banks where many rows
+ *               need it)
  *   "knn_eval"  b200m_knn2_sorted_u8, exact evaluation of the two winning chunks: 0 = tensor cores over gathered
  *               rows (default), 1 = dp4a
  *   "profile"   1 = time sweep launches with CUDA events (see b200m_profile_read) */

@@ -124,3 +124,33 @@ def test_knn2_chunk_pipeline_eval_variants(pkg, cases, golden_dir, knn_eval):
     finally:
         pkg.set_option("knn_eval", 0)
         torch.cuda.synchronize()
+
+
+@pytest.mark.parametrize("refine", [0, 1])
+def test_refine_variants_equal_cv2(pkg, cases, refine):
+    """Both forms of the refinement (0 = the fused kernel, the default; 1 = streaming classification + one warp per
+    row to evaluate) on the real pairs, where a third of the rows needs its winning chunk evaluated, and on a
+    bank built to send rows to the fallback sweep."""
+    data, ref = cases
+    pkg.set_option("refine", refine)
+    try:
+        assert pkg.get_option("refine") == refine
+        for case in ("16k", "ragged_8k_16k", "full"):
+            q, t = data[case]
+            bank = pkg.DescriptorBank.from_arrays([q, t])
+            for key, ratio, mutual in (("ratio_mutual", 0.75, True), ("ratio", 0.75, False), ("mutual", 0.0, True)):
+                gq, gt, gd = pkg.match_pairs(bank, [[0, 1]], ratio=ratio, mutual=mutual).to_lists()[0]
+                eq, et, ed = ref[case][key]
+                assert np.array_equal(gq, eq) and np.array_equal(gt, et), (case, key, len(gq), len(eq))
+                assert np.array_equal(_bits(gd), _bits(ed)), (case, key)
+        rng = np.random.default_rng(3)
+        arrays = [rng.integers(0, 256, size=(k, 128)).astype(np.uint8) for k in (3000, 2500, 1111)]   # uniform bytes: 10 % fall back
+        bank = pkg.DescriptorBank.from_arrays(arrays)
+        pairs = [[0, 1], [1, 2], [2, 0], [1, 0]]
+        got = pkg.match_pairs(bank, pairs, ratio=0.9, mutual=True).to_lists()
+        for (a, b), (gq, gt, gd) in zip(pairs, got):
+            eq, et, ed = oracle_cv2.match(arrays[a], arrays[b], 0.9, True)
+            assert np.array_equal(gq, eq) and np.array_equal(gt, et) and np.array_equal(_bits(gd), _bits(ed)), (a, b)
+    finally:
+        pkg.set_option("refine", 0)
+        torch.cuda.synchronize()
