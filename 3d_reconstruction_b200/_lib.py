@@ -35,6 +35,7 @@ SYMBOLS = (
     "b200m_five_point_f64",
     "b200m_assign_pairs_bf16",
     "b200m_vq_f32",
+    "b200m_vq_f32_static",
     "b200m_compact_matches",
     "b200m_match_stats_read",
     "b200m_profile_read",
@@ -109,6 +110,8 @@ def lib() -> C.CDLL:
                                          vp, sz, vp]
     L.b200m_vq_f32.restype = C.c_int
     L.b200m_vq_f32.argtypes = [vp, i64, i32, vp, i32, vp, vp, vp, vp]
+    L.b200m_vq_f32_static.restype = C.c_int
+    L.b200m_vq_f32_static.argtypes = [vp, i64, i32, vp, i32, vp, vp, vp]
     L.b200m_compact_matches.restype = C.c_int
     L.b200m_compact_matches.argtypes = [vp, vp, vp, vp, vp, i64, i64, vp, vp, vp, vp]
     L.b200m_profile_read.restype = C.c_int

@@ -1294,6 +1294,73 @@ int b200m_vq_f32(const float* obs, int64_t n_obs, int32_t dim, const double* cod
   return B200M_OK;
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// b200m_vq_f32_static: the vq entry point for callers that cannot hand us device scratch (plugins whose engine owns
+// the memory pool, bindings without the CUDA runtime, services forbidden to cudaMalloc after start-up). The squared
+// codebook norms go into an array that is part of this library's device image instead of caller memory: every GPU that
+// loads the library carries these 32 KiB until the process exits. Nothing on this path allocates or frees.
+//
+// g_vq_static_code_sqr is a __device__ variable. Device code may use the name directly; in HOST code the name is only
+// a handle for the runtime, not a device address, so it must never be passed to a kernel as is. The host gets the
+// real address from cudaGetSymbolAddress, per device (each device has its own copy at its own address).
+static __device__ __align__(256) double g_vq_static_code_sqr[B200M_VQ_STATIC_MAX_CODES];
+
+namespace {
+
+constexpr int kVqStaticMaxDevices = 64;
+
+// Device address of g_vq_static_code_sqr on the CURRENT device; looked up on the first call per device and kept.
+// cudaGetSymbolAddress allocates nothing (the array came with the module), but it is not a stream operation, which
+// is why the header asks for the first call on a device to happen outside stream capture.
+int vq_static_scratch(double** out) {
+  static std::mutex mu;
+  static double* addr[kVqStaticMaxDevices] = {};
+  int dev = -1;
+  CUDA_TRY(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kVqStaticMaxDevices) return fail(B200M_E_BAD_ARG, "b200m_vq_f32_static: device ordinal out of range%s");
+  std::lock_guard<std::mutex> lk(mu);
+  if (!addr[dev]) {
+    void* p = nullptr;
+    CUDA_TRY(cudaGetSymbolAddress(&p, g_vq_static_code_sqr));
+    if (!p) return fail(B200M_E_CUDA, "cudaGetSymbolAddress returned a null address for the built-in vq scratch%s");
+    addr[dev] = static_cast<double*>(p);
+  }
+  *out = addr[dev];
+  return B200M_OK;
+}
+
+}  // namespace
+
+int b200m_vq_f32_static(const float* obs, int64_t n_obs, int32_t dim, const double* codebook, int32_t n_codes,
+                        int32_t* out_code, double* out_dist, void* stream) {
+  if (n_obs == 0) return B200M_OK;
+  if (!obs || !codebook || !out_code || n_obs < 0 || n_codes <= 0) return fail(B200M_E_BAD_ARG, "null argument / bad sizes%s");
+  if (n_codes > B200M_VQ_STATIC_MAX_CODES) {
+    snprintf(g_err, sizeof(g_err),
+             "b200m_vq_f32_static: n_codes = %d exceeds the built-in scratch of %d codebook rows "
+             "(B200M_VQ_STATIC_MAX_CODES); call b200m_vq_f32 with caller-allocated scratch instead",
+             static_cast<int>(n_codes), B200M_VQ_STATIC_MAX_CODES);
+    return B200M_E_BAD_ARG;
+  }
+  if (dim <= 0 || dim > 256) return fail(B200M_E_BAD_DIM, "vq handles descriptor lengths up to 256%s");
+  if (device_info().ok != 1) return fail(B200M_E_NO_DEVICE, "no sm_100 CUDA device available (no CPU fallback)%s");
+  double* code_sqr = nullptr;
+  if (int rc = vq_static_scratch(&code_sqr)) return rc;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  // entries [0, n_codes) are rewritten here before the arg-min kernel (same stream) reads them, so whatever an earlier
+  // call left in the shared array does not matter and nothing has to be cleared
+  b200m::vq_code_sqr_kernel<<<(n_codes + 127) / 128, 128, 0, st>>>(codebook, dim, n_codes, code_sqr);
+  CUDA_TRY(cudaGetLastError());
+  const size_t smem = sizeof(double) * b200m::kVqObsPerBlock * dim;
+  CUDA_TRY(ensure_smem_attr(b200m::vq_argmin_kernel, 65536));
+  const int64_t blocks = (n_obs + b200m::kVqObsPerBlock - 1) / b200m::kVqObsPerBlock;
+  b200m::vq_argmin_kernel<<<static_cast<unsigned>(blocks), b200m::kVqThreads, smem, st>>>(
+      obs, n_obs, dim, codebook, code_sqr, n_codes, out_code, out_dist);
+  CUDA_TRY(cudaGetLastError());
+  g_prof.launches.fetch_add(2);
+  return B200M_OK;
+}
+
 int b200m_compact_matches(const int32_t* query_idx, const int32_t* train_idx, const float* dist,
                           const int32_t* count, const int64_t* offsets, int64_t n_pairs, int64_t cap,
                           int32_t* flat_query_idx, int32_t* flat_train_idx, float* flat_dist, void* stream) {

@@ -195,6 +195,30 @@ int b200m_assign_pairs_bf16(const void* mdesc_bf16, const float* matchability, c
 int b200m_vq_f32(const float* obs, int64_t n_obs, int32_t dim, const double* codebook, int32_t n_codes,
                  int32_t* out_code, double* out_dist, double* code_sqr_scratch, void* stream);
 
+/* b200m_vq_f32 for callers that cannot provide device scratch. (No counterpart in the reference: the reference never
+ * manages device memory itself.)
+ *
+ * b200m_vq_f32 needs a float64 [n_codes] scratch array that the caller allocates on the device. Some hosts of this
+ * library have no way to do that: a plugin that is handed its input and output device buffers by an engine which owns
+ * the memory pool, a binding (ctypes / cgo / JNI stub) that links this library but not the CUDA runtime, a service
+ * that runs inside a fixed memory budget where cudaMalloc after start-up is forbidden, or code running while another
+ * component holds the device in a state where allocation is not allowed. For them the squared codebook norms live in
+ * an array that is part of the library image itself: B200M_VQ_STATIC_MAX_CODES float64 values (32 KiB) in device
+ * global memory, held by every GPU that loads the library until the process exits.
+ *
+ * Same arguments (minus the scratch pointer), same kernels and bit-identical outputs as b200m_vq_f32. Differences:
+ *   - n_codes > B200M_VQ_STATIC_MAX_CODES is refused with B200M_E_BAD_ARG (use b200m_vq_f32 with your own scratch);
+ *   - the call allocates and frees nothing, on the device or through any library. The first call on each device looks
+ *     up the device address of the built-in array (once per device, with that device current); make that first call
+ *     before starting any stream capture;
+ *   - all calls on one device share the one array. It keeps whatever the previous call left there; nothing in it has
+ *     to start at zero, because each call rewrites entries [0, n_codes) before it reads them. Two calls that can run on
+ *     the GPU at the same time (different streams, or different host threads on different streams) race on it:
+ *     serialise them, or give all but one of them b200m_vq_f32 with private scratch. */
+#define B200M_VQ_STATIC_MAX_CODES 4096
+int b200m_vq_f32_static(const float* obs, int64_t n_obs, int32_t dim, const double* codebook, int32_t n_codes,
+                        int32_t* out_code, double* out_dist, void* stream);
+
 /* Batched geometric verification of match lists, the step after the matcher in the reference
  * (matching.py:133-142): cv2.findEssentialMat(k0, k1, K, method=RANSAC, prob=0.999, threshold=1)
  * followed by cv2.recoverPose(E, k0[mask], k1[mask], K).
