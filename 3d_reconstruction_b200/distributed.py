@@ -107,6 +107,39 @@ def allgather_bank(bank, n_loc: int) -> None:
         w.wait()
 
 
+def agree_all(ok: bool, device) -> bool:
+    """True on every rank iff `ok` is true on every rank (one MIN all-reduce of a flag). For decisions that pick which
+    collectives run next: if only some ranks took the other branch, the job would hang instead of failing."""
+    rank, ws = world()
+    if ws == 1:
+        return bool(ok)
+    flag = torch.tensor([1 if ok else 0], dtype=torch.int32, device=device)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    return bool(int(flag[0]))
+
+
+def check_counts_everywhere(count: torch.Tensor, cap: int) -> None:
+    """PairMatches.check_overflow as a COLLECTIVE: the smallest and the largest out_count over ALL ranks are reduced
+    (one MAX all-reduce of two numbers), and the same exception is raised on every rank -- OverflowError when some
+    pair on some rank found more matches than `cap`, ValueError when some rank's pair list named an image outside the
+    bank. Without this only the affected rank would raise, just before gather_packed, and the others would sit in that
+    collective until the backend's timeout. count: this rank's int32 out_count (may be empty)."""
+    rank, ws = world()
+    if count.numel():
+        mn, mx = torch.aminmax(count)
+        st = torch.stack([-mn, mx]).to(torch.int64)
+    else:
+        st = torch.tensor([0, 0], dtype=torch.int64, device=count.device)
+    if ws > 1:
+        dist.all_reduce(st, op=dist.ReduceOp.MAX)
+    neg_mn, mx = (int(x) for x in st.tolist())
+    if neg_mn > 0:
+        raise ValueError("on at least one rank the pair list names an image outside the bank (out_count = -1 for that pair)")
+    if mx > cap:
+        raise OverflowError(f"a pair (on some rank) produced {mx} matches but cap is {cap}; matches are never truncated "
+                            "silently -- raised on every rank")
+
+
 def gather_packed(counts: torch.Tensor, fields: list, n_pairs_of: list, dst: int = 0):
     """Variable-length gather of per-rank match lists with ONE size exchange and ONE message per rank.
     counts: int32 [P_r] matches per pair of this rank's (contiguous, rank-ordered) slice; fields: 4-byte tensors of
@@ -202,12 +235,19 @@ def _symm_bank(n_pad: int, ks: int, dev: torch.device):
     """Cached symmetric-memory bank, or None when symmetric memory cannot be set up here (then NCCL moves the bank)."""
     key = (n_pad, ks, dev.index)
     if key not in _symm_banks:
+        import warnings
         try:
-            _symm_banks[key] = _SymmBank(n_pad, ks, dev)
+            sb = _SymmBank(n_pad, ks, dev)
         except Exception as ex:      # no P2P mapping between these GPUs, or an older torch: fall back to the NCCL all-gather
-            import warnings
             warnings.warn(f"symmetric memory unavailable ({type(ex).__name__}: {ex}); using the NCCL all-gather")
-            _symm_banks[key] = None
+            sb = None
+        # the transport is a JOB-wide choice: a rank that went on alone to the NCCL all-gather while the others wait in
+        # the symmetric-memory barrier would hang the job. Every rank reaches this line once per shape (the cache keys
+        # are the same everywhere), so one flag all-reduce settles it.
+        if not agree_all(sb is not None, dev) and sb is not None:
+            warnings.warn("symmetric memory failed on another rank; every rank uses the NCCL all-gather")
+            sb = None
+        _symm_banks[key] = sb
     return _symm_banks[key]
 
 
@@ -359,7 +399,8 @@ def match_pairs_host(desc_host_local: torch.Tensor, k_per_image, n_img: int, pai
         match(rest0, P)
         if rank == dst:                                 # host work under the running kernels: gathered position -> list index
             order = torch.from_numpy(np.concatenate([pp[0] for pp in parts])).to(dev, non_blocking=True)
-        flat = out.flatten()
+        check_counts_everywhere(out.count, cap)          # collective: an overflow on one rank raises on all of them
+        flat = out.flatten(check=False)
         mark("match_rest", 1)
         counts = (flat.offsets[1:] - flat.offsets[:-1]).to(torch.int32)
         mark("gather", 0)

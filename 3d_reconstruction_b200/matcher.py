@@ -45,9 +45,11 @@ class PairMatches:
         if mx > self.cap:
             raise OverflowError(f"a pair produced {mx} matches but cap is {self.cap}; matches are never truncated silently")
 
-    def flatten(self) -> "FlatMatches":
-        """Device-side compaction into flat lists + offsets (one host sync for the total)."""
-        self.check_overflow()
+    def flatten(self, check: bool = True) -> "FlatMatches":
+        """Device-side compaction into flat lists + offsets (one host sync for the total). check=False only when the
+        caller has just validated the counts itself (distributed.check_counts_everywhere does so on all ranks at once)."""
+        if check:
+            self.check_overflow()
         P = int(self.count.numel())
         offsets = torch.zeros((P + 1,), dtype=torch.int64, device=self.count.device)
         if P:

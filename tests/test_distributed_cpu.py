@@ -232,3 +232,39 @@ def test_rank_throughput_weights_agree_on_all_ranks(tmp_path):
     assert abs(a["w"][0] / a["w"][1] - 1.1) < 0.01
     assert len(a["idx"]) > len(b["idx"])
     assert np.array_equal(np.sort(np.concatenate([a["idx"], b["idx"]])), np.arange(40 * 39 // 2))
+
+
+def _count_check_worker(rank, world, port, out_path):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    dmod = importlib.import_module("3d_reconstruction_b200.distributed")
+    seen = []
+    # (counts of rank 0, counts of rank 1, cap): only rank 1 overflows / only rank 0 holds a bad pair / an empty slice / fine
+    cases = [([3, 5, 0], [2, 9], 8), ([4, -1], [1, 1, 1], 8), ([], [8, 8], 8), ([1, 2], [], 1)]
+    for c0, c1, cap in cases:
+        mine = torch.tensor(c0 if rank == 0 else c1, dtype=torch.int32)
+        try:
+            dmod.check_counts_everywhere(mine, cap)
+            seen.append("ok")
+        except (OverflowError, ValueError) as ex:
+            seen.append(type(ex).__name__)
+        # the collective that follows in match_pairs_host must still line up on both ranks after an error
+        t = torch.tensor([rank + 1])
+        dist.all_reduce(t)
+        assert int(t) == 3
+    agreed = [dmod.agree_all(ok, "cpu") for ok in (True, rank == 0, False)]
+    torch.save({"seen": seen, "agreed": agreed}, f"{out_path}.{rank}")
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_count_errors_are_raised_on_every_rank(tmp_path):
+    """distributed.check_counts_everywhere / agree_all: an overflow (count > cap) or a bad pair (count = -1) on ONE
+    rank raises the same exception on BOTH, so no rank walks into gather_packed alone; a transport flag that only one
+    rank sets is false everywhere."""
+    out = str(tmp_path / "c")
+    mp.spawn(_count_check_worker, args=(2, _free_port(), out), nprocs=2, join=True)
+    a, b = torch.load(out + ".0", weights_only=False), torch.load(out + ".1", weights_only=False)
+    assert a["seen"] == b["seen"] == ["OverflowError", "ValueError", "ok", "OverflowError"]
+    assert a["agreed"] == b["agreed"] == [True, False, False]
