@@ -34,7 +34,7 @@ namespace {
 thread_local char g_err[512] = "";
 
 // Process-global tuning knobs; every field is an atomic so that a set_option from one host thread and a
-// launch from another never race (each entry point reads a knob once per call).
+// launch from another never race. Entry points do not read these directly: see OptScope / opt() below.
 struct Options {
   std::atomic<int64_t> epilogue{1};
   std::atomic<int64_t> grid{0};
@@ -57,6 +57,43 @@ struct Options {
   // many rows need it: 1.8x faster refinement on uniform random bytes, 23 us more per batch otherwise)
   std::atomic<int64_t> refine{0};
 } g_opt;
+
+// One consistent view of the knobs per entry-point call. A public entry point opens an OptScope first thing; the
+// outermost scope on this host thread copies every knob ONCE, and everything below it -- the workspace size check, the
+// batch size the workspace is carved for, the per-batch kernel choices, nested public calls such as
+// b200m_workspace_bytes -- reads that copy through opt(). A b200m_set_option from another thread therefore takes effect
+// at the next call, never in the middle of one (where a larger "batch" between the size check and the carve would make
+// the kernels write past the checked workspace).
+struct OptSnap {
+  int64_t epilogue, grid, batch, kernel, pipeline, chunk, float_sweep, knn_eval, refine;
+};
+thread_local OptSnap t_opt;
+thread_local int t_opt_depth = 0;
+
+void snapshot_options() {
+  t_opt.epilogue = g_opt.epilogue.load();
+  t_opt.grid = g_opt.grid.load();
+  t_opt.batch = g_opt.batch.load();
+  t_opt.kernel = g_opt.kernel.load();
+  t_opt.pipeline = g_opt.pipeline.load();
+  t_opt.chunk = g_opt.chunk.load();
+  t_opt.float_sweep = g_opt.float_sweep.load();
+  t_opt.knn_eval = g_opt.knn_eval.load();
+  t_opt.refine = g_opt.refine.load();
+}
+
+struct OptScope {
+  OptScope() { if (t_opt_depth++ == 0) snapshot_options(); }
+  ~OptScope() { --t_opt_depth; }
+  OptScope(const OptScope&) = delete;
+  OptScope& operator=(const OptScope&) = delete;
+};
+
+// the knobs as the current entry-point call sees them (outside any scope: as they are right now)
+const OptSnap& opt() {
+  if (t_opt_depth == 0) snapshot_options();
+  return t_opt;
+}
 
 // Optional per-launch timing of the sweeps with CUDA events on the launching stream ("profile" option).
 // The event pool and the lists are guarded by `mu` (two host threads may launch concurrently); the pool is
@@ -301,7 +338,7 @@ template <int kKind>
 int launch_any(const CUtensorMap& tmap_a, const CUtensorMap& tmap_a2, const CUtensorMap& tmap_b,
                const b200m::SweepParams& sp, int grid, cudaStream_t st) {
 #ifdef B200M_EXPERIMENTAL
-  if (g_opt.kernel == 4) return launch_sweep_pair<kKind>(tmap_a, tmap_a2, tmap_b, sp, grid, st);
+  if (opt().kernel == 4) return launch_sweep_pair<kKind>(tmap_a, tmap_a2, tmap_b, sp, grid, st);
 #endif
   return launch_sweep<kKind>(tmap_a, tmap_a2, tmap_b, sp, grid, st);
 }
@@ -310,7 +347,7 @@ constexpr int64_t kDefaultBatchRows = int64_t(1) << 22;   // pairs * k_stride pe
 
 // Largest internal batch a call over n_pairs pairs may use: what the workspace is sized and carved for.
 int64_t batch_cap(int64_t k_stride, int64_t n_pairs) {
-  const int64_t opt_batch = g_opt.batch;
+  const int64_t opt_batch = opt().batch;
   int64_t b = opt_batch > 0 ? opt_batch : (kDefaultBatchRows / (k_stride > 0 ? k_stride : 1));
   if (b < 1) b = 1;
   if (b > n_pairs) b = n_pairs;
@@ -433,7 +470,7 @@ int grid_for(int64_t work, int block) {
 }
 
 int sweep_grid(int64_t items) {
-  const int64_t opt_grid = g_opt.grid;
+  const int64_t opt_grid = opt().grid;
   int grid = opt_grid > 0 ? static_cast<int>(opt_grid) : device_info().sms;
   if (grid > items) grid = static_cast<int>(items);
   return grid < 1 ? 1 : grid;
@@ -475,7 +512,7 @@ b200m::SweepParams base_params(const int32_t* norm_table, int32_t n_img, const i
 // exact2: the second neighbour must be exact (knnMatch output / top-2 pipeline).
 int sweep_rows(const CUtensorMap& tmap_bank, const b200m::SweepParams& sp, bool exact2, cudaStream_t st) {
   const int grid = sweep_grid(static_cast<int64_t>(sp.n_pairs) * sp.blocks_per_pair);
-  switch (g_opt.epilogue) {
+  switch (opt().epilogue) {
     case 0: return launch_any<b200m::kTop2Exact>(tmap_bank, tmap_bank, tmap_bank, sp, grid, st);
     case 2: return launch_any<b200m::kPeak>(tmap_bank, tmap_bank, tmap_bank, sp, grid, st);
     default:
@@ -742,6 +779,7 @@ int b200m_bank_sort_u8(const uint8_t* bank, const int32_t* norm_table, const int
 }
 
 size_t b200m_workspace_bytes(int64_t k_stride, int64_t n_pairs) {
+  OptScope opt_scope;
   if (k_stride <= 0 || n_pairs <= 0) return 256;
   return carve(nullptr, nullptr, batch_cap(k_stride, n_pairs), k_stride);
 }
@@ -749,6 +787,7 @@ size_t b200m_workspace_bytes(int64_t k_stride, int64_t n_pairs) {
 int b200m_knn2_u8(const uint8_t* bank, const int32_t* norm_table, const int32_t* k_per_image, int32_t n_img,
                   int64_t k_stride, const int32_t* pairs, int64_t n_pairs, int32_t* out_train_idx,
                   float* out_dist, void* workspace, size_t workspace_bytes, void* stream) {
+  OptScope opt_scope;
   int rc = check_common(bank, norm_table, k_per_image, n_img, k_stride, pairs, n_pairs);
   if (rc) return rc;
   if (n_pairs == 0) return B200M_OK;
@@ -779,6 +818,7 @@ int b200m_knn2_sorted_u8(const uint8_t* bank, const int32_t* norm_table, const u
                          const int32_t* sort_table, const int32_t* k_per_image, int32_t n_img, int64_t k_stride,
                          const int32_t* pairs, int64_t n_pairs, int32_t* out_train_idx, float* out_dist, void* workspace,
                          size_t workspace_bytes, void* stream) {
+  OptScope opt_scope;
   int rc = check_common(bank, norm_table, k_per_image, n_img, k_stride, pairs, n_pairs);
   if (rc) return rc;
   if (n_pairs == 0) return B200M_OK;
@@ -842,7 +882,7 @@ int b200m_knn2_sorted_u8(const uint8_t* bank, const int32_t* norm_table, const u
     {
       ProfScope ps(&g_prof.refine, st);
       b200m::knn_bucket_kernel<<<static_cast<unsigned>(nb), 1024, 0, st>>>(kp);
-      if (g_opt.knn_eval == 0)
+      if (opt().knn_eval == 0)
         b200m::knn_eval_tc_kernel<<<dim3(static_cast<unsigned>(kp.n_chunks), static_cast<unsigned>(nb)), b200m::kKnnTcThreads, 0, st>>>(kp);
       else
         b200m::knn_eval_kernel<<<dim3(static_cast<unsigned>(kp.n_chunks), static_cast<unsigned>(nb)), b200m::kKnnEvalThreads, 0, st>>>(kp);
@@ -869,6 +909,7 @@ int b200m_match_pairs_u8(const uint8_t* bank, const int32_t* norm_table, const u
                          const int32_t* pairs, int64_t n_pairs, double ratio, int mutual, int32_t* out_query_idx,
                          int32_t* out_train_idx, float* out_dist, int32_t* out_count, int64_t cap, void* workspace,
                          size_t workspace_bytes, void* stream) {
+  OptScope opt_scope;
   int rc = check_common(bank, norm_table, k_per_image, n_img, k_stride, pairs, n_pairs);
   if (rc) return rc;
   if (n_pairs == 0) return B200M_OK;
@@ -892,12 +933,12 @@ int b200m_match_pairs_u8(const uint8_t* bank, const int32_t* norm_table, const u
   CUDA_TRY(cudaMemsetAsync(w.stats, 0, sizeof(unsigned long long) * b200m::kStatSlots * b200m::kStatFields, st));
 
   // ---------------------------------------------------------------- pipeline 2: chunk sweep on the sorted bank
-  if (g_opt.pipeline == 2 && sorted_bank && g_opt.epilogue != 0) {
+  if (opt().pipeline == 2 && sorted_bank && opt().epilogue != 0) {
     rc = make_row_tmap(&tmap_sbank, sorted_bank, static_cast<uint64_t>(n_img) * k_stride);
     if (rc) return rc;
     const SortTable tv = sort_table_view(sort_table, n_img, k_stride);
     const int do_ratio = ratio > 0.0 ? 1 : 0;
-    const int64_t opt_kernel = g_opt.kernel;
+    const int64_t opt_kernel = opt().kernel;
     for (int64_t p0 = 0; p0 < n_pairs; p0 += B) {
       const int64_t nb = (n_pairs - p0 < B) ? (n_pairs - p0) : B;
       const int32_t* pb = pairs + 2 * p0;
@@ -910,8 +951,8 @@ int b200m_match_pairs_u8(const uint8_t* bank, const int32_t* norm_table, const u
       cp.blocks_per_pair = static_cast<int32_t>(k_stride / b200m::kRows);
       cp.n_img = n_img;
       cp.rowres = w.rowres;
-      cp.peak = g_opt.epilogue == 2 ? 1 : 0;
-      cp.chunk_cols = opt_kernel == 6 ? 64 : (opt_kernel == 5 && g_opt.chunk == 64 && !cp.peak) ? 64 : 32;
+      cp.peak = opt().epilogue == 2 ? 1 : 0;
+      cp.chunk_cols = opt_kernel == 6 ? 64 : (opt_kernel == 5 && opt().chunk == 64 && !cp.peak) ? 64 : 32;
       rc = launch_chunk_sweep(tmap_sbank, cp, opt_kernel == 6 ? sweep_grid(1 << 20) : sweep_grid(nb * cp.blocks_per_pair),
                               opt_kernel, st);
       if (rc) return rc;
@@ -942,7 +983,7 @@ int b200m_match_pairs_u8(const uint8_t* bank, const int32_t* norm_table, const u
       rp.need_list = w.cand_q;
       {
         dim3 grid(static_cast<unsigned>((k_stride + b200m::kRefineThreads - 1) / b200m::kRefineThreads), static_cast<unsigned>(nb));
-        if (g_opt.refine == 1) {
+        if (opt().refine == 1) {
           CUDA_TRY(cudaMemsetAsync(rp.need_count, 0, sizeof(int32_t) * nb, st));
           ProfScope ps(&g_prof.refine, st);
           b200m::refine_classify_kernel<<<grid, b200m::kRefineThreads, 0, st>>>(rp);
@@ -991,7 +1032,7 @@ int b200m_match_pairs_u8(const uint8_t* bank, const int32_t* norm_table, const u
   // ---------------------------------------------------------------- pipelines 0 / 1 (original bank only)
   // pipeline 1: top-1 sweep, the Lowe test is settled by a verify sweep over the candidates;
   // pipeline 0 (and the debug epilogue): exact top-2 sweep, only the mutual check is verified.
-  const bool exact2 = g_opt.pipeline == 0 || g_opt.epilogue == 0;
+  const bool exact2 = opt().pipeline == 0 || opt().epilogue == 0;
   const int do_ratio = (!exact2 && ratio > 0.0) ? 1 : 0;
   for (int64_t p0 = 0; p0 < n_pairs; p0 += B) {
     const int64_t nb = (n_pairs - p0 < B) ? (n_pairs - p0) : B;
@@ -1025,6 +1066,7 @@ int b200m_match_pairs_u8(const uint8_t* bank, const int32_t* norm_table, const u
 }
 
 size_t b200m_workspace_bytes_bf16(int64_t k_stride, int64_t n_pairs) {
+  OptScope opt_scope;
   if (k_stride <= 0 || n_pairs <= 0) return 256;
   return static_cast<size_t>(2) * batch_cap(k_stride, n_pairs) * k_stride * sizeof(float2) + 512;
 }
@@ -1034,6 +1076,7 @@ int b200m_match_pairs_bf16(const void* bank_bf16, const int32_t* k_per_image, in
                            int use_threshold, int mutual, int32_t* out_query_idx, int32_t* out_train_idx,
                            float* out_score, int32_t* out_count, int64_t cap, void* workspace,
                            size_t workspace_bytes, void* stream) {
+  OptScope opt_scope;
   if (!bank_bf16 || !k_per_image || n_img <= 0) return fail(B200M_E_BAD_ARG, "null bank / k_per_image or n_img <= 0%s");
   if (dim != 128 && dim != 256) return fail(B200M_E_BAD_DIM, "the bf16 path handles descriptor lengths 128 and 256%s");
   if (k_stride <= 0 || (k_stride % B200M_TILE_T) != 0)
@@ -1053,7 +1096,7 @@ int b200m_match_pairs_bf16(const void* bank_bf16, const int32_t* k_per_image, in
   float2* rowbest = reinterpret_cast<float2*>((reinterpret_cast<uintptr_t>(workspace) + 255) & ~uintptr_t(255));
   for (int64_t p0 = 0; p0 < n_pairs; p0 += B) {
     const int64_t nb = (n_pairs - p0 < B) ? (n_pairs - p0) : B;
-    if (g_opt.float_sweep == 0) {
+    if (opt().float_sweep == 0) {
       rc = float_single_sweep_batch(tmap, k_per_image, n_img, k_stride, dim, pairs + 2 * p0, nb, B * k_stride, rowbest, nullptr,
                                     score_threshold, use_threshold, mutual ? 1 : 0, out_query_idx + p0 * cap,
                                     out_train_idx + p0 * cap, out_score + p0 * cap, out_count + p0, cap, st);
@@ -1091,10 +1134,13 @@ int b200m_match_pairs_bf16(const void* bank_bf16, const int32_t* k_per_image, in
 // single-sweep log-sum-exp float [B][k_stride / 256][k_stride].
 constexpr int64_t kMaxNormImgs = 1 << 18;
 size_t b200m_workspace_bytes_assign(int64_t k_stride, int64_t n_pairs) {
+  OptScope opt_scope;
   if (k_stride <= 0 || n_pairs <= 0) return 256;
   const size_t B = static_cast<size_t>(batch_cap(k_stride, n_pairs));
-  return 2 * B * k_stride * (sizeof(float2) + sizeof(float)) + kMaxNormImgs * sizeof(float) + 1024 +
-         B * static_cast<size_t>(k_stride / 256) * k_stride * sizeof(float) + 1024;
+  // the column partial sums -- the one term that grows with k_stride^2 (1 GiB at k_stride = 16,384, B = 256) -- are
+  // only needed when the single-sweep log-sum-exp can run at all, i.e. with "float_sweep" = 0
+  const size_t colpart = opt().float_sweep == 0 ? B * static_cast<size_t>(k_stride / 256) * k_stride * sizeof(float) : 0;
+  return 2 * B * k_stride * (sizeof(float2) + sizeof(float)) + kMaxNormImgs * sizeof(float) + 1024 + colpart + 1024;
 }
 
 int b200m_assign_pairs_bf16(const void* mdesc_bf16, const float* matchability, const int32_t* k_per_image,
@@ -1102,6 +1148,7 @@ int b200m_assign_pairs_bf16(const void* mdesc_bf16, const float* matchability, c
                             float filter_threshold, int use_threshold, int32_t* out_query_idx, int32_t* out_train_idx,
                             float* out_score, int32_t* out_count, int64_t cap, void* workspace, size_t workspace_bytes,
                             void* stream) {
+  OptScope opt_scope;
   if (!mdesc_bf16 || !matchability || !k_per_image || n_img <= 0)
     return fail(B200M_E_BAD_ARG, "null descriptors / matchability / k_per_image or n_img <= 0%s");
   if (dim != 128 && dim != 256) return fail(B200M_E_BAD_DIM, "the bf16 path handles descriptor lengths 128 and 256%s");
@@ -1126,7 +1173,7 @@ int b200m_assign_pairs_bf16(const void* mdesc_bf16, const float* matchability, c
   float* colpart = reinterpret_cast<float*>(lse_flag + 64);
   // pass 1 as ONE sweep per pair too (row and column log-sum-exp from the same exponentials) unless the two-direction
   // sweeps are asked for; needs the largest row norm of every image as the common reference point
-  const bool lse_single = g_opt.float_sweep == 0 && n_img <= kMaxNormImgs;
+  const bool lse_single = opt().float_sweep == 0 && n_img <= kMaxNormImgs;
   if (lse_single) {
     CUDA_TRY(cudaMemsetAsync(maxnorm, 0, sizeof(float) * n_img, st));
     const int64_t rows = static_cast<int64_t>(n_img) * k_stride;
@@ -1182,7 +1229,7 @@ int b200m_assign_pairs_bf16(const void* mdesc_bf16, const float* matchability, c
     rc = dim == 256 ? launch_ip_sweep<256, b200m::ip::kIpLse>(tmap, ip, grid, st)
                     : launch_ip_sweep<128, b200m::ip::kIpLse>(tmap, ip, grid, st);
     if (rc) return rc;
-    if (g_opt.float_sweep == 0) {      // pass 2 as ONE sweep per pair: row arg-max and column maxima of the full score
+    if (opt().float_sweep == 0) {      // pass 2 as ONE sweep per pair: row arg-max and column maxima of the full score
       rc = float_single_sweep_batch(tmap, k_per_image, n_img, k_stride, dim, pairs + 2 * p0, nb, B * k_stride, rowbest, nbuf,
                                     filter_threshold, use_threshold, 1, out_query_idx + p0 * cap, out_train_idx + p0 * cap,
                                     out_score + p0 * cap, out_count + p0, cap, st);

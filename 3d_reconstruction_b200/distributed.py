@@ -236,6 +236,7 @@ def _symm_bank(n_pad: int, ks: int, dev: torch.device):
     key = (n_pad, ks, dev.index)
     if key not in _symm_banks:
         import warnings
+        release_symm_banks()         # one shape at a time: a bank + its sorted copy per shape would pile up otherwise
         try:
             sb = _SymmBank(n_pad, ks, dev)
         except Exception as ex:      # no P2P mapping between these GPUs, or an older torch: fall back to the NCCL all-gather
@@ -249,6 +250,15 @@ def _symm_bank(n_pad: int, ks: int, dev: torch.device):
             sb = None
         _symm_banks[key] = sb
     return _symm_banks[key]
+
+
+def release_symm_banks() -> None:
+    """Drop the cached symmetric-memory bank(s) so their device memory (a whole bank, its norm-sorted copy and the
+    tables, per rank) can be reused. Called automatically when match_pairs_host meets a new bank shape (the cache holds
+    ONE shape); call it yourself after the last match_pairs_host of a job. Every rank must do so at the same point of
+    the program, like any other step of a multi-rank job (the next call rebuilds the buffers collectively)."""
+    for key in [k for k in _symm_banks if k[0] != "nccl"]:
+        del _symm_banks[key]
 
 
 def transport_in_use() -> str:

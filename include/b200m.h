@@ -177,7 +177,13 @@ int b200m_match_pairs_bf16(const void* bank_bf16, const int32_t* k_per_image, in
  * A row i matches j when j = arg-max_j score[i,:], i = arg-max_i score[:,j] and (use_threshold != 0)
  * exp(score) > filter_threshold. out_score = exp(score) (= matching_scores0 of the reference);
  * other outputs as b200m_match_pairs_u8. With use_threshold == 0 the list holds every mutual pair,
- * from which matches0/1 and matching_scores0/1 of the reference follow exactly (host side). */
+ * from which matches0/1 and matching_scores0/1 of the reference follow exactly (host side).
+ * Workspace footprint, with B = pairs per internal batch (min(n_pairs, 2^22 / k_stride) unless "batch" is set):
+ *   24 * B * k_stride bytes (row results and log-sum-exp tables) + 1 MiB (largest row norm per image)
+ *   + with "float_sweep" = 0 only: 4 * B * (k_stride / 256) * k_stride bytes of column partial sums -- quadratic in
+ *     k_stride: 128 MiB at k_stride = 2,048 (B = 2,048), 1 GiB at k_stride = 16,384 (B = 256); lower "batch" to shrink it.
+ * The size depends on the "float_sweep" and "batch" options as they are when b200m_workspace_bytes_assign is called:
+ * a workspace sized under one setting and used under another is refused with B200M_E_WORKSPACE if it is too small. */
 size_t b200m_workspace_bytes_assign(int64_t k_stride, int64_t n_pairs);
 int b200m_assign_pairs_bf16(const void* mdesc_bf16, const float* matchability, const int32_t* k_per_image,
                             int32_t n_img, int64_t k_stride, int32_t dim,

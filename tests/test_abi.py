@@ -34,6 +34,24 @@ def test_options_roundtrip(pkg):
         pkg.set_option("nonsense", 1)
 
 
+def test_options_are_read_afresh_by_every_call(pkg):
+    """Entry points work on a per-call copy of the knobs (one consistent view from the workspace check to the last
+    batch); the copy must not outlive the call: a set_option shows in the very next size query, both ways."""
+    lib = pkg._lib.lib()
+    base = lib.b200m_workspace_bytes(256, 100)
+    pkg.set_option("batch", 7)
+    small = lib.b200m_workspace_bytes(256, 100)
+    pkg.set_option("batch", 0)
+    assert small < base and lib.b200m_workspace_bytes(256, 100) == base
+    # the head's column partial sums (quadratic in k_stride) are only part of the size when the single-sweep
+    # log-sum-exp can run ("float_sweep" = 0)
+    one = lib.b200m_workspace_bytes_assign(2048, 64)
+    pkg.set_option("float_sweep", 1)
+    two = lib.b200m_workspace_bytes_assign(2048, 64)
+    pkg.set_option("float_sweep", 0)
+    assert one - two == 64 * (2048 // 256) * 2048 * 4 and lib.b200m_workspace_bytes_assign(2048, 64) == one
+
+
 def test_workspace_bytes_saturates(pkg):
     lib = pkg._lib.lib()
     small = lib.b200m_workspace_bytes(256, 1)
