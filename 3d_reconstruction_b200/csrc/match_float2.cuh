@@ -33,7 +33,11 @@ namespace ip {
 
 constexpr int kRows2 = 256;                       // rows per work item (two M-tiles)
 constexpr int kBStages2 = 5;
-constexpr int kColKeyNone = static_cast<int>(0x80808080u);   // cudaMemset(0x80): below the key of every finite score
+// cudaMemset(0x80). As an ordered key this is the score -3.39e38 (float bits 0xff7f7f7f), NOT below every finite key
+// (key(-FLT_MAX) = 0x80800000 is smaller): a column whose largest score lay under -3.39e38 would keep the pre-set value
+// and simply find no row equal to it, i.e. stay unmatched. Scores of that size do not come out of these sweeps (inner
+// products of bf16 rows with finite norms, log-assignments of them), so it serves as "no row seen yet".
+constexpr int kColKeyNone = static_cast<int>(0x80808080u);
 constexpr int kClaimNone = 0x7f7f7f7f;                        // cudaMemset(0x7f): above every row index
 
 template <int kDim>
@@ -69,7 +73,11 @@ struct Ip2Params {
   int32_t* lse_flag;            // out: set when a sum left the fp32 range (the caller re-runs the batch on the two-direction sweep)
 };
 
-constexpr float kLseTiny = 7.9e-31f;   // 2^-100: a sum below it had its largest term within 2^26 of the smallest normal
+// Smallest sum the single-sweep log-sum-exp accepts, PER TERM of the sum: ex2.approx.ftz flushes every exponential below
+// 2^-126 to zero, so a sum of n terms can silently lose up to n * 2^-126; asking for sum >= n * 2^-102 keeps that loss
+// below 2^-24 of the sum (fp32 rounding) whatever the number of columns / rows. Smaller sums raise lse_flag and the
+// batch is redone with per-row maxima. (n = 16,384: 2^-88, i.e. a largest term ~61 nats below the reference point.)
+constexpr float kLseTinyPerTerm = 0x1p-102f;
 
 // Column sums over the 32 lanes of a warp for 32 columns at once: c[k] (k = 0..31) holds this lane's value of
 // column k; afterwards c[0] of lane l is the sum over all lanes of column l. Butterfly: at every step a lane keeps
@@ -261,8 +269,9 @@ ip_sweep2_kernel(const __grid_constant__ CUtensorMap tmap, const Ip2Params p) {
         // ---- log-sum-exp of every row AND every column of sim (lightglue.py:196-208) from ONE sweep.
         // Reference point of the exponentials: ref = |longest query row| * |longest train row| >= every sim[i, j]
         // (Cauchy-Schwarz), the same for the whole pair, so that exp(sim - ref) <= 1 serves the row sums and the
-        // column sums alike -- one ex2 per score. A row / column whose largest term sits more than ~ 69 nats below
-        // ref would lose it to the fp32 range: such sums raise lse_flag and the caller falls back.
+        // column sums alike -- one ex2 per score. A row / column whose largest term sits more than ~ 61-69 nats
+        // (kLseTinyPerTerm times the number of terms) below ref would lose part of its sum to the fp32 range: such
+        // sums raise lse_flag and the caller falls back.
         const float ref = sqrtf(__ldg(p.maxnorm + row_img) * __ldg(p.maxnorm + col_img));
         const float ref2 = ref * kLog2e;
         float rs0 = 0.f, rs1 = 0.f;
@@ -356,7 +365,7 @@ ip_sweep2_kernel(const __grid_constant__ CUtensorMap tmap, const Ip2Params p) {
             float ss = m ? rs1 : rs0;
 #pragma unroll
             for (int oo = 0; oo < 3; ++oo) ss += rsum[(par * 3 + oo) * kRows2 + r];
-            if (!(ss >= kLseTiny) || ss > 3.0e38f) atomicOr(p.lse_flag, 1);
+            if (!(ss >= kLseTinyPerTerm * static_cast<float>(n_cols)) || ss > 3.0e38f) atomicOr(p.lse_flag, 1);
             const int64_t row = static_cast<int64_t>(blk) * kRows2 + r;
             p.nbw[obase + row] = log_sigmoid(__ldg(p.z + static_cast<int64_t>(row_img) * p.k_stride + row)) - (ref + logf(ss));
           }
@@ -567,7 +576,7 @@ ip_lse_finalize_kernel(const float* __restrict__ colpart, const float* __restric
   const float* src = colpart + static_cast<int64_t>(pair) * parts_all * k_stride + col;
   float ss = 0.f;
   for (int q = 0; q < parts; ++q) ss += src[static_cast<int64_t>(q) * k_stride];
-  if (!(ss >= kLseTiny) || ss > 3.0e38f) atomicOr(lse_flag, 1);
+  if (!(ss >= kLseTinyPerTerm * static_cast<float>(pi.kq)) || ss > 3.0e38f) atomicOr(lse_flag, 1);
   const float ref = sqrtf(__ldg(maxnorm + pi.qi) * __ldg(maxnorm + pi.ti));
   nb[(static_cast<int64_t>(n_pairs) + pair) * k_stride + col] =
       log_sigmoid(__ldg(z + static_cast<int64_t>(pi.ti) * k_stride + col)) - (ref + logf(ss));

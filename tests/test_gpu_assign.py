@@ -145,10 +145,33 @@ def test_assignment_head_module_vs_fp32_restatement(pkg):
         assert torch.all(out["scores"][i] > 0.1)
 
 
+@pytest.mark.parametrize("below", [56.0, 62.0, 68.0])
+def test_assign_row_maxima_near_the_edge_of_the_common_reference_range(pkg, below):
+    """Every row but one has its largest score `below` nats under the pair's reference point (one long row and the
+    longest column set it), with 2,048 columns: around 60 nats the single-sweep sums come close to where flushed
+    exponentials (ex2.approx.ftz, < 2^-126 each, up to n of them) would stop being negligible. The accepted range
+    scales with the number of terms (kLseTinyPerTerm); on either side of that edge -- single sweep kept, or batch redone
+    with per-row maxima -- partners and scores must be the oracle's."""
+    dim, m, n = 128, 1200, 2048
+    gen = torch.Generator().manual_seed(123)
+    world = torch.nn.functional.normalize(torch.randn(2600, dim, generator=gen), dim=1)
+    d0 = 4.5 * torch.nn.functional.normalize(world[torch.randperm(2600, generator=gen)[:m]] + 0.04 * torch.randn(m, dim, generator=gen), dim=1)
+    d1 = 4.5 * torch.nn.functional.normalize(world[torch.randperm(2600, generator=gen)[:n]] + 0.04 * torch.randn(n, dim, generator=gen), dim=1)
+    d0[17] *= (20.0 + below) / 20.25                       # reference point = |d0[17]| * 4.5 = 20 + below; other rows peak near 20
+    d0, d1 = d0.to(torch.bfloat16).float().numpy(), d1.to(torch.bfloat16).float().numpy()
+    z0 = (1.0 + 1.5 * torch.randn(m, generator=gen)).numpy()
+    z1 = (1.0 + 1.5 * torch.randn(n, generator=gen)).numpy()
+    for th in (None, 0.1):
+        q, t, s = _run_pair(pkg, d0, d1, z0, z1, th)
+        _, _, _, (m0, _, ms0, _), _ = oracle_float.assign(d0, d1, z0, z1, th)
+        _compare(q, t, s, m0, ms0, min_agree=0.99)
+        assert len(q) > 100
+
+
 @pytest.mark.parametrize("case", ["all_rows_long", "one_long_row"])
 def test_assign_scores_outside_the_common_reference_range(pkg, case):
     """The single-sweep log-sum-exp measures every exponential of a pair from ONE reference point (the product of the
-    longest row norms). Rows whose largest score lies far below it (> ~69 nats) would lose their sums to the fp32
+    longest row norms). Rows whose largest score lies far below it (> ~61-69 nats) would lose their sums to the fp32
     range: the kernel flags that and the batch is redone with per-row maxima. Long descriptors (|d| = 30: scores up
     to 900) and a single outlier row that inflates the reference must give the oracle's result all the same."""
     dim, m, n = 128, 600, 520

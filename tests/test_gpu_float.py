@@ -105,3 +105,28 @@ def test_float_lightglue_shaped(pkg):
     assert agree >= 0.995 and gap <= 1e-5
     m0 = out["matches0"][0].cpu().numpy()
     assert (m0[matches[:, 0]] == matches[:, 1]).all()
+
+
+def test_float_exact_tie_between_rows_is_a_pinned_contract(pkg, float_sweep):
+    """Rows 0 and 1 score bit-equal (1.0) in column 0; row 0 itself prefers column 1 (2.0). The reference
+    (lightglue.py:237-242: scores.max(1).indices, the FIRST maximal row) gives column 0 to row 0, whose own
+    arg-max lies elsewhere, so column 0 and row 1 stay unmatched -- the sweep per direction ("float_sweep" = 1) and
+    the oracle do exactly that. The single sweep (default) resolves the tie among the rows whose own arg-max IS the
+    column and therefore also emits (1, 0): a documented deviation on exact ties between different rows (DESIGN.md
+    section 3.7), pinned here for both settings so that it cannot change unnoticed."""
+    dim = 128
+    d0 = np.zeros((3, dim), np.float32)
+    d1 = np.zeros((3, dim), np.float32)
+    d1[0, 0] = 1.0                     # column 0 = e0
+    d1[1, 1] = 1.0                     # column 1 = e1
+    d1[2, 5] = 1.0
+    d0[0, 0], d0[0, 1] = 1.0, 2.0      # row 0: sim = (1, 2, 0) -> prefers column 1
+    d0[1, 0] = 1.0                     # row 1: sim = (1, 0, 0) -> prefers column 0, ties with row 0 there
+    d0[2, 5] = 3.0                     # row 2 <-> column 2: an undisputed pair
+    q, t, s = pkg.match_float(d0, d1)
+    eq, et, es = oracle_float.match(d0, d1)
+    assert list(zip(eq.tolist(), et.tolist())) == [(0, 1), (2, 2)]        # the reference's answer
+    if float_sweep == 1:
+        assert list(zip(q.tolist(), t.tolist())) == [(0, 1), (2, 2)] and s.tolist() == [2.0, 3.0]
+    else:
+        assert list(zip(q.tolist(), t.tolist())) == [(0, 1), (1, 0), (2, 2)] and s.tolist() == [2.0, 1.0, 3.0]
