@@ -10,6 +10,7 @@ from .matcher import (B200Matcher, FlatMatches, MatchConfig, PairMatches, digest
                       match, match_float, match_pairs, match_pairs_float, match_pairs_host)
 from .assignment import AssignmentHead, assign_pairs  # noqa: F401
 from .geometry import PoseBatch, essential_ransac  # noqa: F401
+from .features import build_codebook, extract_features, sift_features  # noqa: F401
 from .driver import Gates, bow_view_graph, match_view_graph, run_matching_stage, save_matches, vq_words  # noqa: F401
 from .scheduler import (blocked_order, exhaustive_pairs, partition, partition_by_owner, window_pairs,  # noqa: F401
                         window_shard)

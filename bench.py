@@ -303,6 +303,89 @@ def secondary_real_sift(pkg, torch, dev, int8_peak):
             "workload": f"real SIFT, DSC_0001 <-> DSC_0002, {kq} x {kt} descriptors, ratio 0.75 + mutual, both directions x 8"}
 
 
+def _flat_digest(torch, out):
+    """Order-sensitive 64-bit digest of a PairMatches (counts, indices and the float32 distance bits), on the device."""
+    flat = out.flatten()
+    h = torch.zeros((), dtype=torch.int64, device=flat.offsets.device)
+    for i, t in enumerate((flat.offsets, flat.query_idx, flat.train_idx, flat.dist.view(torch.int32))):
+        v = t.to(torch.int64)
+        w = torch.arange(1, v.numel() + 1, dtype=torch.int64, device=v.device) * (2 * i + 3)
+        h = h * 1000003 + (v * w).sum()
+    return f"{int(h.item()) & 0xFFFFFFFFFFFFFFFF:016x}"
+
+
+def secondary_mutual_only(pkg, torch, dev, int8_peak):
+    """The reference matcher's OWN rule -- mutual arg-best, no ratio test (lightglue.py:235-254; cv2
+    BFMatcher(crossCheck=True)) -- on BASELINE config 3 shapes: 512 directed pairs over 33 images x 16,384, once with
+    both directions of 256 image pairs in the list and once with 512 pairs in one direction only. With ratio <= 0 every
+    query row is a candidate, so the mutual check is a second full sweep (the verify sweep): this row puts that cost on
+    the record. Size-independent check, outside the timed region: the mutual lists of (a, b) and (b, a) are each
+    other's transposes."""
+    syn = importlib.import_module("3d_reconstruction_b200.synthetic")
+    n_img, k = 33, 16384
+    desc, kpi = syn.make_bank_tensor(n_img, k, seed=SEED, device=dev)
+    bank = pkg.DescriptorBank.from_packed(desc, kpi)
+    und = pkg.blocked_order(pkg.exhaustive_pairs(n_img))
+    lists = {"both_directions": np.concatenate([und[:256], und[:256, ::-1]], 0), "one_direction": und[:512]}
+    ws = torch.empty(int(pkg._lib.lib().b200m_workspace_bytes(k, 512)), dtype=torch.uint8, device=dev)
+    r = {}
+    for name, pl in lists.items():
+        pairs = torch.from_numpy(np.ascontiguousarray(pl, dtype=np.int32)).to(dev)
+        out = pkg.match_pairs(bank, pairs, ratio=0.0, mutual=True, cap=k, workspace=ws)
+        torch.cuda.synchronize()
+        out.check_overflow()
+        best, med = _timed(torch, lambda: pkg.match_pairs(bank, pairs, ratio=0.0, mutual=True, cap=k, out=out, workspace=ws), 3)
+        r[name] = _int8_line(len(pairs), k, best, med, int8_peak)
+        r[name]["matches_per_pair"] = float(out.count.sum().item()) / len(pairs)
+        r[name]["digest"] = _flat_digest(torch, out)
+        if name == "both_directions":
+            ok = bool(torch.equal(out.count[:256], out.count[256:]))
+            for p in (0, 100, 255):                       # (q, t) of (a, b) == (t, q) of (b, a), as sets
+                n = int(out.count[p].item())
+                fwd = out.query_idx[p, :n].to(torch.int64) * k + out.train_idx[p, :n]
+                bwd = out.train_idx[256 + p, :n].to(torch.int64) * k + out.query_idx[256 + p, :n]
+                ok = ok and bool(torch.equal(torch.sort(fwd).values, torch.sort(bwd).values))
+            r[name]["transpose_symmetric"] = ok
+    r["workload"] = "mutual arg-best only (ratio test off), 512 directed pairs over 33 images x 16384 u8 descriptors"
+    r["note"] = ("ops counted as ONE K x K contraction per pair; the mutual check of every row runs as a second full sweep "
+                 "here, so 0.5 of the sweep rate is this mode's ceiling until reverse pairs are reused")
+    return r
+
+
+def secondary_u8_k2048(pkg, torch, dev, int8_peak, peaks):
+    """The reference's SHIPPED size (feature_extraction.py:10: at most 2,048 keypoints per image) on the u8 path:
+    4,096 pairs over 128 images x 2,048 x 128 u8, whole rule (2-NN + ratio 0.75 + mutual), bank resident. Small-K regime:
+    8 work items per pair, so the step is many short batches -- reported with tensor AND HBM fractions and the number of
+    kernel launches per step."""
+    syn = importlib.import_module("3d_reconstruction_b200.synthetic")
+    n_img, k, n_pairs = 128, 2048, 4096
+    desc, kpi = syn.make_bank_tensor(n_img, k, seed=SEED, device=dev)
+    bank = pkg.DescriptorBank.from_packed(desc, kpi)
+    pairs = torch.from_numpy(pkg.blocked_order(pkg.exhaustive_pairs(n_img))[:n_pairs]).to(dev)
+    ws = torch.empty(int(pkg._lib.lib().b200m_workspace_bytes(k, n_pairs)), dtype=torch.uint8, device=dev)
+    out = pkg.match_pairs(bank, pairs, cap=k, workspace=ws)
+    torch.cuda.synchronize()
+    out.check_overflow()
+    pkg.set_option("profile", 1)
+    try:
+        pkg.profile_read()
+        pkg.match_pairs(bank, pairs, cap=k, out=out, workspace=ws)
+        torch.cuda.synchronize()
+        launches = int(pkg.profile_read()["launches"])
+    finally:
+        pkg.set_option("profile", 0)
+    best, med = _timed(torch, lambda: pkg.match_pairs(bank, pairs, cap=k, out=out, workspace=ws), 5)
+    r = _int8_line(n_pairs, k, best, med, int8_peak)
+    hbm = float(peaks.get("hbm_gbs", 6650.0))
+    # algorithmic bytes per pair: both images' descriptor rows once (sorted query + sorted train), their norms, the row results
+    bytes_pair = 2 * k * 128 + 2 * k * 4 + k * 16
+    r.update({"matches": int(out.count.sum().item()), "digest": _flat_digest(torch, out), "launches_per_step": launches,
+              "algorithmic_gbs": bytes_pair * n_pairs / med / 1e9, "frac_of_hbm": bytes_pair * n_pairs / med / 1e9 / hbm,
+              "hbm_peak_gbs": hbm, "us_per_pair": 1e6 * med / n_pairs,
+              "workload": "4096 pairs over 128 images x 2048 u8 descriptors (the reference's shipped keypoint budget), whole rule"})
+    return r
+
+
 def secondary_c4(pkg, dmod, torch, dist, dev, rank, world, int8_peak):
     """BASELINE.json configs[3]: 2,000 images x 8,192 keypoints, each image against the next 32 (63,472 pairs).
     One GPU: the whole bank resident. N GPUs: rank 0 holds the bank on the host and every rank receives only its
@@ -383,6 +466,7 @@ def secondary_c5(pkg, torch, dev, peaks):
     from oracle import oracle_float
     n_img, k, n_pairs = 128, 2048, 4096
     bf16_peak = float(peaks.get("bf16_tflops", 1590.0))
+    hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
     res = {}
     rng = np.random.default_rng(0)
     pairs = np.stack([rng.integers(0, n_img, n_pairs), rng.integers(0, n_img, n_pairs)], 1).astype(np.int32)
@@ -407,6 +491,7 @@ def secondary_c5(pkg, torch, dev, peaks):
         cpu_s = (time.perf_counter() - t0) / 4
         res[f"c5_d{dim}"] = {"pairs": n_pairs, "pairs_per_s": n_pairs / med, "ms": 1e3 * med,
                              "algorithmic_tflops": flops / med / 1e12, "frac_of_bf16_peak": flops / med / 1e12 / bf16_peak,
+                             "frac_of_hbm": 2.0 * k * dim * 2 * n_pairs / med / 1e9 / hbm_peak,
                              "cpu_reference_pairs_per_s": 1.0 / cpu_s, "cpu_threads": torch.get_num_threads(),
                              "workload": f"4096 random pairs over 128 images x 2048 x {dim} bf16, mutual arg-max + threshold"}
         # the log double soft-max assignment head
@@ -425,10 +510,12 @@ def secondary_c5(pkg, torch, dev, peaks):
         cpu_s = (time.perf_counter() - t0) / 4
         res[f"c5_head_d{dim}"] = {"pairs": n_pairs, "pairs_per_s": n_pairs / med, "ms": 1e3 * med,
                                   "algorithmic_tflops": flops / med / 1e12, "frac_of_bf16_peak": flops / med / 1e12 / bf16_peak,
+                                  "frac_of_hbm": (2.0 * k * dim * 2 + 2.0 * k * 4) * n_pairs / med / 1e9 / hbm_peak,
                                   "cpu_reference_pairs_per_s": 1.0 / cpu_s, "cpu_threads": torch.get_num_threads(),
                                   "workload": f"same pairs, log double soft-max + matchability + filter_matches (D = {dim})"}
         del bank, out, ws, unit
     res["bf16_peak_tflops"] = bf16_peak
+    res["hbm_peak_gbs"] = hbm_peak      # frac_of_hbm: both images' bf16 rows (+ logits) per pair / time / measured copy bandwidth
     return res
 
 
@@ -699,6 +786,10 @@ def main():
             secondary["knn2"] = secondary_knn2(pkg, torch, dev, int8_peak)
             torch.cuda.empty_cache()
             secondary["c1_real_sift"] = secondary_real_sift(pkg, torch, dev, int8_peak)
+            torch.cuda.empty_cache()
+            secondary["mutual_only"] = secondary_mutual_only(pkg, torch, dev, int8_peak)
+            torch.cuda.empty_cache()
+            secondary["u8_k2048"] = secondary_u8_k2048(pkg, torch, dev, int8_peak, peaks)
             torch.cuda.empty_cache()
             secondary.update(secondary_c5(pkg, torch, dev, peaks))
 
