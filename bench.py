@@ -338,6 +338,17 @@ def secondary_mutual_only(pkg, torch, dev, int8_peak):
         r[name] = _int8_line(len(pairs), k, best, med, int8_peak)
         r[name]["matches_per_pair"] = float(out.count.sum().item()) / len(pairs)
         r[name]["digest"] = _flat_digest(torch, out)
+        pkg.set_option("profile", 1)                      # one more call, outside the timing: device ms per kernel class
+        try:
+            pkg.profile_read()
+            pkg.match_pairs(bank, pairs, ratio=0.0, mutual=True, cap=k, out=out, workspace=ws)
+            torch.cuda.synchronize()
+            pr = pkg.profile_read()
+        finally:
+            pkg.set_option("profile", 0)
+        r[name]["ms_by_kernel_class"] = {kk: pr[kk] for kk in ("first_sweep_ms", "verify_sweep_ms", "fallback_sweep_ms", "refine_ms",
+                                                             "select_ms", "emit_ms")}
+        r[name]["rows"] = {kk: vv for kk, vv in pkg.match_stats(ws).items() if kk.startswith("rows")}
         if name == "both_directions":
             ok = bool(torch.equal(out.count[:256], out.count[256:]))
             for p in (0, 100, 255):                       # (q, t) of (a, b) == (t, q) of (b, a), as sets

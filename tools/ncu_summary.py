@@ -24,9 +24,23 @@ def main(path):
         for h, u in zip(hdr, units):
             if h in WANT:
                 print(f"  {h:75s} {d[h]} {u}")
-        stalls = [(h, float(d[h])) for h in hdr if h.startswith("smsp__average_warp") and "issue_stalled" in h and h.endswith("_per_warp_active.pct") and d[h]]
-        stalls.sort(key=lambda x: -x[1])
-        print("  stalls:", ", ".join(f"{h.split('issue_stalled_')[1].split('_per_warp')[0]} {v:.1f}%" for h, v in stalls[:9]))
+        # warp-state section of --set full: smsp__average_warps_issue_stalled_<reason>_per_issue_active.ratio (warp cycles
+        # spent in <reason> per issued instruction); older ncu versions name it ..._per_warp_active.pct
+        stalls = {}
+        for h in hdr:
+            if "issue_stalled_" not in h or not d.get(h):
+                continue
+            if not (h.endswith("_per_issue_active.ratio") or h.endswith("_per_warp_active.pct")):
+                continue
+            reason = h.split("issue_stalled_")[1].rsplit("_per_", 1)[0]
+            try:
+                stalls[(reason, h.rsplit(".", 1)[1])] = float(d[h].replace(",", ""))
+            except ValueError:
+                pass
+        top = sorted(stalls.items(), key=lambda x: -x[1])[:10]
+        print("  stalls:", ", ".join(f"{r} {v:.2f} {'cyc/inst' if kind == 'ratio' else '%'}" for (r, kind), v in top))
+        if not top:
+            print("  (no warp-state metrics matched; headers mentioning 'stall':", [h for h in hdr if "stall" in h][:12], ")")
 
 
 if __name__ == "__main__":
