@@ -4,9 +4,10 @@ MatchAssignment.forward (:218-227) projects both descriptor sets, forms sim = md
 turns it into a log assignment matrix with a row soft-max, a column soft-max and the matchability
 logits (sigmoid_log_double_softmax, :196-208), and filter_matches (:235-254) keeps mutual arg-max pairs
 whose exp(score) exceeds filter_threshold. The reference materialises sim, two log-soft-max copies and
-the (M+1) x (N+1) score matrix; here two tensor-core sweeps per direction keep everything on chip:
-  pass 1  row log-sum-exp of sim in both directions (= row and column normalisers)
-  pass 2  arg-max of 2 sim - lse_row - lse_col + logsigmoid(z0) + logsigmoid(z1), both directions
+the (M+1) x (N+1) score matrix; here TWO tensor-core sweeps per pair keep everything on chip (option "float_sweep" = 0,
+the default; "float_sweep" = 1 runs one sweep per direction and pass, four per pair):
+  pass 1  log-sum-exp of every row AND every column of sim from one sweep (= row and column normalisers)
+  pass 2  row arg-max and column maxima of 2 sim - lse_row - lse_col + logsigmoid(z0) + logsigmoid(z1)
 then the mutual check / threshold / match list (b200m_assign_pairs_bf16, include/b200m.h).
 
   * assign_pairs      batched: projected descriptors (FloatBank) + matchability logits + pair list

@@ -1,10 +1,15 @@
-"""Multi-GPU plumbing: one process per GPU (torchrun), NCCL over NVLink for the two exchange steps.
+"""Multi-GPU plumbing: one process per GPU (torchrun), NCCL / NVLink for the exchange steps.
 
-The path shards by image pair with no collective during compute:
-  1. the packed bank is broadcast once from rank 0,
-  2. every rank enumerates the same pair list and takes its static, cost-balanced contiguous slice,
-  3. match lists are gathered to rank 0 at the end (variable length: counts first, then payload).
-Works with the gloo backend on CPU tensors too (used by the world_size-2 CPU tests).
+The path shards by image pair with no collective during compute. Two ways to run it:
+  * bank resident (bench.py's `value` leg): broadcast_bank_tensors once, every rank takes its static, cost-balanced
+    slice of the same pair list (my_pairs), gather_flat / gather_packed bring the variable-length lists to rank 0;
+  * from HOST buffers (match_pairs_host, bench.py's `e2e` leg): every rank uploads and prepares only its own image
+    slice, pairs between a rank's own images are matched while the prepared slices travel between the GPUs (copy
+    engines over symmetric memory; NCCL all-gathers as the fallback -- the choice is agreed by all ranks, agree_all),
+    the rest follows, one packed gather to `dst`. Count errors (overflow, bad pair) are raised on EVERY rank
+    (check_counts_everywhere), never on one rank alone in front of a collective.
+  * scatter_bank_window: the halo-sharded bank of a sequential sweep (BASELINE config 4).
+The helpers also work with the gloo backend on CPU tensors (the world_size-2 CPU tests).
 """
 from __future__ import annotations
 

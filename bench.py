@@ -16,7 +16,9 @@ pass of the full matching rule (2-NN, Lowe ratio 0.75, mutual check) over all pa
   cpu_baseline  cv2.BFMatcher(NORM_L2).knnMatch k=2 + reverse k=1 + ratio filter on a bounded sample
   config.result_digest / matches_total   64-bit digest of EVERY match record of the value leg, summed over
             the ranks: equal at N = 1, 2, 4, 8 <=> the N-GPU lists are the 1-GPU lists
-  secondary BASELINE.json configs 2, 4 and 5 measured outside the timed regions (short)
+  secondary the other BASELINE.json configs and regimes, measured outside the timed regions (short): C4 at every N; at
+            N = 1 also C2, the knnMatch(k=2) table, the real SIFT pair of config 1, mutual-only matching, the u8 path at
+            the reference's shipped 2,048 keypoints, C5 (float, raw arg-max and the full head) and the BoW vq kernel
 N > 1 splits the fixed pair list over the ranks (static cost-balanced partition): "scaling": "strong".
 """
 from __future__ import annotations
@@ -395,6 +397,38 @@ def secondary_u8_k2048(pkg, torch, dev, int8_peak, peaks):
               "hbm_peak_gbs": hbm, "us_per_pair": 1e6 * med / n_pairs,
               "workload": "4096 pairs over 128 images x 2048 u8 descriptors (the reference's shipped keypoint budget), whole rule"})
     return r
+
+
+def secondary_vq(pkg, torch, dev, peaks):
+    """Visual words of the BoW pair scheduler (matching.py:26-28) at the reference's own size: 290 images x 2,048
+    descriptors x 128 floats against 200 words; b200m_vq_f32 and its no-allocation twin b200m_vq_f32_static, outputs
+    compared. HBM-bound in principle (304 MB of descriptors read once), fp64 FMA-bound in practice."""
+    lib = pkg._lib.lib()
+    n_obs, dim, n_codes = 290 * 2048, 128, 200
+    g = torch.Generator(device=dev).manual_seed(5)
+    obs = (torch.rand((n_obs, dim), generator=g, device=dev) * 255).round()
+    cb = (torch.rand((n_codes, dim), generator=g, device=dev, dtype=torch.float64) * 255)
+    scratch = torch.empty((n_codes,), dtype=torch.float64, device=dev)
+    code = torch.empty((n_obs,), dtype=torch.int32, device=dev)
+    code_s = torch.empty_like(code)
+    st = torch.cuda.current_stream().cuda_stream
+
+    def run(static):
+        if static:
+            pkg._lib.check(lib.b200m_vq_f32_static(obs.data_ptr(), n_obs, dim, cb.data_ptr(), n_codes, code_s.data_ptr(), None, st))
+        else:
+            pkg._lib.check(lib.b200m_vq_f32(obs.data_ptr(), n_obs, dim, cb.data_ptr(), n_codes, code.data_ptr(), None,
+                                            scratch.data_ptr(), st))
+    run(False), run(True)
+    torch.cuda.synchronize()
+    _, med = _timed(torch, lambda: run(False), 5)
+    _, med_s = _timed(torch, lambda: run(True), 5)
+    hbm = float(peaks.get("hbm_gbs", 6650.0))
+    byt = n_obs * dim * 4 + n_obs * 4
+    return {"descriptors": n_obs, "words": n_codes, "ms": 1e3 * med, "ms_static_entry": 1e3 * med_s,
+            "descriptors_per_s": n_obs / med, "algorithmic_gbs": byt / med / 1e9, "frac_of_hbm": byt / med / 1e9 / hbm,
+            "fp64_gflops": 2.0 * n_obs * n_codes * dim / med / 1e9, "static_entry_identical": bool(torch.equal(code, code_s)),
+            "workload": "290 x 2048 float32 descriptors (128-d) -> nearest of 200 float64 words, scipy vq arithmetic"}
 
 
 def secondary_c4(pkg, dmod, torch, dist, dev, rank, world, int8_peak):
@@ -801,6 +835,8 @@ def main():
             secondary["mutual_only"] = secondary_mutual_only(pkg, torch, dev, int8_peak)
             torch.cuda.empty_cache()
             secondary["u8_k2048"] = secondary_u8_k2048(pkg, torch, dev, int8_peak, peaks)
+            torch.cuda.empty_cache()
+            secondary["vq"] = secondary_vq(pkg, torch, dev, peaks)
             torch.cuda.empty_cache()
             secondary.update(secondary_c5(pkg, torch, dev, peaks))
 
